@@ -1,0 +1,73 @@
+"""Import the UNMODIFIED reference (TEST INFRASTRUCTURE; build container only).
+
+``/root/reference`` exists only where the repo is built, never on the GPU box, so nothing
+that runs there (``-m gpu`` tests, ``smoke()``, ``bench.py``) may call this module.  It is
+used by ``oracle/make_golden.py`` to pin the NumPy restatement against the reference's own
+outputs, and by ``tests/test_oracle_vs_reference.py`` (skipped when the path is absent).
+
+Recipe: matplotlib is not installed, and two reference modules import
+it at module level (Utils/ConvOps_1d.py:314, Utils/boundary_conditions.py:4), so stub
+modules are inserted; ``/root/reference`` and ``/root/reference/Utils`` go on ``sys.path``
+exactly as the reference's scripts arrange it.
+"""
+from __future__ import annotations
+
+import importlib
+import importlib.util
+import os
+import sys
+import types
+import warnings
+
+REFERENCE_ROOT = os.environ.get("CPPRE_REFERENCE_ROOT", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isdir(os.path.join(REFERENCE_ROOT, "Utils"))
+
+
+def load():
+    """Returns a namespace with the reference modules.  Our own drop-in mirrors use the same
+    module names, so any of those already imported are evicted first."""
+    if not available():
+        raise RuntimeError(f"reference checkout not found at {REFERENCE_ROOT}")
+    for name in ("matplotlib", "matplotlib.pyplot"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    names = ["Utils", "Utils.ConvOps_2d", "Utils.ConvOps_1d", "Utils.VectorConvOps",
+             "ConvOps_2d", "ConvOps_1d", "ConvOps_0d", "ConvOps_Spatial", "boundary_conditions",
+             "VectorConvOps_Spatial", "fft_conv_pytorch", "fft_conv_pytorch.fft_conv",
+             "fft_conv_pytorch.utils", "Other_UQ", "Other_UQ.Evaluation",
+             "Other_UQ.Evaluation.PRE_estimations"]
+    saved = {n: sys.modules.pop(n) for n in names if n in sys.modules}
+    old_path = list(sys.path)
+    sys.path[:0] = [REFERENCE_ROOT, os.path.join(REFERENCE_ROOT, "Utils")]
+    ns = types.SimpleNamespace()
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ns.ConvOps_2d = importlib.import_module("Utils.ConvOps_2d")
+            ns.ConvOps_1d = importlib.import_module("ConvOps_1d")
+            ns.ConvOps_0d = importlib.import_module("ConvOps_0d")
+            ns.ConvOps_Spatial = importlib.import_module("ConvOps_Spatial")
+            ns.boundary_conditions = importlib.import_module("boundary_conditions")
+            ns.VectorConvOps_Spatial = importlib.import_module("VectorConvOps_Spatial")
+            ns.fft_conv = importlib.import_module("fft_conv_pytorch.fft_conv")
+            try:
+                ns.VectorConvOps = importlib.import_module("Utils.VectorConvOps")
+            except Exception as exc:  # pragma: no cover
+                ns.VectorConvOps = exc
+            # PRE_estimations lives in a directory without __init__.py: load by path.
+            spec = importlib.util.spec_from_file_location(
+                "_ref_PRE_estimations",
+                os.path.join(REFERENCE_ROOT, "Other_UQ", "Evaluation", "PRE_estimations.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            ns.PRE_estimations = mod
+    finally:
+        sys.path[:] = old_path
+        for n in names:
+            sys.modules.pop(n, None)
+        sys.modules.update(saved)
+    return ns
