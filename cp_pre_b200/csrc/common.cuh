@@ -1,0 +1,122 @@
+// Internal helpers shared by the libcppre translation units (not part of the C ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/cppre.h"
+
+namespace cppre {
+
+// ---- error plumbing ---------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+void set_path(const char* name);
+extern std::atomic<uint64_t> g_launches;
+inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define CPPRE_CHECK_CUDA(expr)                                                             \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            ::cppre::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),     \
+                               __FILE__, __LINE__);                                        \
+            return CPPRE_ERR_CUDA;                                                         \
+        }                                                                                  \
+    } while (0)
+
+#define CPPRE_REQUIRE(cond, code, ...)                                                     \
+    do {                                                                                   \
+        if (!(cond)) {                                                                     \
+            ::cppre::set_error(__VA_ARGS__);                                               \
+            return (code);                                                                 \
+        }                                                                                  \
+    } while (0)
+
+// Checks the launch that was just enqueued (configuration errors surface here).
+#define CPPRE_CHECK_LAUNCH()                                                               \
+    do {                                                                                   \
+        ::cppre::count_launch();                                                           \
+        CPPRE_CHECK_CUDA(cudaGetLastError());                                              \
+    } while (0)
+
+// ---- order-preserving float <-> uint32 key ------------------------------------------------
+// Unsigned order of the key == total order np.sort uses: negatives (reversed), zeros,
+// positives, +inf, then NaNs whose sign bit is clear.
+__host__ __device__ __forceinline__ uint32_t float_to_key(uint32_t bits) {
+    return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);
+}
+__host__ __device__ __forceinline__ uint32_t key_to_float_bits(uint32_t key) {
+    return (key & 0x80000000u) ? (key & 0x7fffffffu) : ~key;
+}
+
+// ---- star (3-point-per-axis) coefficient set of one derivative slot ----------------------
+enum Arm { ARM_C = 0, ARM_TM = 1, ARM_TP = 2, ARM_XM = 3, ARM_XP = 4, ARM_YM = 5, ARM_YP = 6 };
+constexpr uint32_t ARMS_T = (1u << ARM_TM) | (1u << ARM_TP);
+constexpr uint32_t ARMS_X = (1u << ARM_XM) | (1u << ARM_XP);
+constexpr uint32_t ARMS_Y = (1u << ARM_YM) | (1u << ARM_YP);
+constexpr uint32_t ARMS_C = (1u << ARM_C);
+constexpr uint32_t ARMS_ALL = 0x7fu;
+
+struct StarCoef {
+    float c[CPPRE_MAX_SLOTS][8];  // [slot][arm], arm 7 unused
+};
+
+// ---- generic tap list ----------------------------------------------------------------------
+struct DevTaps {
+    int32_t begin[CPPRE_MAX_SLOTS + 1];
+    int8_t o2[CPPRE_MAX_TAPS];
+    int8_t o1[CPPRE_MAX_TAPS];
+    int8_t o0[CPPRE_MAX_TAPS];
+    float c[CPPRE_MAX_TAPS];
+};
+
+struct FieldView {
+    const float* p;
+    int64_t sb, s2, s1, s0;
+};
+
+struct EpiDev {
+    int32_t mode, flags, reduce;
+    const float* ref;
+    int64_t rb, r2, r1, r0;
+    const float* weight;
+    float* out;
+    int64_t ob, o2, o1, o0;
+    float* scores;
+};
+
+struct Geometry {
+    int32_t B, N2, N1, N0;  // input extents
+    int32_t O2, O1, O0;     // output extents
+};
+
+// Host-side normalisation shared by the generic and the TMA path (stencil_common.cu).
+struct Prepared {
+    Geometry g;
+    DevTaps taps;
+    FieldView fields[CPPRE_MAX_FIELDS];
+    EpiDev epi;
+    float scalars[CPPRE_MAX_SCALARS];
+    int kind, n_fields, n_slots;
+};
+int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_field_t* fields,
+            const cppre_epilogue_t* epi, Prepared* out);
+int program_fields(int kind);
+int program_slots(int kind);
+
+int launch_generic(const Prepared& P, cudaStream_t stream);
+// returns 1 when eligible (and fills nothing), 0 otherwise
+int tma_eligible(const cppre_program_t* prog, const Prepared& P);
+int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+
+// ---- score reductions ------------------------------------------------------------------
+// Non-negative floats (after |.|) are ordered like their bit patterns, and a NaN (sign
+// cleared) compares above +inf, so an unsigned max both reduces and propagates NaN the way
+// np.max does.
+__device__ __forceinline__ uint32_t score_bits(float v) { return __float_as_uint(v); }
+
+}  // namespace cppre

@@ -1,0 +1,365 @@
+// K2 (per-cell statistics over the sample axis), K3 (order statistics along the sample axis)
+// and K5 (coverage counts): the conformal-calibration half of the hot path.
+//
+// Layout: score / residual tensors are [n, cells] with cells contiguous, so "thread = cell,
+// loop over samples" gives fully coalesced 128-byte warp accesses on every row.
+#include "common.cuh"
+
+namespace cppre {
+namespace {
+
+constexpr int kThreads = 256;
+
+// ------------------------------------------------------------------------------------------
+// K2: Welford in fp64, one thread per cell
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
+                    int64_t n, int64_t cells, double* __restrict__ mean, double* __restrict__ m2) {
+    const int64_t c = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (c >= cells) return;
+    const float* pa = a + c;
+    const float* pb = b ? b + c : nullptr;
+    if (n == 0) { mean[c] = 0.0; m2[c] = 0.0; return; }
+    // shifted sums in fp64: d = x - x_0, so sum(d^2) - sum(d)^2/n does not cancel unless the
+    // column mean is > 1e6 standard deviations away from its first sample
+    float x0 = __ldg(pa);
+    if (pb) x0 = __fsub_rn(x0, __ldg(pb));
+    const double k = (double)x0;
+    double s1 = 0.0, s2 = 0.0;
+    int64_t i = 0;
+    for (; i + 4 <= n; i += 4) {   // 4 independent loads in flight per thread
+        float x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            x[u] = __ldg(pa + (i + u) * as);
+            if (pb) x[u] = __fsub_rn(x[u], __ldg(pb + (i + u) * bs));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const double d = (double)x[u] - k;
+            s1 += d;
+            s2 = fma(d, d, s2);
+        }
+    }
+    for (; i < n; ++i) {
+        float x = __ldg(pa + i * as);
+        if (pb) x = __fsub_rn(x, __ldg(pb + i * bs));
+        const double d = (double)x - k;
+        s1 += d;
+        s2 = fma(d, d, s2);
+    }
+    mean[c] = k + s1 / (double)n;
+    const double v = s2 - s1 * s1 / (double)n;
+    m2[c] = v > 0.0 ? v : (v == v ? 0.0 : v);   // clamp round-off negatives, keep NaN
+}
+
+__global__ void __launch_bounds__(kThreads)
+cell_std_kernel(const double* __restrict__ m2, double count, float add_eps, int64_t cells,
+                float* __restrict__ sd, float* __restrict__ inv) {
+    const int64_t c = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (c >= cells) return;
+    const float v = __fadd_rn((float)sqrt(m2[c] / count), add_eps);
+    sd[c] = v;
+    if (inv) inv[c] = __fdiv_rn(1.0f, v);
+}
+
+// scores[i] = max_c |a-b| / mod  -- one block row per sample, grid-stride over cells
+__global__ void __launch_bounds__(kThreads)
+joint_score_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
+                   const float* __restrict__ mod, int64_t cells, int32_t chunks, float* scores) {
+    const int64_t i = blockIdx.x / chunks;
+    const int chunk = blockIdx.x % chunks;
+    uint32_t m = 0u;
+    for (int64_t c = (int64_t)chunk * kThreads + threadIdx.x; c < cells; c += (int64_t)chunks * kThreads) {
+        float x = __ldg(a + i * as + c);
+        if (b) x = __fsub_rn(x, __ldg(b + i * bs + c));
+        const float v = __fdiv_rn(fabsf(x), __ldg(mod + c));
+        // |x|/mod is >= 0 or NaN for mod > 0; fabsf clears a sign a negative mod would give
+        m = max(m, score_bits(fabsf(v)));
+    }
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(reinterpret_cast<unsigned int*>(scores) + i, m);
+}
+
+// ------------------------------------------------------------------------------------------
+// K3a: per-cell multi-rank select -- column tile in shared memory, one thread per cell,
+// data-independent bitonic network on order-preserving uint32 keys (threads never interact,
+// so no barriers inside the sort; column c of the tile lives in bank c: conflict-free).
+// ------------------------------------------------------------------------------------------
+constexpr int kSortCells = 32;       // cells (threads) per CTA -> 128-byte row segments
+constexpr int kMaxRanks = 32;
+
+struct RankList {
+    int32_t n;
+    int32_t r[kMaxRanks];
+};
+
+__global__ void __launch_bounds__(kSortCells)
+select_sort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int32_t npow2, int64_t cells,
+                   RankList ranks, float* __restrict__ out) {
+    extern __shared__ uint32_t keys[];   // [npow2][kSortCells]
+    const int lane = threadIdx.x;
+    const int64_t c = (int64_t)blockIdx.x * kSortCells + lane;
+    const bool live = c < cells;
+    bool has_nan = false;
+    for (int i = 0; i < npow2; ++i) {
+        uint32_t k = 0xffffffffu;        // padding sorts last
+        if (live && i < n) {
+            const uint32_t bits = __float_as_uint(__ldg(x + (int64_t)i * xs + c));
+            has_nan |= (bits & 0x7fffffffu) > 0x7f800000u;
+            k = float_to_key(bits);
+        }
+        keys[i * kSortCells + lane] = k;
+    }
+    for (int size = 2; size <= npow2; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll 4
+            for (int t = 0; t < (npow2 >> 1); ++t) {
+                const int lo = ((t & ~(stride - 1)) << 1) | (t & (stride - 1));
+                const int hi = lo | stride;
+                const bool up = (lo & size) == 0;
+                const uint32_t a = keys[lo * kSortCells + lane];
+                const uint32_t b = keys[hi * kSortCells + lane];
+                const bool sw = up ? (a > b) : (a < b);
+                keys[lo * kSortCells + lane] = sw ? b : a;
+                keys[hi * kSortCells + lane] = sw ? a : b;
+            }
+        }
+    }
+    if (!live) return;
+    for (int r = 0; r < ranks.n; ++r) {
+        const uint32_t k = keys[ranks.r[r] * kSortCells + lane];
+        out[(int64_t)r * cells + c] = has_nan ? __uint_as_float(0x7fc00000u)
+                                              : __uint_as_float(key_to_float_bits(k));
+    }
+}
+
+// K3b: per-cell single-rank radix select straight from global memory (any n).  8 passes of
+// 4 bits; the 16 bucket counters are compared-and-added so they stay in registers.
+__global__ void __launch_bounds__(kThreads)
+select_radix_kernel(const float* __restrict__ x, int64_t xs, int64_t n, int64_t cells, RankList ranks,
+                    float* __restrict__ out) {
+    const int64_t c = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (c >= cells) return;
+    const float* px = x + c;
+    bool has_nan = false;
+    for (int64_t i = 0; i < n; ++i)
+        has_nan |= (__float_as_uint(__ldg(px + i * xs)) & 0x7fffffffu) > 0x7f800000u;
+    for (int r = 0; r < ranks.n; ++r) {
+        uint32_t prefix = 0u, mask = 0u;
+        int64_t k = ranks.r[r];
+        for (int shift = 28; shift >= 0; shift -= 4) {
+            uint32_t cnt[16];
+#pragma unroll
+            for (int d = 0; d < 16; ++d) cnt[d] = 0u;
+            for (int64_t i = 0; i < n; ++i) {
+                const uint32_t key = float_to_key(__float_as_uint(__ldg(px + i * xs)));
+                const bool m = (key & mask) == prefix;
+                const uint32_t dig = (key >> shift) & 15u;
+#pragma unroll
+                for (int d = 0; d < 16; ++d) cnt[d] += (m && dig == (uint32_t)d) ? 1u : 0u;
+            }
+            uint32_t digit = 15u;
+            bool found = false;
+#pragma unroll
+            for (int d = 0; d < 16; ++d) {
+                if (!found) {
+                    if (k < (int64_t)cnt[d]) { digit = d; found = true; }
+                    else k -= cnt[d];
+                }
+            }
+            prefix |= digit << shift;
+            mask |= 15u << shift;
+        }
+        out[(int64_t)r * cells + c] = has_nan ? __uint_as_float(0x7fc00000u)
+                                              : __uint_as_float(key_to_float_bits(prefix));
+    }
+}
+
+// K3c: one 8-bit radix histogram pass over a flat array (Joint quantile across GPUs)
+__global__ void __launch_bounds__(kThreads)
+radix_hist_kernel(const float* __restrict__ x, int64_t n, uint32_t prefix, uint32_t mask, int shift,
+                  uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[256];
+    sh[threadIdx.x] = 0u;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+        const uint32_t key = float_to_key(__float_as_uint(__ldg(x + i)));
+        if ((key & mask) == prefix) atomicAdd(&sh[(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (sh[threadIdx.x]) atomicAdd(hist + threadIdx.x, sh[threadIdx.x]);
+}
+
+// ------------------------------------------------------------------------------------------
+// K5: coverage
+// ------------------------------------------------------------------------------------------
+template <bool BAND>
+__global__ void __launch_bounds__(kThreads)
+inside_kernel(const float* __restrict__ y, int64_t ys, const float* __restrict__ p0, int64_t s0,
+              const float* __restrict__ p1, int64_t s1, float q, int64_t cells, int32_t chunks,
+              uint32_t* __restrict__ inside) {
+    const int64_t i = blockIdx.x / chunks;
+    const int chunk = blockIdx.x % chunks;
+    uint32_t cnt = 0u;
+    for (int64_t c = (int64_t)chunk * kThreads + threadIdx.x; c < cells; c += (int64_t)chunks * kThreads) {
+        const float v = __ldg(y + i * ys + c);
+        float lo, hi;
+        if (BAND) {   // p0 = centre (or null), p1 = half width (or null); separately rounded ops
+            const float ctr = p0 ? __ldg(p0 + i * s0 + c) : 0.0f;
+            const float h = p1 ? __fmul_rn(q, __ldg(p1 + c)) : q;
+            lo = __fsub_rn(ctr, h);
+            hi = __fadd_rn(ctr, h);
+        } else {
+            lo = __ldg(p0 + i * s0 + c);
+            hi = __ldg(p1 + i * s1 + c);
+        }
+        cnt += (v >= lo && v <= hi) ? 1u : 0u;
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(inside + i, cnt);
+}
+
+int chunks_for(int64_t n, int64_t cells) {
+    // enough blocks to fill the machine a few times, never more than one block per 256 cells
+    int64_t want = (148 * 16 + n - 1) / (n > 0 ? n : 1);
+    const int64_t cap = (cells + kThreads - 1) / kThreads;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return (int)want;
+}
+
+}  // namespace
+}  // namespace cppre
+
+using namespace cppre;
+
+extern "C" {
+
+int cppre_cell_moments(const float* d_a, int64_t as, const float* d_b, int64_t bs, int64_t n,
+                       int64_t cells, double* d_mean, double* d_m2, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_mean && d_m2 && (d_a || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
+    const int64_t blocks = (cells + kThreads - 1) / kThreads;
+    cell_moments_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
+                                                                               d_mean, d_m2);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_cell_std(const double* d_m2, double count, float add_eps, int64_t cells, float* d_std,
+                   float* d_inv, void* stream) {
+    CPPRE_REQUIRE(cells >= 0 && count > 0, CPPRE_ERR_BAD_ARG, "bad size");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_m2 && d_std, CPPRE_ERR_BAD_ARG, "null pointer");
+    const int64_t blocks = (cells + kThreads - 1) / kThreads;
+    cell_std_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_m2, count, add_eps, cells, d_std,
+                                                                           d_inv);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_joint_score(const float* d_a, int64_t as, const float* d_b, int64_t bs, const float* d_mod,
+                      int64_t n, int64_t cells, float* d_scores, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    if (n == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_a && d_mod && d_scores, CPPRE_ERR_BAD_ARG, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    CPPRE_CHECK_CUDA(cudaMemsetAsync(d_scores, 0, sizeof(float) * (size_t)n, st));
+    if (cells == 0) return CPPRE_OK;
+    const int chunks = chunks_for(n, cells);
+    CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    joint_score_kernel<<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
+                                                                   d_scores);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+size_t cppre_select_workspace_bytes(int64_t, int64_t) { return 0; }
+
+int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                       const int32_t* h_ranks, int32_t n_ranks, float* d_out, void*, void* stream) {
+    CPPRE_REQUIRE(n >= 1 && cells >= 0 && n_ranks >= 0, CPPRE_ERR_BAD_ARG, "bad size (n=%lld)", (long long)n);
+    if (cells == 0 || n_ranks == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_scores && h_ranks && d_out, CPPRE_ERR_BAD_ARG, "null pointer");
+    CPPRE_REQUIRE(n < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "n too large");
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int r0 = 0; r0 < n_ranks; r0 += kMaxRanks) {
+        RankList rl;
+        rl.n = (n_ranks - r0 < kMaxRanks) ? n_ranks - r0 : kMaxRanks;
+        for (int r = 0; r < rl.n; ++r) {
+            CPPRE_REQUIRE(h_ranks[r0 + r] >= 0 && h_ranks[r0 + r] < n, CPPRE_ERR_BAD_ARG,
+                          "rank %d out of range [0,%lld)", h_ranks[r0 + r], (long long)n);
+            rl.r[r] = h_ranks[r0 + r];
+        }
+        float* out = d_out + (int64_t)r0 * cells;
+        int npow2 = 1;
+        while (npow2 < n) npow2 <<= 1;
+        const size_t smem = (size_t)npow2 * kSortCells * sizeof(uint32_t);
+        if (smem <= 128 * 1024) {
+            static size_t configured = 0;
+            if (smem > configured) {
+                CPPRE_CHECK_CUDA(cudaFuncSetAttribute(select_sort_kernel,
+                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                configured = smem;
+            }
+            const int64_t blocks = (cells + kSortCells - 1) / kSortCells;
+            select_sort_kernel<<<(unsigned)blocks, kSortCells, smem, st>>>(d_scores, row_stride, (int)n, npow2,
+                                                                          cells, rl, out);
+        } else {
+            const int64_t blocks = (cells + kThreads - 1) / kThreads;
+            select_radix_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d_scores, row_stride, n, cells, rl, out);
+        }
+        CPPRE_CHECK_LAUNCH();
+    }
+    return CPPRE_OK;
+}
+
+int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,
+                     uint32_t* d_hist, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && shift >= 0 && shift <= 24, CPPRE_ERR_BAD_ARG, "bad argument");
+    if (n == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_x && d_hist, CPPRE_ERR_BAD_ARG, "null pointer");
+    int64_t blocks = (n + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    radix_hist_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_x, n, prefix, mask, shift, d_hist);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_inside_count(const float* d_y, int64_t ys, const float* d_lo, int64_t los, const float* d_hi,
+                       int64_t his, int64_t n, int64_t cells, uint32_t* d_inside, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    if (n == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_inside && (cells == 0 || (d_y && d_lo && d_hi)), CPPRE_ERR_BAD_ARG, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    CPPRE_CHECK_CUDA(cudaMemsetAsync(d_inside, 0, sizeof(uint32_t) * (size_t)n, st));
+    if (cells == 0) return CPPRE_OK;
+    const int chunks = chunks_for(n, cells);
+    CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    inside_kernel<false><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_lo, los, d_hi, his, 0.0f, cells,
+                                                                     chunks, d_inside);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_inside_count_band(const float* d_y, int64_t ys, const float* d_centre, int64_t cs,
+                            const float* d_half, float q, int64_t n, int64_t cells, uint32_t* d_inside,
+                            void* stream) {
+    CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    if (n == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_inside && (cells == 0 || d_y), CPPRE_ERR_BAD_ARG, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    CPPRE_CHECK_CUDA(cudaMemsetAsync(d_inside, 0, sizeof(uint32_t) * (size_t)n, st));
+    if (cells == 0) return CPPRE_OK;
+    const int chunks = chunks_for(n, cells);
+    CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    inside_kernel<true><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_centre, cs, d_half, 0, q, cells,
+                                                                    chunks, d_inside);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,614 @@
+// K1, TMA star kernel (sm_100a): the fast path for residual programs whose derivative slots
+// are 3-point-per-axis "star" stencils (every operator ConvOps_1d/2d builds with Taylor order
+// 2, and any additive composition of them).
+//
+// Data movement
+//   * each CTA owns a tile of TX rows x 128 columns of one sample and marches along the slow
+//     axis N2 (time for contiguous [BS,Nt,Nx,Ny] data);
+//   * one elected thread stages plane t+k of every field into a ring of shared-memory tiles
+//     with cp.async.bulk.tensor (TMA), completion signalled on an mbarrier.  Tiles carry a
+//     +-1 row and +-4 column halo; out-of-range coordinates are zero-filled by the TMA unit,
+//     which IS the reference's zero "same" padding (F.conv3d padding=k//2) -- no boundary
+//     branches in the kernel;
+//   * the t-1 / t / t+1 centre values live in registers (a 3-deep register pipeline), so a
+//     plane is read from shared memory once for its centre values (128-bit LDS) plus the x+-1
+//     rows (128-bit LDS) and two scalar y+-1 edge values per row;
+//   * derivative coefficients sit in the kernel parameter (constant) bank and are used as
+//     FFMA constant operands; which arms of each slot exist is a template parameter, so zero
+//     taps cost nothing.
+// Epilogue (fused, same kernel): minus reference residual, |.|, per-cell weight
+// (1/modulation), then either a 128-bit coalesced store or a per-sample max/sum kept in
+// registers, reduced with redux.sync / shuffles and one atomic per warp -- the Joint score
+// never materialises the residual tensor.
+#include <cuda.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <type_traits>
+
+#include "common.cuh"
+#include "programs.cuh"
+
+namespace cppre {
+
+namespace {
+
+constexpr int kTPR = 32;            // threads per tile row (one warp)
+constexpr int kWarps = 8;           // thread rows per CTA
+constexpr int kThreads = kTPR * kWarps;
+constexpr int kTW = 4 * kTPR;       // tile width in cells (128)
+constexpr int kTWP = kTW + 8;       // smem row: 4 halo/pad cells each side keeps the interior 16-byte aligned
+constexpr int kMaxStages = 8;
+
+template <int NF>
+struct alignas(64) StarParams {
+    CUtensorMap map[NF];
+    StarCoef coef;
+    float scalars[CPPRE_MAX_SCALARS];
+    EpiDev e;
+    int32_t N2, N1, N0;   // logical extents (N1 = 1 in batch-rows mode)
+    int32_t R;            // extent of the tile-row axis: N1, or B in batch-rows mode
+    int32_t col_tiles, row_tiles;
+    int32_t stages;
+    uint32_t buf_bytes;   // bytes of one (stage, field) tile, 128-aligned
+};
+
+template <int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (N > 0) {
+        static_for<N - 1>(f);
+        f(std::integral_constant<int, N - 1>{});
+    }
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
+// Register-resident neighbourhood of one thread: RX rows x 4 columns per field.
+template <int NF, int RX, uint64_t MASKS>
+struct StarCtx {
+    const StarCoef& k;
+    float (&prev)[NF][RX][4];
+    float (&cur)[NF][RX][4];
+    float (&next)[NF][RX][4];
+    float (&xm)[NF][4];
+    float (&xp)[NF][4];
+    float (&ym)[NF][RX];
+    float (&yp)[NF][RX];
+
+    template <int SLOT, int FD, int I>
+    __device__ __forceinline__ float D() const {
+        constexpr int j = I / 4, i = I % 4;
+        constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
+        constexpr int jm = j > 0 ? j - 1 : 0, jp = j < RX - 1 ? j + 1 : RX - 1;
+        constexpr int im = i > 0 ? i - 1 : 0, ip = i < 3 ? i + 1 : 3;
+        const float* c = k.c[SLOT];
+        // accumulation in row-major tap order (t-, x-, y-, centre, y+, x+, t+), like the oracle
+        float acc = 0.0f;
+        if constexpr ((m >> ARM_TM) & 1) acc = fmaf(c[ARM_TM], prev[FD][j][i], acc);
+        if constexpr ((m >> ARM_XM) & 1) acc = fmaf(c[ARM_XM], (j > 0 ? cur[FD][jm][i] : xm[FD][i]), acc);
+        if constexpr ((m >> ARM_YM) & 1) acc = fmaf(c[ARM_YM], (i > 0 ? cur[FD][j][im] : ym[FD][j]), acc);
+        if constexpr ((m >> ARM_C) & 1) acc = fmaf(c[ARM_C], cur[FD][j][i], acc);
+        if constexpr ((m >> ARM_YP) & 1) acc = fmaf(c[ARM_YP], (i < 3 ? cur[FD][j][ip] : yp[FD][j]), acc);
+        if constexpr ((m >> ARM_XP) & 1) acc = fmaf(c[ARM_XP], (j < RX - 1 ? cur[FD][jp][i] : xp[FD][i]), acc);
+        if constexpr ((m >> ARM_TP) & 1) acc = fmaf(c[ARM_TP], next[FD][j][i], acc);
+        return acc;
+    }
+    template <int FD, int I>
+    __device__ __forceinline__ float V() const {
+        return cur[FD][I / 4][I % 4];
+    }
+};
+
+template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS>
+__global__ void __launch_bounds__(kThreads)
+star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
+    constexpr int NF = Prog<KIND>::NF;
+    constexpr int TX = kWarps * RX;               // rows per tile
+    constexpr int HALO = BATCH_ROWS ? 0 : 1;      // row halo only when rows are a stencil axis
+    constexpr int SR = TX + 2 * HALO;             // smem rows per tile
+    constexpr uint32_t BOX_BYTES = (uint32_t)(SR * kTWP * sizeof(float));
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 127u) & ~127u;   // TMA destinations must be 128-byte aligned
+    uint8_t* const sm = smem_raw + (base - raw);
+    const uint32_t bars = base + (uint32_t)p.stages * NF * p.buf_bytes;  // mbarriers follow the ring
+
+    const int tid = threadIdx.x;
+    const int tc = tid & (kTPR - 1);
+    const int tr = tid >> 5;
+
+    // flattened grid: column tile fastest, then row tile, then outer (sample) index, so CTAs
+    // that share halo rows are launched together and hit each other's lines in L2
+    int bid = blockIdx.x;
+    const int ct = bid % p.col_tiles;
+    bid /= p.col_tiles;
+    const int rt = bid % p.row_tiles;
+    const int outer = bid / p.row_tiles;
+    const int col0 = ct * kTW;
+    const int row0 = rt * TX;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.stages; ++s) mbar_init(bars + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int NPL = p.N2;
+    auto issue = [&](int plane, int stage) {
+        const uint32_t bar = bars + 8u * stage;
+        mbar_expect_tx(bar, BOX_BYTES * NF);
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const uint32_t dst = base + (uint32_t)(stage * NF + f) * p.buf_bytes;
+            if constexpr (BATCH_ROWS)   // map dims (N0, N2, B, 1): tile rows are samples
+                tma_load_4d(dst, &p.map[f], bar, col0 - 4, plane, row0, 0);
+            else                        // map dims (N0, N1, N2, B)
+                tma_load_4d(dst, &p.map[f], bar, col0 - 4, row0 - HALO, plane, outer);
+        }
+    };
+    if (tid == 0) {
+        const int pre = NPL < p.stages ? NPL : p.stages;
+        for (int q = 0; q < pre; ++q) issue(q, q);
+    }
+
+    float prev[NF][RX][4], cur[NF][RX][4], next[NF][RX][4];
+    float xm[NF][4], xp[NF][4], ym[NF][RX], yp[NF][RX];
+#pragma unroll
+    for (int f = 0; f < NF; ++f)
+#pragma unroll
+        for (int j = 0; j < RX; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) prev[f][j][i] = 0.0f;
+
+    // word offset of this thread's first centre cell inside a tile
+    const int cell_off = (HALO + tr * RX) * kTWP + 4 + 4 * tc;
+    auto tile = [&](int stage, int f) -> const float* {
+        return reinterpret_cast<const float*>(sm + (size_t)(stage * NF + f) * p.buf_bytes);
+    };
+    auto load_centres = [&](float (&dst)[NF][RX][4], int stage) {
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const float* t = tile(stage, f) + cell_off;
+#pragma unroll
+            for (int j = 0; j < RX; ++j) {
+                const float4 v = *reinterpret_cast<const float4*>(t + j * kTWP);
+                dst[f][j][0] = v.x; dst[f][j][1] = v.y; dst[f][j][2] = v.z; dst[f][j][3] = v.w;
+            }
+        }
+    };
+
+    mbar_wait(bars, 0);
+    load_centres(cur, 0);
+
+    const int y = col0 + 4 * tc;                   // first column of this thread
+    const bool col_live = y < p.N0;                // N0 % 4 == 0: a float4 is all in or all out
+    const bool score = p.e.mode == CPPRE_EPI_SCORE;
+    const bool rmax = p.e.reduce == CPPRE_REDUCE_MAX;
+    const bool in0 = (p.e.flags & CPPRE_FLAG_INTERIOR_0) != 0;
+    const bool in1 = (p.e.flags & CPPRE_FLAG_INTERIOR_1) != 0;
+    const bool in2 = (p.e.flags & CPPRE_FLAG_INTERIOR_2) != 0;
+    const bool do_abs = (p.e.flags & CPPRE_FLAG_ABS) != 0;
+    // SCORE mode: which of the four columns count (y == 0 / y == N0-1 dropped by INTERIOR_0)
+    const bool skip_first = score && in0 && y == 0;
+    const bool skip_last = score && in0 && y + 3 == p.N0 - 1;
+    uint32_t acc_max[RX];
+    float acc_sum[RX];
+#pragma unroll
+    for (int j = 0; j < RX; ++j) { acc_max[j] = 0u; acc_sum[j] = 0.0f; }
+
+    const StarCtx<NF, RX, MASKS> ctx{p.coef, prev, cur, next, xm, xp, ym, yp};
+
+    int stage = 0;
+    int nstage = p.stages > 1 ? 1 : 0;
+    uint32_t nphase = p.stages > 1 ? 0u : 1u;      // parity of the barrier guarding plane t+1
+    uint32_t phase = 0;
+    for (int t = 0; t < NPL; ++t) {
+        if (t + 1 < NPL) {
+            mbar_wait(bars + 8u * nstage, nphase);
+            load_centres(next, nstage);
+        } else {
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+#pragma unroll
+                for (int j = 0; j < RX; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) next[f][j][i] = 0.0f;
+        }
+        // x+-1 rows and y+-1 edge cells of plane t
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const float* tl = tile(stage, f) + cell_off;
+            if constexpr (!BATCH_ROWS) {
+                const float4 a = *reinterpret_cast<const float4*>(tl - kTWP);
+                const float4 b = *reinterpret_cast<const float4*>(tl + RX * kTWP);
+                xm[f][0] = a.x; xm[f][1] = a.y; xm[f][2] = a.z; xm[f][3] = a.w;
+                xp[f][0] = b.x; xp[f][1] = b.y; xp[f][2] = b.z; xp[f][3] = b.w;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { xm[f][i] = 0.0f; xp[f][i] = 0.0f; }
+            }
+#pragma unroll
+            for (int j = 0; j < RX; ++j) {
+                ym[f][j] = tl[j * kTWP - 1];
+                yp[f][j] = tl[j * kTWP + 4];
+            }
+        }
+
+        const bool plane_live = !(score && in2 && (t == 0 || t == NPL - 1));
+        if (plane_live && col_live) {
+            static_for<RX>([&](auto J) {
+                constexpr int j = decltype(J)::value;
+                const int row = row0 + tr * RX + j;
+                if (row < p.R) {
+                    const int b = BATCH_ROWS ? row : outer;
+                    const int x = BATCH_ROWS ? 0 : row;
+                    float r[4];
+                    r[0] = Prog<KIND>::template eval<4 * j + 0>(ctx, p.scalars);
+                    r[1] = Prog<KIND>::template eval<4 * j + 1>(ctx, p.scalars);
+                    r[2] = Prog<KIND>::template eval<4 * j + 2>(ctx, p.scalars);
+                    r[3] = Prog<KIND>::template eval<4 * j + 3>(ctx, p.scalars);
+                    if (p.e.ref) {
+                        const float4 q = __ldg(reinterpret_cast<const float4*>(
+                            p.e.ref + (int64_t)b * p.e.rb + (int64_t)t * p.e.r2 + (int64_t)x * p.e.r1 + y));
+                        r[0] -= q.x; r[1] -= q.y; r[2] -= q.z; r[3] -= q.w;
+                    }
+                    if (do_abs) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) r[i] = fabsf(r[i]);
+                    }
+                    if (p.e.weight) {
+                        const float4 w = __ldg(reinterpret_cast<const float4*>(
+                            p.e.weight + ((int64_t)t * p.N1 + x) * p.N0 + y));
+                        r[0] *= w.x; r[1] *= w.y; r[2] *= w.z; r[3] *= w.w;
+                    }
+                    if (!score) {
+                        float4 o = make_float4(r[0], r[1], r[2], r[3]);
+                        *reinterpret_cast<float4*>(p.e.out + (int64_t)b * p.e.ob + (int64_t)t * p.e.o2 +
+                                                   (int64_t)x * p.e.o1 + y) = o;
+                    } else if (!(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1))) {
+                        if (rmax) {
+                            uint32_t m = max(score_bits(r[1]), score_bits(r[2]));
+                            if (!skip_first) m = max(m, score_bits(r[0]));
+                            if (!skip_last) m = max(m, score_bits(r[3]));
+                            acc_max[j] = max(acc_max[j], m);
+                        } else {
+                            float s = r[1] + r[2];
+                            if (!skip_first) s += r[0];
+                            if (!skip_last) s += r[3];
+                            acc_sum[j] += s;
+                        }
+                    }
+                }
+            });
+        }
+        __syncthreads();                            // every warp is done reading ring slot `stage`
+        if (tid == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
+        // rotate the register pipeline and the ring cursors
+#pragma unroll
+        for (int f = 0; f < NF; ++f)
+#pragma unroll
+            for (int j = 0; j < RX; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { prev[f][j][i] = cur[f][j][i]; cur[f][j][i] = next[f][j][i]; }
+        stage = nstage;
+        phase = nphase;
+        if (++nstage == p.stages) { nstage = 0; nphase ^= 1u; }
+    }
+    (void)phase;
+
+    if (score) {
+        static_for<RX>([&](auto J) {
+            constexpr int j = decltype(J)::value;
+            const int row = row0 + tr * RX + j;
+            const int b = BATCH_ROWS ? row : outer;
+            const bool ok = row < p.R;               // warp-uniform (one warp per tile row)
+            if (rmax) {
+                const uint32_t m = __reduce_max_sync(0xffffffffu, acc_max[j]);
+                if (tc == 0 && ok && m) atomicMax(reinterpret_cast<unsigned int*>(p.e.scores) + b, m);
+            } else {
+                float s = acc_sum[j];
+#pragma unroll
+                for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                if (tc == 0 && ok) atomicAdd(p.e.scores + b, s);
+            }
+        });
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
+                cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+struct StarHost {
+    bool batch_rows;
+    uint64_t masks;     // arms actually present, 7 bits per slot
+    StarCoef coef;
+};
+
+// Classifies the request; returns false when some slot has a tap off the star.
+bool classify(const cppre_program_t* prog, const Prepared& P, StarHost* H) {
+    const Geometry& g = P.g;
+    if (g.O2 != g.N2 || g.O1 != g.N1 || g.O0 != g.N0) return false;   // "same" padding only
+    bool k333 = true, k313 = true;
+    for (int s = 0; s < P.n_slots; ++s) {
+        const int* k = prog->ksize[s];
+        const int* pd = prog->pad[s];
+        k333 = k333 && k[0] == 3 && k[1] == 3 && k[2] == 3 && pd[0] == 1 && pd[1] == 1 && pd[2] == 1;
+        k313 = k313 && k[0] == 3 && k[1] == 1 && k[2] == 3 && pd[0] == 1 && pd[1] == 0 && pd[2] == 1;
+    }
+    if (!(k333 || (k313 && g.N1 == 1))) return false;
+    H->batch_rows = !k333;
+    H->masks = 0;
+    memset(&H->coef, 0, sizeof(H->coef));
+    for (int s = 0; s < P.n_slots; ++s) {
+        for (int t = P.taps.begin[s]; t < P.taps.begin[s + 1]; ++t) {
+            const int a = P.taps.o2[t], b = P.taps.o1[t], c = P.taps.o0[t];
+            int arm = -1;
+            if (a == 0 && b == 0 && c == 0) arm = ARM_C;
+            else if (b == 0 && c == 0) arm = a < 0 ? ARM_TM : ARM_TP;
+            else if (a == 0 && c == 0) arm = b < 0 ? ARM_XM : ARM_XP;
+            else if (a == 0 && b == 0) arm = c < 0 ? ARM_YM : ARM_YP;
+            if (arm < 0) return false;
+            H->coef.c[s][arm] = P.taps.c[t];
+            H->masks |= (uint64_t)1 << (7 * s + arm);
+        }
+    }
+    return true;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+bool layout_ok(const Prepared& P, bool batch_rows) {
+    const Geometry& g = P.g;
+    if (g.N0 % 4 != 0 || g.N0 < 4) return false;
+    for (int f = 0; f < P.n_fields; ++f) {
+        const FieldView& v = P.fields[f];
+        if (!aligned16(v.p) || v.s0 != 1) return false;
+        if ((g.N1 > 1 && (v.s1 % 4 != 0 || v.s1 <= 0)) || (g.N2 > 1 && (v.s2 % 4 != 0 || v.s2 <= 0)) ||
+            (g.B > 1 && (v.sb % 4 != 0 || v.sb <= 0)))
+            return false;
+    }
+    const EpiDev& e = P.epi;
+    if (e.mode == CPPRE_EPI_STORE) {
+        if (!aligned16(e.out) || e.o0 != 1) return false;
+        if ((g.N1 > 1 && e.o1 % 4) || (g.N2 > 1 && e.o2 % 4) || (g.B > 1 && e.ob % 4)) return false;
+    }
+    if (e.ref) {
+        if (!aligned16(e.ref) || e.r0 != 1) return false;
+        if ((g.N1 > 1 && e.r1 % 4) || (g.N2 > 1 && e.r2 % 4) || (g.B > 1 && e.rb % 4)) return false;
+    }
+    if (e.weight && !aligned16(e.weight)) return false;
+    (void)batch_rows;
+    return true;
+}
+
+template <int KIND, bool BR, int RX, uint64_t MASKS>
+int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
+    constexpr int NF = Prog<KIND>::NF;
+    constexpr int TX = kWarps * RX;
+    constexpr int HALO = BR ? 0 : 1;
+    constexpr int SR = TX + 2 * HALO;
+    EncodeTiledFn encode = get_encode();
+    CPPRE_REQUIRE(encode != nullptr, CPPRE_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+
+    StarParams<NF> sp;
+    memset(&sp, 0, sizeof(sp));
+    const Geometry& g = P.g;
+    const int R = BR ? g.B : g.N1;
+    for (int f = 0; f < NF; ++f) {
+        const FieldView& v = P.fields[f];
+        // Tensor-map dims, innermost first.  3-D problems: (N0, N1, N2, B), box 136 x (TX+2) x 1 x 1.
+        // Batch-rows (1-D+time) problems: (N0, N2, B, 1), box 136 x 1 x TX x 1 -- same smem image,
+        // and the byte strides stay ascending for contiguous data.  A stride on an extent-1
+        // axis is never used for addressing but must still be a positive multiple of 16 bytes.
+        auto fix = [&](int64_t s, uint64_t extent) -> cuuint64_t {
+            return (cuuint64_t)((extent > 1 && s > 0) ? s : g.N0) * sizeof(float);
+        };
+        cuuint64_t dims[4], strides[3];
+        cuuint32_t box[4];
+        if (BR) {
+            dims[0] = g.N0; dims[1] = g.N2; dims[2] = g.B; dims[3] = 1;
+            strides[0] = fix(v.s2, dims[1]); strides[1] = fix(v.sb, dims[2]); strides[2] = fix(0, 1);
+            box[0] = kTWP; box[1] = 1; box[2] = SR; box[3] = 1;
+        } else {
+            dims[0] = g.N0; dims[1] = g.N1; dims[2] = g.N2; dims[3] = g.B;
+            strides[0] = fix(v.s1, dims[1]); strides[1] = fix(v.s2, dims[2]); strides[2] = fix(v.sb, dims[3]);
+            box[0] = kTWP; box[1] = SR; box[2] = 1; box[3] = 1;
+        }
+        const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+        CUresult rc = encode(&sp.map[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(v.p), dims,
+                             strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        CPPRE_REQUIRE(rc == CUDA_SUCCESS, CPPRE_ERR_UNSUPPORTED,
+                      "cuTensorMapEncodeTiled rejected field %d (CUresult %d)", f, (int)rc);
+    }
+    sp.coef = H.coef;
+    memcpy(sp.scalars, P.scalars, sizeof(sp.scalars));
+    sp.e = P.epi;
+    sp.N2 = g.N2;
+    sp.N1 = g.N1;
+    sp.N0 = g.N0;
+    sp.R = R;
+    sp.col_tiles = (g.N0 + kTW - 1) / kTW;
+    sp.row_tiles = (R + TX - 1) / TX;
+    sp.buf_bytes = ((uint32_t)(SR * kTWP * sizeof(float)) + 127u) & ~127u;
+
+    // ring depth: as deep as fits while leaving room for >= 2 CTAs per SM
+    static int env_stages = -1;
+    if (env_stages < 0) {
+        const char* s = getenv("CPPRE_TMA_STAGES");
+        env_stages = s ? atoi(s) : 0;
+    }
+    int stages = env_stages > 0 ? env_stages : 4;
+    const size_t per_stage = (size_t)NF * sp.buf_bytes;
+    while (stages > 2 && stages * per_stage + 256 > 110 * 1024) --stages;
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages < 2) stages = 2;
+    sp.stages = stages;
+    const size_t smem = stages * per_stage + 8 * kMaxStages + 128;
+    CPPRE_REQUIRE(smem <= 227 * 1024, CPPRE_ERR_UNSUPPORTED, "tile ring of %zu bytes exceeds shared memory", smem);
+
+    auto kern = star_kernel<KIND, BR, RX, MASKS>;
+    static size_t configured = 0;   // per instantiation
+    if (smem > configured) {
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    const int64_t blocks = (int64_t)sp.col_tiles * sp.row_tiles * (BR ? 1 : g.B);
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    kern<<<(unsigned)blocks, kThreads, smem, st>>>(sp);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+// Arm presets.  A request runs on the first preset whose arm sets contain the arms it uses.
+constexpr uint64_t pack(uint32_t a, uint32_t b = 0, uint32_t c = 0, uint32_t d = 0) {
+    return (uint64_t)a | ((uint64_t)b << 7) | ((uint64_t)c << 14) | ((uint64_t)d << 21);
+}
+constexpr uint32_t A1D = ARMS_C | ARMS_T | ARMS_Y;   // everything a 1-D+time star can hold
+
+typedef int (*LaunchFn)(const Prepared&, const StarHost&, cudaStream_t);
+struct Variant {
+    int kind;
+    bool batch_rows;
+    int rx;
+    uint64_t masks;
+    LaunchFn fn;
+};
+#define V(K, BR, RX, M) Variant{K, BR, RX, M, &launch_variant<K, BR, RX, M>}
+
+// "shipped" = the kernels the reference constructors produce on contiguous data (note
+// D_y == D_t); "fixed" = D_y along N0; "full" = any star.
+constexpr uint64_t M_LIN = pack(ARMS_ALL);
+constexpr uint64_t M_LIN1D = pack(A1D);
+constexpr uint64_t M_BURG = pack(ARMS_T, ARMS_Y, ARMS_C | ARMS_Y);
+constexpr uint64_t M_BURG_FULL = pack(A1D, A1D, A1D);
+constexpr uint64_t M_NSC = pack(ARMS_X, ARMS_T);
+constexpr uint64_t M_NSC_FIX = pack(ARMS_X, ARMS_Y);
+constexpr uint64_t M_NSC_FULL = pack(ARMS_ALL, ARMS_ALL);
+constexpr uint64_t M_NSM = pack(ARMS_T, ARMS_X, ARMS_T, ARMS_C | ARMS_X | ARMS_Y);
+constexpr uint64_t M_NSM_FIX = pack(ARMS_T, ARMS_X, ARMS_Y, ARMS_C | ARMS_X | ARMS_Y);
+constexpr uint64_t M_NSM_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL, ARMS_ALL);
+constexpr uint64_t M_MHD = pack(ARMS_T, ARMS_X, ARMS_T);
+constexpr uint64_t M_MHD_FIX = pack(ARMS_T, ARMS_X, ARMS_Y);
+constexpr uint64_t M_MHD_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL);
+
+const Variant kVariants[] = {
+    V(CPPRE_PROG_LINEAR, false, 1, M_LIN), V(CPPRE_PROG_LINEAR, false, 2, M_LIN),
+    V(CPPRE_PROG_LINEAR, true, 1, M_LIN1D), V(CPPRE_PROG_LINEAR, true, 2, M_LIN1D),
+    V(CPPRE_PROG_BURGERS, true, 1, M_BURG), V(CPPRE_PROG_BURGERS, true, 2, M_BURG),
+    V(CPPRE_PROG_BURGERS, true, 1, M_BURG_FULL),
+    V(CPPRE_PROG_NS_CONTINUITY, false, 1, M_NSC), V(CPPRE_PROG_NS_CONTINUITY, false, 2, M_NSC),
+    V(CPPRE_PROG_NS_CONTINUITY, false, 1, M_NSC_FIX), V(CPPRE_PROG_NS_CONTINUITY, false, 1, M_NSC_FULL),
+    V(CPPRE_PROG_NS_MOMENTUM, false, 1, M_NSM), V(CPPRE_PROG_NS_MOMENTUM, false, 2, M_NSM),
+    V(CPPRE_PROG_NS_MOMENTUM, false, 1, M_NSM_FIX), V(CPPRE_PROG_NS_MOMENTUM, false, 1, M_NSM_FULL),
+    V(CPPRE_PROG_MHD_CONTINUITY, false, 1, M_MHD), V(CPPRE_PROG_MHD_CONTINUITY, false, 2, M_MHD),
+    V(CPPRE_PROG_MHD_CONTINUITY, false, 1, M_MHD_FIX), V(CPPRE_PROG_MHD_CONTINUITY, false, 1, M_MHD_FULL),
+    V(CPPRE_PROG_MHD_MOMENTUM, false, 1, M_MHD), V(CPPRE_PROG_MHD_MOMENTUM, false, 1, M_MHD_FIX),
+    V(CPPRE_PROG_MHD_MOMENTUM, false, 1, M_MHD_FULL),
+    V(CPPRE_PROG_MHD_ENERGY, false, 1, M_MHD), V(CPPRE_PROG_MHD_ENERGY, false, 1, M_MHD_FIX),
+    V(CPPRE_PROG_MHD_ENERGY, false, 1, M_MHD_FULL),
+    V(CPPRE_PROG_MHD_INDUCTION, false, 1, M_MHD), V(CPPRE_PROG_MHD_INDUCTION, false, 1, M_MHD_FIX),
+    V(CPPRE_PROG_MHD_INDUCTION, false, 1, M_MHD_FULL),
+    V(CPPRE_PROG_MHD_GAUSS, false, 1, M_MHD), V(CPPRE_PROG_MHD_GAUSS, false, 2, M_MHD),
+    V(CPPRE_PROG_MHD_GAUSS, false, 1, M_MHD_FIX), V(CPPRE_PROG_MHD_GAUSS, false, 1, M_MHD_FULL),
+};
+#undef V
+
+int preferred_rx() {
+    static int rx = -1;
+    if (rx < 0) {
+        const char* s = getenv("CPPRE_TMA_RX");
+        rx = s ? atoi(s) : 0;
+    }
+    return rx;
+}
+
+const Variant* pick(int kind, const StarHost& H, const Geometry& g) {
+    // first preset (table order = tightest first) that covers the arms in use; among equal
+    // presets prefer the requested / heuristic rows-per-thread
+    const Variant* best = nullptr;
+    int want = preferred_rx();
+    if (want <= 0) {
+        const int R = H.batch_rows ? g.B : g.N1;
+        want = R >= 16 ? 2 : 1;
+    }
+    for (const Variant& v : kVariants) {
+        if (v.kind != kind || v.batch_rows != H.batch_rows) continue;
+        if ((H.masks & ~v.masks) != 0) continue;
+        if (!best) best = &v;
+        else if (v.masks == best->masks && v.rx == want) best = &v;
+        if (best->masks != v.masks) break;
+    }
+    return best;
+}
+
+}  // namespace
+
+int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
+    StarHost H;
+    if (!classify(prog, P, &H)) return 0;
+    if (!layout_ok(P, H.batch_rows)) return 0;
+    if (P.g.N2 < 1) return 0;
+    return pick(P.kind, H, P.g) != nullptr;
+}
+
+int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t st) {
+    StarHost H;
+    CPPRE_REQUIRE(classify(prog, P, &H) && layout_ok(P, H.batch_rows), CPPRE_ERR_UNSUPPORTED,
+                  "request does not qualify for the TMA star kernel");
+    const Variant* v = pick(P.kind, H, P.g);
+    CPPRE_REQUIRE(v != nullptr, CPPRE_ERR_UNSUPPORTED, "no TMA variant for program %d", P.kind);
+    return v->fn(P, H, st);
+}
+
+}  // namespace cppre

@@ -1,0 +1,384 @@
+"""Tensor-level wrappers over the libcppre C ABI.
+
+PyTorch is plumbing here: it owns device memory and streams; every computation is one of the
+library's CUDA kernels, enqueued on the caller's current stream.  Inputs living on the host
+(CPU tensors, NumPy arrays -- the reference's default) are staged to the
+current CUDA device and results are brought back, so the reference-facing API is a drop-in; a
+host without CUDA raises -- there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+# --------------------------------------------------------------------------------------
+# device plumbing
+# --------------------------------------------------------------------------------------
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("cp_pre_b200 needs a CUDA device (B200, sm_100a): it has no CPU fallback")
+
+
+def _stream(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)
+
+
+class Staged:
+    """Remembers where a user array came from so results can be returned the same way."""
+
+    def __init__(self, x):
+        self.numpy = isinstance(x, np.ndarray) or np.isscalar(x)
+        self.device = None if self.numpy else (x.device if isinstance(x, torch.Tensor) else None)
+
+    def back(self, t: torch.Tensor):
+        if self.numpy:
+            return t.detach().cpu().numpy()
+        if self.device is not None and t.device != self.device:
+            return t.to(self.device)
+        return t
+
+
+def to_cuda(x, dtype=torch.float32) -> torch.Tensor:
+    """Host array / CPU tensor -> current CUDA device (H2D); CUDA tensor -> itself."""
+    require_cuda()
+    if isinstance(x, torch.Tensor):
+        t = x.detach()
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(x))
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    if not t.is_cuda:
+        t = t.cuda(non_blocking=False)
+    return t
+
+
+def _rows(t: torch.Tensor):
+    """[n, ...] -> ([n, cells] with unit cell stride, row stride)."""
+    n = t.shape[0]
+    flat = t.reshape(n, -1)
+    if flat.numel() and flat.shape[1] > 1 and flat.stride(1) != 1:
+        flat = flat.contiguous()
+    rs = flat.stride(0) if flat.shape[0] > 1 else (flat.shape[1] if flat.dim() > 1 else 1)
+    return flat, int(rs)
+
+
+# --------------------------------------------------------------------------------------
+# K1: residual programs
+# --------------------------------------------------------------------------------------
+def _axis_order(t: torch.Tensor):
+    """Permutation of the logical axes (1,2,3) that puts the largest stride first."""
+    strides = [abs(t.stride(d)) if t.shape[d] > 1 else -1 for d in (1, 2, 3)]
+    # extent-1 axes keep their place; the others are ordered by stride
+    real = [d for d in range(3) if strides[d] >= 0]
+    order = sorted(real, key=lambda d: -strides[d])
+    perm = list(range(3))
+    for slot, d in zip(real, order):
+        perm[slot] = d
+    return perm
+
+
+def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.ndarray],
+                pads: Sequence[Sequence[int]], scalars: Sequence[float] = (), *,
+                mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
+                ref: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None,
+                path: int = L.PATH_AUTO, canonicalise: bool = True) -> torch.Tensor:
+    """Runs one fused residual program.
+
+    fields   CUDA fp32 tensors, all of logical shape [B, N2, N1, N0], any strides (views welcome)
+    kernels  one dense fp32 ndarray [k2, k1, k0] per derivative slot (cross-correlation taps)
+    pads     per-slot zero padding (p2, p1, p0)
+    Returns the [B, O2, O1, O0] field (STORE) or the [B] scores (SCORE).
+    """
+    lib = L.load()
+    require_cuda()
+    f0 = fields[0]
+    if any(f.shape != f0.shape for f in fields):
+        raise ValueError("all fields of a residual program must share one shape")
+    if any(f.dtype != torch.float32 for f in fields):
+        raise RuntimeError("expected scalar type Float (fields must be float32)")
+    kernels = [np.ascontiguousarray(k, dtype=np.float32) for k in kernels]
+    pads = [tuple(int(v) for v in p) for p in pads]
+
+    # Physical-layout canonicalisation: a permuted view such
+    # as pred.permute(0,1,4,2,3) is processed in its memory order -- fields, taps, padding,
+    # weight and reference are permuted alike and the result is returned as the inverse
+    # permuted view, so no .contiguous() copy of the input is ever made.
+    perm = [0, 1, 2]
+    if canonicalise and f0.numel() > 0 and all(_axis_order(f) == _axis_order(f0) for f in fields):
+        perm = _axis_order(f0)
+    if perm != [0, 1, 2]:
+        tperm = [0] + [1 + d for d in perm]
+        fields = [f.permute(tperm) for f in fields]
+        kernels = [np.ascontiguousarray(np.transpose(k, perm)) for k in kernels]
+        pads = [tuple(p[d] for d in perm) for p in pads]
+        if ref is not None:
+            ref = ref.permute(tperm)
+        if weight is not None:
+            weight = weight.permute(perm).contiguous()
+        bit = {0: L.FLAG_INTERIOR_2, 1: L.FLAG_INTERIOR_1, 2: L.FLAG_INTERIOR_0}
+        nf = flags & L.FLAG_ABS
+        for new_axis, old_axis in enumerate(perm):
+            if flags & bit[old_axis]:
+                nf |= bit[new_axis]
+        flags = nf
+        f0 = fields[0]
+
+    B, N2, N1, N0 = (int(v) for v in f0.shape)
+    prog = L.Program()
+    prog.kind, prog.n_fields, prog.n_slots = kind, len(fields), len(kernels)
+    for s, (k, p) in enumerate(zip(kernels, pads)):
+        if k.ndim != 3:
+            raise ValueError("slot kernels must be 3-D [k2,k1,k0]")
+        for d in range(3):
+            prog.ksize[s][d] = k.shape[d]
+            prog.pad[s][d] = p[d]
+        prog.h_taps[s] = k.ctypes.data
+    for i, v in enumerate(scalars):
+        prog.scalars[i] = float(v)
+    k0, p0 = kernels[0], pads[0]
+    O = [n + 2 * p - k + 1 for n, p, k in zip((N2, N1, N0), p0, k0.shape)]
+    if min(O) < 0:
+        raise RuntimeError(f"kernel size {tuple(k0.shape)} can't be greater than the padded input {(N2, N1, N0)}")
+
+    fl = (L.Field * len(fields))()
+    for i, f in enumerate(fields):
+        fl[i].d_data = f.data_ptr() if f.numel() else 0
+        for d in range(4):
+            fl[i].stride[d] = f.stride(d)
+    epi = L.Epilogue()
+    epi.mode, epi.flags, epi.reduce = mode, flags, reduce
+    dev = f0.device
+    keep = []
+    if ref is not None:
+        if tuple(ref.shape) != (B, *O):
+            raise ValueError(f"reference residual has shape {tuple(ref.shape)}, expected {(B, *O)}")
+        epi.d_ref = ref.data_ptr()
+        for d in range(4):
+            epi.ref_stride[d] = ref.stride(d)
+        keep.append(ref)
+    if weight is not None:
+        if tuple(weight.shape) != tuple(O):
+            raise ValueError(f"weight has shape {tuple(weight.shape)}, expected {tuple(O)}")
+        weight = weight.contiguous()
+        epi.d_weight = weight.data_ptr()
+        keep.append(weight)
+    with torch.cuda.device(dev):
+        if mode == L.EPI_STORE:
+            out = torch.empty((B, *O), dtype=torch.float32, device=dev)
+            epi.d_out = out.data_ptr() if out.numel() else 0
+            for d in range(4):
+                epi.out_stride[d] = out.stride(d)
+        else:
+            out = torch.empty((B,), dtype=torch.float32, device=dev)
+            epi.d_scores = out.data_ptr() if B else 0
+        shape = (C.c_int64 * 4)(B, N2, N1, N0)
+        L.check(lib.cppre_residual(C.byref(prog), shape, fl, C.byref(epi), int(path), _stream(dev)))
+    if mode == L.EPI_STORE and perm != [0, 1, 2]:
+        inv = [0] * 3
+        for new_axis, old_axis in enumerate(perm):
+            inv[old_axis] = new_axis
+        out = out.permute([0] + [1 + d for d in inv])
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# K2 / K3 / K5: conformal calibration
+# --------------------------------------------------------------------------------------
+def cell_moments(a: torch.Tensor, b: Optional[torch.Tensor] = None):
+    """Per-cell (mean, M2) in fp64 of a-b over axis 0; a, b CUDA fp32 [n, ...]."""
+    lib = L.load()
+    fa, sa = _rows(a)
+    fb, sb = (None, 0) if b is None else _rows(b)
+    n, cells = fa.shape
+    mean = torch.empty(cells, dtype=torch.float64, device=a.device)
+    m2 = torch.empty(cells, dtype=torch.float64, device=a.device)
+    with torch.cuda.device(a.device):
+        L.check(lib.cppre_cell_moments(_ptr(fa), sa, _ptr(fb), sb, n, cells, _ptr(mean), _ptr(m2),
+                                       _stream(a.device)))
+    return mean, m2
+
+
+def cell_std_from_m2(m2: torch.Tensor, count: float, eps: float = 0.0, want_inv: bool = False):
+    lib = L.load()
+    cells = m2.numel()
+    sd = torch.empty(cells, dtype=torch.float32, device=m2.device)
+    inv = torch.empty(cells, dtype=torch.float32, device=m2.device) if want_inv else None
+    with torch.cuda.device(m2.device):
+        L.check(lib.cppre_cell_std(_ptr(m2), float(count), float(eps), cells, _ptr(sd), _ptr(inv),
+                                   _stream(m2.device)))
+    return (sd, inv) if want_inv else sd
+
+
+def cell_std(a: torch.Tensor, b: Optional[torch.Tensor] = None, eps: float = 0.0, want_inv: bool = False):
+    """Population std (ddof = 0) over axis 0 of a-b, shaped like a[0]."""
+    if a.shape[0] == 0:
+        raise ValueError("std over an empty sample axis")
+    _, m2 = cell_moments(a, b)
+    res = cell_std_from_m2(m2, a.shape[0], eps, want_inv)
+    if want_inv:
+        return res[0].reshape(a.shape[1:]), res[1].reshape(a.shape[1:])
+    return res.reshape(a.shape[1:])
+
+
+def joint_score(a: torch.Tensor, b: Optional[torch.Tensor], mod: torch.Tensor) -> torch.Tensor:
+    lib = L.load()
+    fa, sa = _rows(a)
+    fb, sb = (None, 0) if b is None else _rows(b)
+    n, cells = fa.shape
+    m = mod.reshape(-1).contiguous()
+    if m.numel() != cells:
+        raise ValueError(f"modulation has {m.numel()} cells, residuals have {cells}")
+    out = torch.empty(n, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        L.check(lib.cppre_joint_score(_ptr(fa), sa, _ptr(fb), sb, _ptr(m), n, cells, _ptr(out),
+                                      _stream(a.device)))
+    return out
+
+
+def select_ranks(scores: torch.Tensor, ranks: Sequence[int]) -> torch.Tensor:
+    """[len(ranks), *scores.shape[1:]]: the ranks[r]-th smallest along axis 0 (NaN-aware)."""
+    lib = L.load()
+    fs, rs = _rows(scores)
+    n, cells = fs.shape
+    ranks = [int(r) for r in ranks]
+    out = torch.empty((len(ranks), cells), dtype=torch.float32, device=scores.device)
+    arr = (C.c_int32 * max(len(ranks), 1))(*ranks)
+    with torch.cuda.device(scores.device):
+        L.check(lib.cppre_select_ranks(_ptr(fs), rs, n, cells, arr, len(ranks), _ptr(out), None,
+                                       _stream(scores.device)))
+    return out.reshape((len(ranks),) + tuple(scores.shape[1:]))
+
+
+def radix_hist(x: torch.Tensor, prefix: int, mask: int, shift: int, hist: torch.Tensor):
+    lib = L.load()
+    flat = x.reshape(-1).contiguous()
+    with torch.cuda.device(x.device):
+        L.check(lib.cppre_radix_hist(_ptr(flat), flat.numel(), prefix, mask, shift, _ptr(hist),
+                                     _stream(x.device)))
+    return hist
+
+
+def inside_count(y: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor) -> torch.Tensor:
+    """uint32-valued int32 tensor [n]: cells of sample i with lo <= y <= hi.  lo/hi are
+    [cells...] (broadcast over samples) or [n, cells...]."""
+    lib = L.load()
+    fy, sy = _rows(y)
+    n, cells = fy.shape
+
+    def bound(t):
+        t = t.to(torch.float32)
+        if t.numel() == 1:
+            t = t.reshape(1).expand(cells)
+        if t.numel() == cells:
+            return t.reshape(-1).contiguous(), 0
+        if t.numel() == n * cells:
+            f, s = _rows(t.reshape(y.shape))
+            return f, s
+        f, s = _rows(torch.broadcast_to(t, y.shape).contiguous())
+        return f, s
+
+    flo, slo = bound(lo)
+    fhi, shi = bound(hi)
+    out = torch.empty(n, dtype=torch.int32, device=y.device)
+    with torch.cuda.device(y.device):
+        L.check(lib.cppre_inside_count(_ptr(fy), sy, _ptr(flo), slo, _ptr(fhi), shi, n, cells, _ptr(out),
+                                       _stream(y.device)))
+    return out
+
+
+def inside_count_band(y: torch.Tensor, centre: Optional[torch.Tensor], half: Optional[torch.Tensor],
+                      q: float) -> torch.Tensor:
+    """Cells with centre - q*half <= y <= centre + q*half (sets never materialised)."""
+    lib = L.load()
+    fy, sy = _rows(y)
+    n, cells = fy.shape
+    fc, sc = (None, 0) if centre is None else _rows(centre)
+    fh = None if half is None else half.reshape(-1).contiguous()
+    out = torch.empty(n, dtype=torch.int32, device=y.device)
+    with torch.cuda.device(y.device):
+        L.check(lib.cppre_inside_count_band(_ptr(fy), sy, _ptr(fc), sc, _ptr(fh), float(q), n, cells,
+                                            _ptr(out), _stream(y.device)))
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# boundary conditions, spectral pointwise
+# --------------------------------------------------------------------------------------
+def make_bc(types, widths, values) -> L.BC:
+    bc = L.BC()
+    for i in range(4):
+        bc.type[i], bc.width[i], bc.value[i] = int(types[i]), int(widths[i]), float(values[i])
+    return bc
+
+
+def bc_padded_shape(bc: L.BC, h: int, w: int):
+    hp, wp = C.c_int64(), C.c_int64()
+    L.check(L.load().cppre_bc_padded_shape(C.byref(bc), h, w, C.byref(hp), C.byref(wp)))
+    return hp.value, wp.value
+
+
+def bc_index_map(bc: L.BC, h: int, w: int):
+    """(rows, row_values, cols, col_values): source indices (-1 = Dirichlet constant) and the
+    constants, straight from the library's host-side resolver."""
+    hp, wp = bc_padded_shape(bc, h, w)
+    rows, cols = (C.c_int32 * max(hp, 1))(), (C.c_int32 * max(wp, 1))()
+    rv, cv = (C.c_float * max(hp, 1))(), (C.c_float * max(wp, 1))()
+    L.check(L.load().cppre_bc_index_map(C.byref(bc), h, w, rows, rv, cols, cv))
+    return (np.array(rows[:hp], dtype=np.int32), np.array(rv[:hp], dtype=np.float32),
+            np.array(cols[:wp], dtype=np.int32), np.array(cv[:wp], dtype=np.float32))
+
+
+def bc_pad(x: torch.Tensor, bc: L.BC) -> torch.Tensor:
+    """x CUDA fp32 [..., H, W] -> [..., Hp, Wp]."""
+    lib = L.load()
+    h, w = x.shape[-2:]
+    hp, wp = bc_padded_shape(bc, h, w)
+    xc = x.contiguous()
+    n_img = xc.numel() // max(h * w, 1) if h * w else int(np.prod(x.shape[:-2]))
+    out = torch.empty(tuple(x.shape[:-2]) + (hp, wp), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(lib.cppre_bc_pad(_ptr(xc), n_img, h, w, C.byref(bc), _ptr(out), _stream(x.device)))
+    return out
+
+
+def bc_conv2d(x: torch.Tensor, bc: L.BC, kernel: np.ndarray) -> torch.Tensor:
+    lib = L.load()
+    h, w = x.shape[-2:]
+    hp, wp = bc_padded_shape(bc, h, w)
+    k = np.ascontiguousarray(kernel, dtype=np.float32)
+    kh, kw = k.shape
+    if hp - kh + 1 < 1 or wp - kw + 1 < 1:
+        raise RuntimeError(f"Kernel size {(kh, kw)} can't be greater than actual input size {(hp, wp)}")
+    xc = x.contiguous()
+    n_img = int(np.prod(x.shape[:-2]))
+    out = torch.empty(tuple(x.shape[:-2]) + (hp - kh + 1, wp - kw + 1), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(lib.cppre_bc_conv2d(_ptr(xc), n_img, h, w, C.byref(bc),
+                                    k.ctypes.data_as(C.POINTER(C.c_float)), kh, kw, _ptr(out),
+                                    _stream(x.device)))
+    return out
+
+
+def spectral_pointwise(sig_hat: torch.Tensor, ker_hat: torch.Tensor, flags: int, eps: float = 1e-6):
+    """sig_hat complex64 [B, ...], ker_hat complex64 [...]; returns sig_hat * g(ker_hat)."""
+    lib = L.load()
+    s = sig_hat.contiguous()
+    k = ker_hat.contiguous()
+    m = k.numel()
+    batch = s.numel() // max(m, 1)
+    out = torch.empty_like(s)
+    sr, kr, orr = (torch.view_as_real(t) for t in (s, k, out))
+    with torch.cuda.device(s.device):
+        L.check(lib.cppre_spectral_pointwise(_ptr(sr), _ptr(kr), batch, m, flags, float(eps), _ptr(orr),
+                                             _stream(s.device)))
+    return out

@@ -1,0 +1,184 @@
+"""Fused residual programs: one libcppre kernel per PDE residual, plus the calibration
+pipelines built on them.
+
+A program binds the reference's *live* operator objects (so whatever is in ``.kernel`` at call
+time is what runs) to one of the library's residual kinds.  ``residual`` returns what the
+reference's ``residual(vars, boundary)`` functions return; ``abs_scores`` / ``joint_scores`` run
+the fused epilogues (|r - ref|, per-cell weight, per-sample max) so no intermediate tensor makes
+an HBM round trip.
+
+    prog = programs.ns_momentum(D_t, D_x, D_y, D_xx_yy, dx, dy, dt, nu)
+    res  = prog.residual(vars)                       # [BS, Nt-2, Nx-2, Ny-2], like the scripts
+    s    = prog.joint_scores(vars, inv_modulation)   # [BS], nothing but the scores is written
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+
+
+class ResidualProgram:
+    """``kind`` evaluated with taps from ``operators`` on the fields ``field_index`` of vars."""
+
+    def __init__(self, kind: int, operators: Sequence, scalars: Sequence[float],
+                 field_index: Optional[Sequence[int]], ndim_space_time: int, name: str):
+        self.kind, self.operators, self.scalars = kind, list(operators), [float(s) for s in scalars]
+        self.field_index = None if field_index is None else list(field_index)
+        self.nd = ndim_space_time          # 3 for [BS,Nt,Nx,Ny] data, 2 for [BS,Nt,Nx]
+        self.name = name
+        self.path = L.PATH_AUTO
+
+    # -- plumbing ---------------------------------------------------------------------
+    def _slots(self):
+        ks, pads = [], []
+        for op in self.operators:
+            k = op._taps(op.kernel)         # AttributeError if the operator has no kernel
+            k3 = op._fl.kernel3(k)
+            ks.append(k3)
+            pads.append(tuple(s // 2 for s in k3.shape))
+        return ks, pads
+
+    def _fields(self, vars_):
+        v = ops.to_cuda(vars_)
+        if self.field_index is None:        # single-field programs take the field itself
+            fs = [v]
+        else:
+            fs = [v[:, j] for j in self.field_index]
+        if self.nd == 2:
+            fs = [f.unsqueeze(2) for f in fs]
+        if fs[0].dim() != 4:
+            raise RuntimeError(f"{self.name}: expected {'[BS,F,Nt,Nx,Ny]' if self.field_index else '[BS,Nt,...]'} input")
+        return fs
+
+    def _interior_flags(self):
+        return (L.FLAG_INTERIOR_0 | L.FLAG_INTERIOR_2 | (L.FLAG_INTERIOR_1 if self.nd == 3 else 0))
+
+    def _unsq(self, t):
+        """[..., Nt, Nx] <-> library layout [..., Nt, 1, Nx] for 1-D+time data."""
+        return t.unsqueeze(-2) if (t is not None and self.nd == 2) else t
+
+    def _crop(self, full):
+        if self.nd == 2:
+            return full[..., 1:-1, 1:-1]
+        return full[..., 1:-1, 1:-1, 1:-1]
+
+    def _run(self, vars_, **kw):
+        ks, pads = self._slots()
+        return ops.run_program(self.kind, self._fields(vars_), ks, pads, self.scalars, path=self.path, **kw)
+
+    # -- the reference-facing call ------------------------------------------------------
+    def residual(self, vars_, boundary=False):
+        """The PDE residual; interior view (``[...,1:-1,1:-1(,1:-1)]``) unless boundary=True."""
+        staged = ops.Staged(vars_)
+        full = self._run(vars_)
+        if self.nd == 2:
+            full = full.squeeze(2)
+        return staged.back(full if boundary else self._crop(full))
+
+    __call__ = residual
+
+    # -- fused epilogues ----------------------------------------------------------------
+    def abs_scores(self, vars_, ref=None, boundary=False):
+        """|residual - ref| (the marginal nonconformity score) in one pass.  ``ref`` is a FULL
+        residual field (boundary=True form) or None."""
+        staged = ops.Staged(vars_)
+        r = None if ref is None else self._unsq(ops.to_cuda(ref))
+        full = self._run(vars_, flags=L.FLAG_ABS, ref=r)
+        if self.nd == 2:
+            full = full.squeeze(2)
+        return staged.back(full if boundary else self._crop(full))
+
+    def joint_scores(self, vars_, inv_modulation=None, ref=None, interior=True, reduce="max"):
+        """Per-sample reduce over cells of |residual - ref| * inv_modulation; only [BS] floats
+        are written.  ``inv_modulation`` / ``ref`` are FULL-size ([Nt,Nx(,Ny)] / [BS,Nt,...])."""
+        staged = ops.Staged(vars_)
+        w = None if inv_modulation is None else self._unsq(ops.to_cuda(inv_modulation))
+        r = None if ref is None else self._unsq(ops.to_cuda(ref))
+        flags = L.FLAG_ABS | (self._interior_flags() if interior else 0)
+        out = self._run(vars_, mode=L.EPI_SCORE, flags=flags, weight=w, ref=r,
+                        reduce=L.REDUCE_MAX if reduce == "max" else L.REDUCE_SUM)
+        return staged.back(out)
+
+
+# ---------------------------------------------------------------------------------------
+# factories (argument meaning = the variables of the reference scripts)
+# ---------------------------------------------------------------------------------------
+def _f(x):
+    """Python / NumPy / 0-d tensor scalar -> float (the scripts mix all three)."""
+    return float(x.item() if hasattr(x, "item") else x)
+
+
+def linear(D):
+    """res = D(u) for an additive-kernel operator (advection, wave)
+    [ref: Joint/Wave_Residuals_CP.py:173-184, Marginal/Advection_Residuals_CP.py:160-164]."""
+    return ResidualProgram(L.PROG_LINEAR, [D], [], None, 3 if D._flavour == "2d" else 2, "linear")
+
+
+def burgers(D_t, D_x, D_xx, dx, dt, nu):
+    """dx*D_t(u) + dt*u*D_x(u) - nu*D_xx(u)*(2*dt/dx)  [ref: Joint/Burgers_Residuals_CP.py:182-187]"""
+    dx, dt, nu = np.float32(_f(dx)), np.float32(_f(dt)), np.float32(_f(nu))
+    return ResidualProgram(L.PROG_BURGERS, [D_t, D_x, D_xx], [dx, dt, nu * (np.float32(2) * dt / dx)], None, 2,
+                           "burgers")
+
+
+def ns_continuity(D_x, D_y, dx, dy):
+    """D_x(u) + (dx/dy)*D_y(v)  [ref: Joint/NS_Residuals_CP.py:222-228]"""
+    return ResidualProgram(L.PROG_NS_CONTINUITY, [D_x, D_y], [_f(dx) / _f(dy)], [0, 1], 3, "ns_continuity")
+
+
+def ns_momentum(D_t, D_x, D_y, D_xx_yy, dx, dy, dt, nu):
+    """res_x + res_y  [ref: Joint/NS_Residuals_CP.py:231-240]"""
+    dx, dy, dt, nu = _f(dx), _f(dy), _f(dt), _f(nu)
+    return ResidualProgram(L.PROG_NS_MOMENTUM, [D_t, D_x, D_y, D_xx_yy], [dx * dy, dt * dy, dt * dx, nu * dt],
+                           [0, 1, 2], 3, "ns_momentum")
+
+
+_MHD = {"continuity": (L.PROG_MHD_CONTINUITY, [0, 1, 2]), "momentum": (L.PROG_MHD_MOMENTUM, [0, 1, 2, 3, 4, 5]),
+        "energy": (L.PROG_MHD_ENERGY, [0, 1, 2, 3, 4, 5]), "induction": (L.PROG_MHD_INDUCTION, [1, 2, 4, 5]),
+        "gauss": (L.PROG_MHD_GAUSS, [4, 5]), "divergence": (L.PROG_MHD_GAUSS, [4, 5])}
+
+
+def mhd(equation, D_t, D_x, D_y, gamma=5 / 3):
+    """Ideal-MHD residuals on vars = [rho,u,v,p,Bx,By]  [ref: Joint/MHD_Residuals_CP.py:225-278]"""
+    kind, idx = _MHD[equation]
+    return ResidualProgram(kind, [D_t, D_x, D_y], [_f(gamma)], idx, 3, "mhd_" + equation)
+
+
+# ---------------------------------------------------------------------------------------
+# calibration pipelines
+# ---------------------------------------------------------------------------------------
+def joint_calibration(program: ResidualProgram, cal_pred, cal_out=None, eps: float = 0.0):
+    """Joint CP calibration [ref: Joint/NS_Residuals_CP.py:289-306]:
+        modulation = std_samples(res(cal_out) - res(cal_pred)) (+ eps)
+        scores[i]  = max_cells |res(cal_out)_i - res(cal_pred)_i| / modulation
+    cal_out=None is the data-free PRE form (residual of the prediction alone).
+    Returns (modulation_full, inv_modulation_full, scores); the *_full arrays cover every cell
+    ([Nt,Nx(,Ny)]); the reference's arrays are their ``[1:-1,...]`` interior."""
+    ref = None if cal_out is None else program.residual(ops.to_cuda(cal_out), boundary=True)
+    # signed difference res_pred - res_out, stored once (full field, shell included)
+    signed = program._run(ops.to_cuda(cal_pred), ref=None if ref is None else program._unsq(ref))
+    if program.nd == 2:
+        signed = signed.squeeze(2)
+    mod, inv = ops.cell_std(signed, None, eps, want_inv=True)
+    # the max runs over the interior only: shell cells get modulation = +inf, so |d|/inf = 0
+    # never wins -- no cropped copy of the residual tensor is made
+    masked = torch.full_like(mod, float("inf"))
+    program._crop(masked).copy_(program._crop(mod))
+    scores = ops.joint_score(signed, None, masked)
+    return mod, inv, scores
+
+
+def marginal_calibration(program: ResidualProgram, cal_pred, cal_out=None, n=None, alphas=(0.1,)):
+    """Marginal CP calibration [ref: Marginal/NS_Residuals_CP.py:289-311]: per-cell quantiles of
+    |res(cal_out) - res(cal_pred)| (or |res(cal_pred)| data-free) for every alpha in one pass."""
+    from .Neural_PDE.UQ.inductive_cp import calibrate_rank
+    ref = None if cal_out is None else program.residual(ops.to_cuda(cal_out), boundary=True)
+    scores = program.abs_scores(ops.to_cuda(cal_pred), ref=ref)
+    rows = scores.shape[0]
+    ranks = [calibrate_rank(rows, rows if n is None else n, a) for a in alphas]
+    return scores, ops.select_ranks(scores, ranks)

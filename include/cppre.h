@@ -1,0 +1,244 @@
+/*
+ * cppre.h -- C ABI of libcppre.so: the B200 (sm_100a) implementation of CP-PRE's hot path.
+ *
+ * The reference (gitvicky/CP-PRE @ 5b70067a) is pure Python: it has no FFI.  Each entry point
+ * below therefore replaces a *library call site* of the reference; the citation after "replaces"
+ * is the reference file:line a maintainer would re-point at this library (the ctypes stubs are
+ * shown in INTEGRATION.md and implemented in cp_pre_b200/_lib.py).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer named d_* is a DEVICE pointer (fp32 unless
+ *    stated), every h_* a HOST pointer; strides are in ELEMENTS, int64;
+ *  - work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden synchronisation
+ *    except where a host scalar is returned, which the doc comment states;
+ *  - the library never allocates memory the caller does not own; scratch is passed in;
+ *  - every function returns 0 on success or a CPPRE_ERR_* code; cppre_last_error() gives the
+ *    thread-local message; no C++ exception crosses the ABI;
+ *  - there is no CPU fallback: without a CUDA device every compute entry point fails with
+ *    CPPRE_ERR_CUDA.
+ */
+#ifndef CPPRE_H_
+#define CPPRE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CPPRE_VERSION 100 /* 0.1.0 */
+
+#define CPPRE_MAX_FIELDS 6
+#define CPPRE_MAX_SLOTS 6
+#define CPPRE_MAX_SCALARS 12
+#define CPPRE_MAX_TAPS 512 /* non-zero taps summed over all slots of one program */
+
+enum {
+    CPPRE_OK = 0,
+    CPPRE_ERR_BAD_ARG = 1,     /* null pointer, negative size, inconsistent shapes */
+    CPPRE_ERR_UNSUPPORTED = 2, /* valid request this build has no kernel for (e.g. kernel > 7) */
+    CPPRE_ERR_CUDA = 3         /* a CUDA runtime/driver call failed; message has the string */
+};
+
+/* Residual programs: which combination of fields and derivative slots is evaluated per cell.
+ * Slots are dense coefficient tensors taken from the caller's live ConvOperator.kernel
+ * objects -- the library executes whatever tensor is there, it never
+ * rebuilds them from operator names. */
+enum {
+    /* r = K0 (x) f0.                                   replaces F.conv3d  Utils/ConvOps_2d.py:149,
+     * F.conv2d Utils/ConvOps_1d.py:150, F.conv1d Utils/ConvOps_0d.py:103, F.conv2d (valid)
+     * Utils/ConvOps_Spatial.py:135 */
+    CPPRE_PROG_LINEAR = 0,
+    /* fields {u}; slots {D_t, D_x, D_xx}; scalars {dx, dt, nu*2*dt/dx}
+     * r = s0*D_t(u) + s1*u*D_x(u) - s2*D_xx(u)          Joint/Burgers_Residuals_CP.py:182-187 */
+    CPPRE_PROG_BURGERS = 1,
+    /* fields {u,v}; slots {D_x, D_y}; scalars {dx/dy}
+     * r = D_x(u) + s0*D_y(v)                            Joint/NS_Residuals_CP.py:222-228 */
+    CPPRE_PROG_NS_CONTINUITY = 2,
+    /* fields {u,v,p}; slots {D_t, D_x, D_y, D_xx_yy}; scalars {dx*dy, dt*dy, dt*dx, nu*dt}
+     * r = res_x + res_y                                 Joint/NS_Residuals_CP.py:231-240,
+     *                                                   Other_UQ/Evaluation/PRE_estimations.py:42-52 */
+    CPPRE_PROG_NS_MOMENTUM = 3,
+    /* fields {rho,u,v,p,Bx,By}; slots {D_t, D_x, D_y}; scalars {gamma}
+     *                                                   Joint/MHD_Residuals_CP.py:225-278,
+     *                                                   Other_UQ/Evaluation/PRE_estimations.py:70-80 */
+    CPPRE_PROG_MHD_CONTINUITY = 4,
+    CPPRE_PROG_MHD_MOMENTUM = 5,
+    CPPRE_PROG_MHD_ENERGY = 6,
+    CPPRE_PROG_MHD_INDUCTION = 7,
+    CPPRE_PROG_MHD_GAUSS = 8,
+    CPPRE_PROG_COUNT = 9
+};
+
+/* One input field: a strided fp32 view of logical shape [B, N2, N1, N0].
+ * 2-D+time data [BS,Nt,Nx,Ny] maps to (B,N2,N1,N0) = (BS,Nt,Nx,Ny); 1-D+time [BS,Nt,Nx] to
+ * (BS,Nt,1,Nx); ODE data [BS,Nt] to (BS,1,1,Nt); space-only [BS,1,Nx,Ny] to (BS,1,Nx,Ny).
+ * Any strides are accepted (inputs are usually permuted views). */
+typedef struct cppre_field {
+    const float* d_data;
+    int64_t stride[4]; /* elements, order [B, N2, N1, N0] */
+} cppre_field_t;
+
+typedef struct cppre_program {
+    int32_t kind;     /* CPPRE_PROG_* */
+    int32_t n_fields; /* must match the program kind */
+    int32_t n_slots;
+    int32_t ksize[CPPRE_MAX_SLOTS][3]; /* dense kernel dims (k2,k1,k0), each in 1..7 */
+    int32_t pad[CPPRE_MAX_SLOTS][3];   /* zero padding per axis: k/2 = "same", 0 = valid */
+    const float* h_taps[CPPRE_MAX_SLOTS]; /* HOST, dense row-major [k2][k1][k0]; cross-correlation */
+    float scalars[CPPRE_MAX_SCALARS];
+} cppre_program_t;
+
+/* What happens to the residual r[b,cell] once computed -- fused into the stencil kernel so no
+ * intermediate tensor makes an HBM round trip.
+ *   v = r - ref (if d_ref);  v = |v| (if ABS);  v = v * weight[cell] (if d_weight)
+ *   STORE: out[b,cell] = v                      replaces the residual tensors + np.abs
+ *                                               Marginal/NS_Residuals_CP.py:289,327
+ *   SCORE: scores[b] = reduce_cells(v)          replaces ncf_metric_joint (max of |a-b|/mod)
+ *                                               Joint/NS_Residuals_CP.py:306 and the residual
+ *                                               tensor it consumed
+ * INTERIOR_d excludes index 0 and N_d-1 of axis d from SCORE reductions (the reference's
+ * [...,1:-1,1:-1,1:-1] crop, Joint/Wave_Residuals_CP.py:184).  */
+enum { CPPRE_EPI_STORE = 0, CPPRE_EPI_SCORE = 1 };
+enum { CPPRE_REDUCE_MAX = 0, CPPRE_REDUCE_SUM = 1 };
+enum {
+    CPPRE_FLAG_ABS = 1,
+    CPPRE_FLAG_INTERIOR_0 = 2, /* axis N0 */
+    CPPRE_FLAG_INTERIOR_1 = 4, /* axis N1 */
+    CPPRE_FLAG_INTERIOR_2 = 8  /* axis N2 */
+};
+/* Which kernel executes the program.  AUTO picks the TMA star kernel when the request
+ * qualifies (3-point star taps, 16-byte aligned rows) and the generic kernel otherwise. */
+enum { CPPRE_PATH_AUTO = 0, CPPRE_PATH_GENERIC = 1, CPPRE_PATH_TMA = 2 };
+
+typedef struct cppre_epilogue {
+    int32_t mode;   /* CPPRE_EPI_* */
+    int32_t flags;  /* CPPRE_FLAG_* */
+    int32_t reduce; /* CPPRE_REDUCE_* (SCORE only) */
+    int32_t reserved;
+    const float* d_ref;    /* optional [B, O2, O1, O0] with ref_stride, or NULL */
+    int64_t ref_stride[4];
+    const float* d_weight; /* optional contiguous [O2, O1, O0], or NULL */
+    float* d_out;          /* STORE: [B, O2, O1, O0] with out_stride */
+    int64_t out_stride[4];
+    float* d_scores;       /* SCORE: [B] contiguous, overwritten */
+} cppre_epilogue_t;
+
+/* ---- library state -------------------------------------------------------------------- */
+int cppre_version(void);
+const char* cppre_last_error(void);
+/* Number of kernels this library has launched in the calling process (all threads). */
+uint64_t cppre_launch_count(void);
+/* Name of the kernel path the last cppre_residual call on this thread used: "tma" | "generic". */
+const char* cppre_last_path(void);
+
+/* ---- K1: fused residual program ------------------------------------------------------- */
+/* Output extent per axis: O_d = N_d + 2*pad_d - k_d + 1 (must agree across slots). */
+int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
+                   const cppre_field_t* fields, const cppre_epilogue_t* epi,
+                   int path, void* stream);
+/* Returns 1 if (prog, shape, fields, epi) qualifies for the TMA star kernel, else 0. */
+int cppre_residual_tma_eligible(const cppre_program_t* prog, const int64_t shape[4],
+                                const cppre_field_t* fields, const cppre_epilogue_t* epi);
+
+/* ---- K2: per-cell statistics over the sample axis ------------------------------------- */
+/* mean[c], m2[c] (sum of squared deviations) of x[i,c] = a[i,c] - b[i,c] over i < n.
+ * a, b: fp32 [n, cells] with row strides; b may be NULL.  Accumulated in fp64.
+ * replaces modulation_func = np.std(a-b, axis=0)   Tests/test_advection_inv_sampling_marginal.py:428,
+ * Joint/NS_Residuals_CP.py:305 */
+int cppre_cell_moments(const float* d_a, int64_t a_row_stride, const float* d_b,
+                       int64_t b_row_stride, int64_t n, int64_t cells, double* d_mean,
+                       double* d_m2, void* stream);
+/* std[c] = sqrt(m2[c]/count) + add_eps (fp32); inv[c] = 1/std[c] if d_inv != NULL. */
+int cppre_cell_std(const double* d_m2, double count, float add_eps, int64_t cells,
+                   float* d_std, float* d_inv, void* stream);
+/* scores[i] = max_c |a[i,c]-b[i,c]| / mod[c]  (IEEE division, NaN-propagating max)
+ * replaces ncf_metric_joint on stored residuals   Joint/NS_Residuals_CP.py:306 */
+int cppre_joint_score(const float* d_a, int64_t a_row_stride, const float* d_b,
+                      int64_t b_row_stride, const float* d_mod, int64_t n, int64_t cells,
+                      float* d_scores, void* stream);
+
+/* ---- K3: order statistics along the sample axis --------------------------------------- */
+/* out[r, c] = the h_ranks[r]-th smallest (0-based) of scores[0..n-1, c]; NaN if the column
+ * holds a NaN (np.quantile behaviour).  scores fp32 [n, cells] with row stride.
+ * replaces np.quantile(..., axis=0, method='higher') inside calibrate()
+ *          (Neural_PDE/UQ/inductive_cp.py, un-vendored; call sites Marginal/NS_Residuals_CP.py:311)
+ * d_work: scratch of cppre_select_workspace_bytes(n, cells) bytes (may be NULL if that is 0). */
+size_t cppre_select_workspace_bytes(int64_t n, int64_t cells);
+int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                       const int32_t* h_ranks, int32_t n_ranks, float* d_out, void* d_work,
+                       void* stream);
+/* One 8-bit radix pass over a flat score array, for a quantile that spans several GPUs:
+ * hist[d] += #{ i : (key(x_i) & mask) == prefix and ((key(x_i) >> shift) & 255) == d },
+ * key = order-preserving uint32 image of the float.  d_hist: 256 x uint32, NOT cleared here.
+ * The caller all-reduces d_hist over ranks (NCCL) between passes. */
+int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,
+                     uint32_t* d_hist, void* stream);
+
+/* ---- K5: coverage --------------------------------------------------------------------- */
+/* inside[i] = #{ c : lo[i,c] <= y[i,c] <= hi[i,c] }, uint32 per sample, overwritten.
+ * lo / hi: row stride 0 broadcasts one [cells] row over all samples.
+ * replaces emp_cov / emp_cov_joint / filter_sims_joint / filter_sims_within_bounds
+ *          (Marginal/NS_Residuals_CP.py:312, Joint/Advection_Residuals_CP.py:327-329,
+ *           Active_Learning/Advection_AL_Marginal.py:169-197) */
+int cppre_inside_count(const float* d_y, int64_t y_row_stride, const float* d_lo,
+                       int64_t lo_row_stride, const float* d_hi, int64_t hi_row_stride, int64_t n,
+                       int64_t cells, uint32_t* d_inside, void* stream);
+/* Same with the prediction set never materialised: lo = c - q*h, hi = c + q*h evaluated in fp32
+ * exactly as NumPy would (separately rounded multiply, subtract, add); c = centre[i,c] or 0 when
+ * d_centre == NULL; h = half[c] or 1 when d_half == NULL.
+ * replaces [pred -/+ qhat*modulation] + emp_cov_joint   Joint/NS_Residuals_CP.py:312,336 */
+int cppre_inside_count_band(const float* d_y, int64_t y_row_stride, const float* d_centre,
+                            int64_t centre_row_stride, const float* d_half, float q, int64_t n,
+                            int64_t cells, uint32_t* d_inside, void* stream);
+
+/* ---- boundary conditions -------------------------------------------------------------- */
+/* Per-side boundary codes, order {left, right, top, bottom}; left/right act on the last axis. */
+enum {
+    CPPRE_BC_DIRICHLET = 0,
+    CPPRE_BC_NEUMANN = 1, /* also 'outflow' */
+    CPPRE_BC_PERIODIC = 2,
+    CPPRE_BC_SYMMETRIC = 3,
+    CPPRE_BC_NONE = 4 /* 'free_slip': the reference pads nothing */
+};
+typedef struct cppre_bc {
+    int32_t type[4];  /* CPPRE_BC_* for left, right, top, bottom */
+    int32_t width[4]; /* ghost widths: kw/2, kw/2, kh/2, kh/2 */
+    float value[4];   /* Dirichlet values */
+} cppre_bc_t;
+/* Padded extents produced by the reference's sequential left,right,top,bottom padding. */
+int cppre_bc_padded_shape(const cppre_bc_t* bc, int64_t h, int64_t w, int64_t* hp, int64_t* wp);
+/* Host-side view of the same index map the kernels use: h_rows[r] / h_cols[c] = source row /
+ * column of padded row r / column c, or -1 where the cell is a Dirichlet constant whose value
+ * is then in h_row_vals[r] / h_col_vals[c] (a row constant wins over a column constant: rows
+ * are padded last).  Arrays of hp and wp entries (cppre_bc_padded_shape).  No GPU needed. */
+int cppre_bc_index_map(const cppre_bc_t* bc, int64_t h, int64_t w, int32_t* h_rows, float* h_row_vals,
+                       int32_t* h_cols, float* h_col_vals);
+/* out[img, :, :] = pad(in[img, :, :]) for img < n_img; in [n_img,H,W], out [n_img,Hp,Wp], both
+ * contiguous.   replaces BoundaryManager.pad_signal   Utils/boundary_conditions.py:80-182 */
+int cppre_bc_pad(const float* d_in, int64_t n_img, int64_t h, int64_t w, const cppre_bc_t* bc,
+                 float* d_out, void* stream);
+/* Valid cross-correlation of the (virtual) padded image with a kh x kw kernel; no padded copy
+ * is made.  out [n_img, Hp-kh+1, Wp-kw+1] contiguous.
+ * replaces pad_signal + F.conv2d   Utils/boundary_conditions.py:184-211,
+ *          Utils/VectorConvOps_Spatial.py:41-55 */
+int cppre_bc_conv2d(const float* d_in, int64_t n_img, int64_t h, int64_t w, const cppre_bc_t* bc,
+                    const float* h_taps, int32_t kh, int32_t kw, float* d_out, void* stream);
+
+/* ---- spectral path -------------------------------------------------------------------- */
+enum {
+    CPPRE_SPEC_CONJ_FIRST = 1, /* K <- conj(K) before anything else (correlation) */
+    CPPRE_SPEC_INVERSE = 2,    /* K <- 1/(K + eps) */
+    CPPRE_SPEC_CONJ_LAST = 4   /* K <- conj(K) after the inverse */
+};
+/* out[b, m] = sig[b, m] * g(ker[m]) on interleaved complex64; g per `flags`.
+ * replaces the pointwise spectrum arithmetic of fft_conv / differentiate / integrate
+ *          Utils/fft_conv_pytorch/fft_conv.py:110-115, Utils/ConvOps_2d.py:207-210,263-268 */
+int cppre_spectral_pointwise(const float* d_sig, const float* d_ker, int64_t batch, int64_t m,
+                             int32_t flags, float eps, float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CPPRE_H_ */

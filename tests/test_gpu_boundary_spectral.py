@@ -1,0 +1,137 @@
+"""GPU parity of boundary padding (bit-exact), BC-fused vector operators, and the spectral path."""
+import numpy as np
+import pytest
+import torch
+
+import cp_pre_b200
+from conftest import assert_close_rel, load_golden
+
+cp_pre_b200.install()
+pytestmark = pytest.mark.gpu
+
+
+def cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def test_pad_signal_bit_exact_against_reference_golden():
+    from boundary_conditions import BoundaryManager
+    g = load_golden("bc")
+    x4, x2 = g["x4"], g["x2"]
+    types = [str(t) for t in g["types"]]
+    for ks in (3, 5, (3, 5)):
+        for ty in types:
+            b = BoundaryManager(ks)
+            b.set_all_boundaries(ty, 1.25)
+            got = b.pad_signal(torch.from_numpy(x4))
+            assert got.device.type == "cpu"
+            np.testing.assert_array_equal(got.numpy(), g[f"all|{ks}|{ty}|x4"], err_msg=f"{ks} {ty}")
+            np.testing.assert_array_equal(b.pad_signal(cuda(x2)).cpu().numpy(), g[f"all|{ks}|{ty}|x2"])
+    for a in types:
+        for c in types:
+            b = BoundaryManager(5)
+            b.set_boundary_type("left", a, 0.5)
+            b.set_boundary_type("right", c, -0.5)
+            b.set_boundary_type("top", c, 2.0)
+            b.set_boundary_type("bottom", a, -2.0)
+            np.testing.assert_array_equal(b.pad_signal(cuda(x4)).cpu().numpy(), g[f"mix|{a}|{c}"], err_msg=f"{a}|{c}")
+    b = BoundaryManager(3)
+    b.set_all_boundaries("symmetric")
+    k = torch.from_numpy(g["conv|k"])
+    assert_close_rel(b.apply_convolution(cuda(x2), k).cpu().numpy(), g["conv|sym|x2"], 1e-5)
+    assert_close_rel(BoundaryManager(3).apply_convolution(torch.from_numpy(x2), k).numpy(), g["conv|per|x2"], 1e-5)
+
+
+def test_vector_operators_spatial_and_2d():
+    import VectorConvOps_Spatial as VS
+    import Utils.VectorConvOps as V2
+    g = load_golden("vector")
+    a, b = cuda(g["a"]), cuda(g["b"])
+    for bc in ("periodic", "neumann", "symmetric", "dirichlet", "free_slip"):
+        assert_close_rel(VS.Divergence(scale=1.7, boundary_cond=bc, device="cpu")(a, b).cpu().numpy(), g[f"div|{bc}"], 1e-5, bc)
+        assert_close_rel(VS.Curl(scale=1.7, boundary_cond=bc, device="cpu")(a, b).cpu().numpy(), g[f"curl|{bc}"], 1e-5, bc)
+        assert_close_rel(VS.Laplace(scale=0.3, boundary_cond=bc, device="cpu")(a).cpu().numpy(), g[f"lap_s|{bc}"], 1e-5, bc)
+        assert_close_rel(VS.Laplace(scale=0.3, boundary_cond=bc, scalar=False, device="cpu")(a, b).cpu().numpy(),
+                         g[f"lap_v|{bc}"], 1e-5, bc)
+    assert_close_rel(VS.Laplace(taylor_order=4, device="cpu")(a).cpu().numpy(), g["lap_s5|periodic"], 1e-5)
+    # Gradient / Vector_Gradient build cuda children (scale honoured on a GPU box); scale=1 golden
+    assert_close_rel(VS.Gradient()(a).cpu().numpy(), g["grad|periodic"], 1e-5)
+    assert_close_rel(VS.Gradient(boundary_cond="neumann")(a, b).cpu().numpy(), g["grad2|neumann"], 1e-5)
+    assert_close_rel(VS.Vector_Gradient()(a, b).cpu().numpy(), g["vgrad|periodic"], 1e-5)
+    gr = VS.Gradient(scale=3.0)
+    assert gr.grad_x.kernel.is_cuda and float(gr.grad_x.kernel.abs().max()) == 1.5
+    v = torch.cat([a, b], 1)
+    w = cuda(g["w"])
+    assert_close_rel(VS.dot(v, w).cpu().numpy(), g["dot"])
+    assert_close_rel(VS.cross(v, w).cpu().numpy(), g["cross"])
+    np.testing.assert_array_equal(VS.vectorize(a, b).cpu().numpy(), g["vectorize"])
+    # 2-D+time family (children built by keyword; the shipped constructors raise)
+    p, q = cuda(g["v2|p"]), cuda(g["v2|q"])
+    div, grad, curl, lap = V2.Divergence(scale=1.3), V2.Gradient(scale=1.3), V2.Curl(scale=1.3), V2.Laplace(scale=0.8)
+    np.testing.assert_array_equal(div.grad_x.kernel.numpy(), g["v2|gx"])
+    np.testing.assert_array_equal(div.grad_y.kernel.numpy(), g["v2|gy"])
+    assert_close_rel(div(p, q).cpu().numpy(), g["v2|div"], 1e-5, "div")
+    assert_close_rel(grad(p, q).cpu().numpy(), g["v2|grad"], 1e-5, "grad")
+    assert_close_rel(curl(p, q).cpu().numpy(), g["v2|curl"], 1e-5, "curl")
+    assert_close_rel(lap(p, q).cpu().numpy(), g["v2|lap"], 1e-5, "lap")
+    assert_close_rel(V2.dot((p, q), (q, p)).cpu().numpy(), g["v2|dot"])
+
+
+def _op(mod, kernel, *a):
+    D = mod.ConvOperator(*a)
+    D.kernel = torch.from_numpy(kernel)
+    return D
+
+
+def test_spectral_paths_against_reference_golden():
+    import ConvOps_0d as C0
+    import ConvOps_1d as C1
+    import ConvOps_Spatial as CS
+    import Utils.ConvOps_2d as C2
+    from fft_conv_pytorch.fft_conv import fft_conv
+    g = load_golden("spectral")
+    tol, WC, ILL = 2e-5, 1e-4, 0.5
+    for pre, mod, args in (("2d", C2, ("t", 1)), ("1d", C1, ("t", 1)), ("0d", C0, (1,))):
+        u = cuda(g[f"{pre}|u"])
+        D = _op(mod, g[f"{pre}|k"], *args)
+        assert_close_rel(D.spectral_convolution(u).cpu().numpy(), g[f"{pre}|spec"], tol, f"{pre} spec")
+        for corr in (0, 1):
+            for sl in (0, 1):
+                assert_close_rel(D.differentiate(u, correlation=bool(corr), slice_pad=bool(sl)).cpu().numpy(),
+                                 g[f"{pre}|diff|{corr}{sl}"], tol, f"{pre} diff {corr}{sl}")
+                got = D.integrate(u, correlation=bool(corr), slice_pad=bool(sl)).cpu().numpy()
+                assert_close_rel(got, g[f"{pre}|int|{corr}{sl}"], ILL, f"{pre} int {corr}{sl} (ill-conditioned)")
+    u = cuda(g["2d|u"])
+    D = _op(C2, g["2d|k"], "t", 1)
+    assert_close_rel(D.spectral_convolution(u, inverse=True).cpu().numpy(), g["2d|spec_inv"], ILL)
+    Ds = C2.ConvOperator("t", 1, conv="spectral")
+    assert_close_rel(Ds(u).cpu().numpy(), g["2d|call_spec"], tol, "conv='spectral' call")
+    assert_close_rel(fft_conv(u.unsqueeze(1), D.kernel[None, None].cuda(), padding=(1, 1, 1), force_fft=True)[:, 0]
+                     .cpu().numpy(), g["2d|spec"], tol, "true-FFT forward path")
+    # well-conditioned inverse cases pin the spectral arithmetic (conj / reciprocal / product kernel)
+    W = _op(C2, g["2d|wc|k"], "t", 1)
+    assert_close_rel(W.spectral_convolution(u, inverse=True).cpu().numpy(), g["2d|wc|spec_inv"], WC)
+    assert_close_rel(W.integrate(u).cpu().numpy(), g["2d|wc|int|00"], WC)
+    assert_close_rel(W.integrate(u, correlation=True, slice_pad=True).cpu().numpy(), g["2d|wc|int|11"], WC)
+    rt = W.integrate(W.differentiate(u, slice_pad=False), slice_pad=False)
+    assert_close_rel(rt.cpu().numpy(), g["2d|wc|roundtrip"], WC, "R4 round trip")
+    u1 = cuda(g["1d|u"])
+    A = _op(C1, g["1d|wc|k"], "t", 1)
+    assert_close_rel(A.integrate(u1).cpu().numpy(), g["1d|wc|int|01"], WC)
+    assert_close_rel(A.integrate(u1, correlation=True, slice_pad=False).cpu().numpy(), g["1d|wc|int|10"], WC)
+    u0 = cuda(g["0d|u"])
+    B = _op(C0, g["0d|wc|k"], 1)
+    assert_close_rel(B.integrate(u0).cpu().numpy(), g["0d|wc|int|01"], WC)
+    assert_close_rel(B.integrate(u0, correlation=True, slice_pad=False).cpu().numpy(), g["0d|wc|int|10"], WC)
+    us = cuda(g["sp|u"])
+    S = _op(CS, g["sp|k"], "x", 1, 1.0, 2, "direct", "cpu")
+    assert_close_rel(S.spectral_convolution(us).cpu().numpy(), g["sp|spec"], tol)
+    assert_close_rel(S.differentiate(us, correlation=True, slice_pad=True).cpu().numpy(), g["sp|diff|11"], tol)
+    Sc = _op(CS, g["sp|wc|k"], "x", 1, 1.0, 2, "direct", "cpu")
+    assert_close_rel(Sc.spectral_convolution(us, inverse=True).cpu().numpy(), g["sp|wc|spec_inv"], WC)
+    assert_close_rel(Sc.integrate(us).cpu().numpy(), g["sp|wc|int|00"], WC)
+    assert_close_rel(Sc.integrate(us, correlation=True, slice_pad=True).cpu().numpy(), g["sp|wc|int|11"], WC)
+    # fft_conv proper: multi-channel broadcast, bias, stride, even kernel with float 'same' padding
+    sig, ker, bias = (torch.from_numpy(g[k]) for k in ("fc|sig", "fc|ker", "fc|bias"))
+    assert_close_rel(fft_conv(sig, ker, bias=bias, padding="same").numpy(), g["fc|same"], tol)
+    assert_close_rel(fft_conv(sig, ker, padding=2, stride=2).numpy(), g["fc|stride"], tol)

@@ -1,0 +1,189 @@
+"""GPU parity of the conformal half: K2 cell statistics, K3 order statistics, K5 coverage.
+Bit-exact where the contract says so (quantile values given identical scores, coverage counts,
+accept masks); fp32 tolerance for std / joint scores."""
+import numpy as np
+import pytest
+import torch
+
+import cp_pre_b200
+from conftest import assert_close_rel, load_golden
+from cp_pre_b200 import ops, programs
+from oracle import cpu_oracle as O
+from oracle import synth
+
+cp_pre_b200.install()
+pytestmark = pytest.mark.gpu
+
+from Neural_PDE.UQ.inductive_cp import (calibrate, calibrate_many, emp_cov, emp_cov_joint,  # noqa: E402
+                                        filter_sims_joint, filter_sims_within_bounds, modulation_func,
+                                        ncf_metric_joint)
+
+ALPHAS = np.arange(0.05, 0.95 + 0.1, 0.1)
+
+
+def cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def test_helpers_against_reference_inline_twins_golden():
+    g = load_golden("cp")
+    cal, val = g["cal"], g["val"]
+    mod = modulation_func(cal, np.zeros(cal.shape))
+    assert isinstance(mod, np.ndarray) and mod.shape == cal.shape[1:]
+    assert_close_rel(mod, g["modulation"], 1e-6, "modulation")
+    assert_close_rel(modulation_func(np.zeros(cal.shape, np.float32) + 0, cal), g["modulation"], 1e-6)  # symmetric
+    sc = ncf_metric_joint(cal, np.zeros(cal.shape), g["modulation"])
+    assert_close_rel(sc, g["joint_scores"], 1e-6, "joint scores")
+    for q in (1.5, 2.5, 3.5):
+        sets = [-q * g["modulation"], q * g["modulation"]]
+        np.testing.assert_array_equal(filter_sims_joint(sets, val), g[f"joint_mask|{q}"])
+        assert emp_cov_joint(sets, val) == float(g[f"joint_cov|{q}"])
+    for within in (False, True):
+        np.testing.assert_array_equal(
+            filter_sims_within_bounds(-g["modulation"], g["modulation"], val, 0.5, within),
+            g[f"filter_bounds|{int(within)}"])
+
+
+@pytest.mark.parametrize("n,cells", [(20, (7,)), (100, (5, 33)), (256, (3, 10, 20)), (500, (40,)), (1000, (9,)),
+                                     (1, (4,)), (1500, (70,))])
+def test_calibrate_is_bit_exact_per_cell(n, cells):
+    rng = np.random.default_rng(n)
+    s = np.abs(rng.standard_normal((n,) + cells)).astype(np.float32)
+    s[rng.integers(0, n, 5), ..., 0] = 0.25            # ties
+    for alpha in ALPHAS:
+        try:
+            want = O.calibrate(s, n, alpha)
+        except ValueError:
+            with pytest.raises(ValueError, match="Quantiles must be in the range"):
+                calibrate(s, n, alpha)
+            continue
+        got = calibrate(s, n, alpha)
+        assert got.dtype == np.float32 and got.shape == want.shape
+        np.testing.assert_array_equal(got, want, err_msg=f"n={n} alpha={alpha}")
+    ok = [a for a in ALPHAS if 0 <= O.calibrate_quantile_level(n, a) <= 1]
+    if ok:
+        many = calibrate_many(cuda(s), n, ok)
+        for i, a in enumerate(ok):
+            np.testing.assert_array_equal(many[i].cpu().numpy(), O.calibrate(s, n, a))
+
+
+def test_calibrate_scalar_joint_form_negative_values_and_nan():
+    rng = np.random.default_rng(0)
+    for n in (19, 512, 4096, 5000):
+        s = rng.standard_normal(n).astype(np.float32) * 3         # negatives exercise the key order
+        for alpha in (0.05, 0.5, 0.9):
+            got = calibrate(s, n, alpha)
+            assert np.ndim(got) == 0 and got == O.calibrate(s, n, alpha)
+        t = calibrate(cuda(s), n, 0.1)
+        assert t.is_cuda and t.dim() == 0 and float(t) == float(O.calibrate(s, n, 0.1))
+    s = np.abs(rng.standard_normal((64, 6))).astype(np.float32)
+    s[10, 2] = np.nan
+    s[11, 4] = np.inf
+    got, want = calibrate(s, 64, 0.1), O.calibrate(s, 64, 0.1)
+    assert np.isnan(got[2]) and np.isnan(want[2])
+    np.testing.assert_array_equal(np.delete(got, 2), np.delete(want, 2))
+    # n argument different from the number of rows (scripts pass len(other_array))
+    assert calibrate(s[:, 0], 80, 0.3) == O.calibrate(s[:, 0], 80, 0.3)
+
+
+def test_modulation_and_joint_scores_against_oracle():
+    rng = np.random.default_rng(4)
+    a = (0.1 * rng.standard_normal((300, 12, 34))).astype(np.float32) + np.float32(5.0)   # mean >> std
+    b = (0.1 * rng.standard_normal((300, 12, 34))).astype(np.float32)
+    mod = modulation_func(a, b)
+    assert_close_rel(mod, O.modulation_func(a, b), 2e-6, "std with large mean")
+    sc = ncf_metric_joint(a, b, mod)
+    assert_close_rel(sc, O.ncf_metric_joint(a, b, mod), 1e-6, "joint score")
+    ta, tb = cuda(a), cuda(b)
+    m2 = modulation_func(ta, tb)
+    assert m2.is_cuda and torch.equal(m2.cpu(), torch.from_numpy(mod))
+    # strided (interior-crop) views are accepted
+    v = ta[:, 1:-1, 1:-1]
+    assert_close_rel(modulation_func(v, tb[:, 1:-1, 1:-1]).cpu().numpy(), O.modulation_func(a, b)[1:-1, 1:-1], 2e-6)
+
+
+def test_coverage_counts_are_exact():
+    rng = np.random.default_rng(5)
+    y = rng.standard_normal((200, 9, 31)).astype(np.float32)
+    pred = (y + 0.3 * rng.standard_normal(y.shape)).astype(np.float32)
+    q_cell = np.abs(rng.standard_normal(y.shape[1:])).astype(np.float32)
+    for sets in ([pred - q_cell, pred + q_cell], [-q_cell, q_cell], [np.float32(-0.7), np.float32(0.7)],
+                 [pred - np.float32(0.4), pred + np.float32(0.4)]):
+        assert emp_cov(sets, y) == O.emp_cov(sets, y)
+        assert emp_cov_joint(sets, y) == O.emp_cov_joint(sets, y)
+        np.testing.assert_array_equal(filter_sims_joint(sets, y), O.filter_sims_joint(sets, y))
+    big = [-10 * np.ones_like(q_cell), 10 * np.ones_like(q_cell)]
+    assert emp_cov_joint(big, y) == 1.0 and emp_cov(big, y) == 1.0
+    # values exactly on the bounds are inside (>=, <=)
+    assert emp_cov([y, y], y) == 1.0
+    # fused band form: [c - q*h, c + q*h] never materialised, same fp32 roundings as NumPy
+    h = np.abs(rng.standard_normal(y.shape[1:])).astype(np.float32)
+    q = np.float32(1.37)
+    cnt = ops.inside_count_band(cuda(y), cuda(pred), cuda(h), float(q)).cpu().numpy()
+    want = ((y >= pred - q * h) & (y <= pred + q * h)).sum(axis=(1, 2))
+    np.testing.assert_array_equal(cnt, want)
+    cnt = ops.inside_count_band(cuda(y), None, cuda(h), float(q)).cpu().numpy()
+    np.testing.assert_array_equal(cnt, ((y >= -q * h) & (y <= q * h)).sum(axis=(1, 2)))
+    for thr in (0.3, 0.8):
+        for within in (False, True):
+            np.testing.assert_array_equal(filter_sims_within_bounds(-h, h, y, thr, within),
+                                          O.filter_sims_within_bounds(-h, h, y, thr, within))
+
+
+def test_radix_histogram_passes_reproduce_the_joint_quantile():
+    """The multi-GPU Joint path: 4 x 8-bit histogram passes (all-reduced between passes when the
+    scores are sharded) find the same order statistic as a sort."""
+    rng = np.random.default_rng(6)
+    x = (rng.standard_normal(10000) * 4).astype(np.float32)
+    keys = O.float_order_key(x)
+    xc = cuda(x)
+    for k in (0, 17, 5000, 9999):
+        prefix = mask = 0
+        kk = k
+        for shift in (24, 16, 8, 0):
+            hist = torch.zeros(256, dtype=torch.int32, device="cuda")
+            ops.radix_hist(xc, prefix, mask, shift, hist)
+            h = hist.cpu().numpy().astype(np.int64)
+            sel = (keys & np.uint32(mask)) == np.uint32(prefix)
+            np.testing.assert_array_equal(h, np.bincount((keys[sel] >> np.uint32(shift)) & np.uint32(255), minlength=256))
+            c = np.cumsum(h)
+            d = int(np.searchsorted(c, kk, side="right"))
+            kk -= int(c[d - 1]) if d else 0
+            prefix |= d << shift
+            mask |= 255 << shift
+        assert prefix == int(np.sort(keys)[k])
+
+
+def test_joint_and_marginal_pipelines_end_to_end():
+    """residual -> modulation -> scores -> qhat -> coverage, reference formulas on the oracle side
+    (Joint/NS_Residuals_CP.py:289-337, Marginal/NS_Residuals_CP.py:289-337)."""
+    import Utils.ConvOps_2d as C2
+    n = synth.NS
+    ko = O.ops_2d()
+    D = dict(D_t=C2.ConvOperator("t", 1), D_x=C2.ConvOperator("x", 1), D_y=C2.ConvOperator("y", 1),
+             D_xx_yy=C2.ConvOperator(("x", "y"), 2))
+    prog = programs.ns_momentum(D["D_t"], D["D_x"], D["D_y"], D["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    shape = (48, 8, 16, 128)
+    pred = synth.fields(41, 3, shape)
+    out = (pred + 0.02 * synth.normal_fields(42, 3, shape)).astype(np.float32)
+    R = lambda v: O.residual_ns_momentum(v[:, 0], v[:, 1], v[:, 2], n["dx"], n["dy"], n["dt"], n["nu"], ko)
+    inner = (slice(None), slice(1, -1), slice(1, -1), slice(1, -1))
+    r_pred, r_out = R(pred)[inner], R(out)[inner]
+    mod_o = O.modulation_func(r_out, r_pred)
+    sc_o = O.ncf_metric_joint(r_out, r_pred, mod_o)
+    mod, inv, sc = programs.joint_calibration(prog, cuda(pred), cuda(out))
+    assert_close_rel(mod[1:-1, 1:-1, 1:-1].cpu().numpy(), mod_o, 2e-5, "pipeline modulation")
+    assert_close_rel(sc.cpu().numpy(), sc_o, 5e-5, "pipeline joint scores")
+    # identical score arrays -> identical qhat (bit exact), then coverage with the fused band kernel
+    for alpha in (0.1, 0.5):
+        qhat = calibrate(sc_o, len(sc_o), alpha)
+        assert qhat == O.calibrate(sc_o, len(sc_o), alpha)
+        sets = [r_pred - qhat * mod_o, r_pred + qhat * mod_o]
+        assert emp_cov_joint(sets, r_out) == O.emp_cov_joint(sets, r_out)
+    # marginal, data-free form: |res(pred)| per-cell quantiles for the whole alpha grid in one pass
+    scores, qh = programs.marginal_calibration(prog, cuda(pred), None, alphas=(0.1, 0.3, 0.5))
+    s_o = np.abs(r_pred)
+    assert_close_rel(scores.cpu().numpy(), s_o, 1e-5, "marginal scores")
+    mine = scores.cpu().numpy()
+    for i, a in enumerate((0.1, 0.3, 0.5)):
+        np.testing.assert_array_equal(qh[i].cpu().numpy(), O.calibrate(mine, len(mine), a))

@@ -1,0 +1,282 @@
+"""GPU parity of K1 (the fused residual/stencil kernels) against the CPU oracle and the golden
+vectors produced by the unmodified reference.  Every call goes through the C ABI
+(cp_pre_b200.ops -> ctypes -> libcppre.so).  Tolerance:
+max|new-ref| <= 1e-5 * max|ref| for residual fields; exact for nothing here (fp32 sums)."""
+import numpy as np
+import pytest
+import torch
+
+import cp_pre_b200
+from conftest import assert_close_rel, load_golden
+from cp_pre_b200 import _lib as L
+from cp_pre_b200 import ops, programs
+from oracle import cpu_oracle as O
+from oracle import synth
+
+cp_pre_b200.install()
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+def cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _mods():
+    import ConvOps_0d
+    import ConvOps_1d
+    import ConvOps_Spatial
+    import Utils.ConvOps_2d as ConvOps_2d
+    return {"2d": ConvOps_2d, "1d": ConvOps_1d, "0d": ConvOps_0d, "sp": ConvOps_Spatial}
+
+
+@pytest.mark.parametrize("prefix,names", [
+    ("2d", ["Dt", "Dx", "Dy", "Dtt", "Dxx", "I", "L3", "L5", "L7", "wave", "dense", "aniso"]),
+    ("1d", ["Dt", "Dx", "Dxx", "I", "L3", "L5", "adv"]),
+    ("0d", ["0_2", "1_2", "1_4", "2_2", "2_4", "2_6"]),
+    ("sp", ["Dx", "L3", "L5"]),
+])
+def test_operator_call_matches_reference_golden(prefix, names):
+    g = load_golden("conv")
+    m = _mods()[prefix]
+    u = g[f"{prefix}|u"]
+    for nm in names:
+        D = m.ConvOperator(1) if prefix == "0d" else m.ConvOperator("x", 1, device="cpu")
+        D.kernel = torch.from_numpy(g[f"{prefix}|{nm}|k"])
+        want = g[f"{prefix}|{nm}|y"]
+        # host tensors in, host tensor out (the reference's default workflow) ...
+        got = D(torch.from_numpy(u))
+        assert got.device.type == "cpu" and got.dtype == torch.float32
+        assert_close_rel(got.numpy(), want, TOL, f"{prefix}|{nm} (host)")
+        # ... and device tensors in, device tensor out
+        got = D(cuda(u))
+        assert got.is_cuda
+        assert_close_rel(got.cpu().numpy(), want, TOL, f"{prefix}|{nm} (device)")
+        # convolution(field, kernel) overwrites .kernel permanently, like the reference
+        E = m.ConvOperator(1) if prefix == "0d" else m.ConvOperator("x", 1, device="cpu")
+        E.convolution(cuda(u), D.kernel)
+        assert E.kernel is D.kernel
+
+
+def test_permuted_view_is_processed_in_place_and_matches_reference():
+    g = load_golden("conv")
+    m = _mods()["2d"]
+    W = m.ConvOperator()
+    W.kernel = torch.from_numpy(g["2d|wave|k"])
+    up = cuda(g["2d|perm|u"]).permute(0, 3, 1, 2)          # [BS,Nt,Nx,Ny] view, t innermost
+    got = W(up)
+    assert got.shape == up.shape
+    assert_close_rel(got.cpu().numpy(), g["2d|perm|y"], TOL, "perm")
+
+
+def _programs_2d():
+    m = _mods()["2d"]
+    C = m.ConvOperator
+    return dict(D_t=C("t", 1), D_x=C("x", 1), D_y=C("y", 1), D_xx_yy=C(("x", "y"), 2))
+
+
+def test_residual_programs_match_reference_golden():
+    g = load_golden("residuals")
+    m1 = _mods()["1d"]
+    c = synth.BURGERS
+    pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                          torch.tensor(c["dx"]), torch.tensor(c["dt"]), torch.tensor(c["nu"]))
+    assert_close_rel(pb.residual(cuda(g["burgers|u"]), boundary=True).cpu().numpy(), g["burgers|res"], TOL, "burgers")
+    o = _programs_2d()
+    n = synth.NS
+    v = cuda(g["ns|vars"])
+    pc = programs.ns_continuity(o["D_x"], o["D_y"], np.asarray(n["dx"]), np.asarray(n["dy"]))
+    assert_close_rel(pc.residual(v, True).cpu().numpy(), g["ns|cont"], TOL, "ns cont")
+    pm = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    assert_close_rel(pm.residual(v, True).cpu().numpy(), g["ns|mom"], TOL, "ns mom")
+    # interior crop is a view of the full field, like the reference's [...,1:-1,1:-1,1:-1]
+    assert_close_rel(pm.residual(v).cpu().numpy(), g["ns|mom"][..., 1:-1, 1:-1, 1:-1], TOL)
+    w = cuda(g["mhd|vars"])
+    for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+        p = programs.mhd(eq, o["D_t"], o["D_x"], o["D_y"])
+        assert_close_rel(p.residual(w, True).cpu().numpy(), g[f"mhd|{eq}"], TOL, eq)
+    # class forms (Other_UQ/Evaluation/PRE_estimations.py)
+    from Other_UQ.Evaluation.PRE_estimations import PRE_MHD, PRE_NS, PRE_Wave
+    pw = PRE_Wave(dt=0.5, dx=1.0, c=1.0)
+    np.testing.assert_array_equal(pw.D.kernel.numpy(), g["wave|k"])
+    assert_close_rel(pw.residual(cuda(g["wave|u"]), boundary=True).cpu().numpy(), g["wave|res_full"], TOL)
+    assert_close_rel(pw.residual(torch.from_numpy(g["wave|u"])).numpy(), g["wave|res"], TOL)
+    assert_close_rel(PRE_NS(n["dt"], n["dx"], n["dy"]).residual(v, boundary=True).cpu().numpy(), g["ns|mom_class"], TOL)
+    assert_close_rel(PRE_MHD(0.01, 1 / 128, 1 / 128).residual(w, boundary=True).cpu().numpy(),
+                     g["mhd|energy_class"], TOL)
+
+
+SHAPES_3D = [(3, 7, 19, 132), (2, 5, 16, 256), (1, 3, 9, 4), (2, 4, 40, 128)]
+
+
+@pytest.mark.parametrize("shape", SHAPES_3D)
+@pytest.mark.parametrize("path", [L.PATH_GENERIC, L.PATH_TMA])
+def test_all_programs_against_oracle_on_both_kernel_paths(shape, path):
+    """Seeded smooth + N(0,1) fields; the TMA star kernel and the generic kernel must both match
+    the oracle, including tiles that straddle the column (128) and row (8/16) tile edges."""
+    o = _programs_2d()
+    ko = O.ops_2d()
+    n = synth.NS
+    for gen in ("smooth", "normal"):
+        v = (synth.fields(5, 6, shape, positive=(0, 3)) if gen == "smooth" else
+             np.abs(synth.normal_fields(6, 6, shape)) + np.float32(0.5))
+        vc = cuda(v)
+        f = [v[:, j] for j in range(6)]
+        progs = {
+            "wave": (programs.linear(_wave_op()), lambda: O.correlate(f[0], _wave_op().kernel.numpy()), vc[:, 0]),
+            "ns_cont": (programs.ns_continuity(o["D_x"], o["D_y"], n["dx"], n["dy"]),
+                        lambda: O.residual_ns_continuity(f[0], f[1], n["dx"], n["dy"], ko), vc),
+            "ns_mom": (programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"]),
+                       lambda: O.residual_ns_momentum(f[0], f[1], f[2], n["dx"], n["dy"], n["dt"], n["nu"], ko), vc),
+        }
+        for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+            progs["mhd_" + eq] = (programs.mhd(eq, o["D_t"], o["D_x"], o["D_y"]),
+                                  (lambda eq=eq: O.residual_mhd(eq, *f, ops=ko)), vc)
+        for name, (prog, oracle, inp) in progs.items():
+            prog.path = path
+            got = prog.residual(inp, boundary=True)
+            assert L.last_path() == ("tma" if path == L.PATH_TMA else "generic"), name
+            assert_close_rel(got.cpu().numpy(), oracle(), TOL, f"{name} {gen} {shape} path={path}")
+
+
+def _wave_op():
+    m = _mods()["2d"]
+    W = m.ConvOperator()
+    W.kernel = m.ConvOperator("t", 2).kernel - 0.25 * m.ConvOperator(("x", "y"), 2).kernel
+    return W
+
+
+@pytest.mark.parametrize("shape", [(5, 9, 260), (17, 6, 128), (3, 4, 8)])
+@pytest.mark.parametrize("path", [L.PATH_GENERIC, L.PATH_TMA])
+def test_burgers_and_advection_1d(shape, path):
+    m1 = _mods()["1d"]
+    c = synth.BURGERS
+    u = synth.fields(9, 1, shape)[:, 0]
+    pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                          c["dx"], c["dt"], c["nu"])
+    pb.path = path
+    assert_close_rel(pb.residual(cuda(u), True).cpu().numpy(), O.residual_burgers(u, c["dx"], c["dt"], c["nu"]),
+                     TOL, f"burgers {shape}")
+    A = m1.ConvOperator()
+    A.kernel = m1.ConvOperator("t", 1).kernel + 0.5 * m1.ConvOperator("x", 1).kernel
+    pa = programs.linear(A)
+    pa.path = path
+    assert_close_rel(pa.residual(cuda(u), True).cpu().numpy(), O.correlate(u, A.kernel.numpy()), TOL)
+    assert L.last_path() == ("tma" if path == L.PATH_TMA else "generic")
+
+
+def test_ragged_and_empty_inputs_take_the_generic_kernel():
+    m = _mods()
+    W = _wave_op()
+    rng = np.random.default_rng(3)
+    for shape in [(2, 5, 7, 197), (1, 1, 1, 1), (3, 2, 1, 5), (2, 80, 3, 2)]:
+        u = rng.standard_normal(shape, dtype=np.float32)
+        got = W(cuda(u))
+        assert L.last_path() == "generic"
+        assert_close_rel(got.cpu().numpy(), O.correlate(u, W.kernel.numpy()), TOL, str(shape))
+    e = W(torch.zeros(0, 4, 4, 4, device="cuda"))
+    assert e.shape == (0, 4, 4, 4)
+    A = m["1d"].ConvOperator()                              # config 1: Nx = 197 (not a multiple of 4)
+    A.kernel = m["1d"].ConvOperator("t", 1).kernel + 0.5 * m["1d"].ConvOperator("x", 1).kernel
+    u = rng.standard_normal((100, 10, 197), dtype=np.float32)
+    assert_close_rel(A(torch.from_numpy(u)).numpy(), O.correlate(u, A.kernel.numpy()), TOL)
+    with pytest.raises(NotImplementedError):                # forcing TMA on an unqualified request fails loudly
+        ops.run_program(L.PROG_LINEAR, [cuda(u).unsqueeze(2)], [A.kernel.numpy().reshape(3, 1, 3)], [(1, 0, 1)],
+                        path=L.PATH_TMA)
+    with pytest.raises(NotImplementedError):                # kernels beyond 7 taps per axis
+        ops.run_program(L.PROG_LINEAR, [cuda(u).unsqueeze(2)], [np.ones((9, 1, 3), np.float32)], [(4, 0, 1)])
+
+
+@pytest.mark.parametrize("path", [L.PATH_GENERIC, L.PATH_TMA])
+@pytest.mark.parametrize("shape", [(6, 9, 20, 132), (4, 5, 16, 256)])
+def test_fused_joint_score_epilogue(path, shape):
+    """scores[b] = max over interior cells of |R(pred) - ref| * weight -- one pass, nothing
+    but [BS] floats written -- against the oracle's residual + np.max."""
+    o, ko, n = _programs_2d(), O.ops_2d(), synth.NS
+    v = synth.fields(21, 3, shape)
+    ref = 0.3 * O.residual_ns_momentum(*(synth.fields(22, 3, shape)[:, j] for j in range(3)),
+                                       n["dx"], n["dy"], n["dt"], n["nu"], ko)
+    rng = np.random.default_rng(1)
+    w = rng.uniform(0.5, 2.0, shape[1:]).astype(np.float32)
+    res = O.residual_ns_momentum(v[:, 0], v[:, 1], v[:, 2], n["dx"], n["dy"], n["dt"], n["nu"], ko)
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    prog.path = path
+    inner = (slice(None), slice(1, -1), slice(1, -1), slice(1, -1))
+    for use_ref in (False, True):
+        for use_w in (False, True):
+            d = np.abs(res - ref) if use_ref else np.abs(res)
+            if use_w:
+                d = d * w
+            got = prog.joint_scores(cuda(v), cuda(w) if use_w else None, cuda(ref) if use_ref else None)
+            assert got.shape == (shape[0],)
+            assert_close_rel(got.cpu().numpy(), d[inner].max(axis=(1, 2, 3)), 2e-5, f"max ref={use_ref} w={use_w}")
+            got = prog.joint_scores(cuda(v), cuda(w) if use_w else None, cuda(ref) if use_ref else None,
+                                    interior=False)
+            assert_close_rel(got.cpu().numpy(), d.max(axis=(1, 2, 3)), 2e-5, "max, shell included")
+            got = prog.joint_scores(cuda(v), cuda(w) if use_w else None, cuda(ref) if use_ref else None,
+                                    reduce="sum")
+            assert_close_rel(got.cpu().numpy(), d[inner].astype(np.float64).sum(axis=(1, 2, 3)), 1e-4, "sum")
+    # marginal score tensor |R - ref|
+    got = prog.abs_scores(cuda(v), ref=cuda(ref))
+    assert_close_rel(got.cpu().numpy(), np.abs(res - ref)[inner], TOL, "abs_scores")
+    # NaN anywhere in a sample's interior propagates to that sample's score only (np.max semantics)
+    vn = v.copy()
+    vn[1, 0, 3, 5, 7] = np.nan
+    s = prog.joint_scores(cuda(vn)).cpu().numpy()
+    assert np.isnan(s[1]) and not np.isnan(np.delete(s, 1)).any()
+
+
+def test_fused_score_1d_batch_rows_mode():
+    m1 = _mods()["1d"]
+    c = synth.BURGERS
+    shape = (37, 12, 260)
+    u = synth.fields(31, 1, shape)[:, 0]
+    res = O.residual_burgers(u, c["dx"], c["dt"], c["nu"])
+    w = np.random.default_rng(2).uniform(0.5, 2.0, shape[1:]).astype(np.float32)
+    for path in (L.PATH_GENERIC, L.PATH_TMA):
+        pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                              c["dx"], c["dt"], c["nu"])
+        pb.path = path
+        got = pb.joint_scores(cuda(u), cuda(w))
+        assert_close_rel(got.cpu().numpy(), (np.abs(res) * w)[:, 1:-1, 1:-1].max(axis=(1, 2)), 2e-5, f"path {path}")
+
+
+def test_linearity_and_null_space_at_full_config_size():
+    """Size-independent properties at BASELINE config 3 (wave, [1024,80,128,128]): the composite
+    kernel annihilates constants away from the zero-padded shell, the operator is linear, and
+    the TMA and generic kernels agree on a slab."""
+    W = _wave_op()
+    bs = 1024
+    g = torch.Generator(device="cuda").manual_seed(0)
+    u = torch.randn(bs, 80, 128, 128, device="cuda", generator=g)
+    r = W(u)
+    assert L.last_path() == "tma" and r.shape == u.shape
+    c = W(torch.full((2, 80, 128, 128), 3.25, device="cuda"))
+    assert float(c[:, 1:-1, 1:-1, 1:-1].abs().max()) < 1e-5
+    v = torch.randn(8, 80, 128, 128, device="cuda", generator=g)
+    lhs = W(u[:8] + 2.0 * v)
+    rhs = r[:8] + 2.0 * W(v)
+    assert float((lhs - rhs).abs().max()) <= 1e-5 * float(rhs.abs().max())
+    pg = programs.linear(W)
+    pg.path = L.PATH_GENERIC
+    rg = pg.residual(u[:16], boundary=True)
+    assert float((rg - r[:16]).abs().max()) <= 1e-6 * float(rg.abs().max())
+    # fused joint score == max of the stored residual, bit for bit (same arithmetic, no weight)
+    s = programs.linear(W).joint_scores(u[:64])
+    assert torch.equal(s, r[:64, 1:-1, 1:-1, 1:-1].abs().amax(dim=(1, 2, 3)))
+
+
+def test_autograd_through_operator_matches_torch_conv3d():
+    """PRE as a training loss (Physics_Informed/Wave_FNO_PI.py): d(loss)/d(field) through D.
+    Floating-point kernel -> checked against a plain PyTorch fp32 reference of the same op."""
+    import torch.nn.functional as F
+    W = _wave_op()
+    u = torch.randn(2, 6, 12, 16, device="cuda", requires_grad=True)
+    loss = (W(u) ** 2).sum()
+    loss.backward()
+    u2 = u.detach().clone().requires_grad_(True)
+    k = W.kernel.cuda()
+    ref = (F.conv3d(u2.unsqueeze(1), k[None, None], padding=1).squeeze(1) ** 2).sum()
+    ref.backward()
+    assert_close_rel(u.grad.cpu().numpy(), u2.grad.cpu().numpy(), 1e-5, "grad")
