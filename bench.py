@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py -- the hot-path benchmark (driver contract in the task statement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ns|wave|burgers]
+
+Workload (default): BASELINE.json configs[3] -- 2-D Navier-Stokes vector PRE (momentum residual via
+the live ConvOperator kernels) + marginal per-cell CP, BS=512, Nt=50, 256x256, fp32, the shape the
+north_star target is quoted on.  One "step" = one pass of the hot path over one synthetic batch:
+
+    scores = |R_momentum(u,v,p)|                         K1 fused TMA stencil + |.| epilogue   (all BS samples)
+    qhat   = per-cell ceil((n+1)(1-a))/n quantile        K3 order statistics                   (calibration half)
+    cov    = mean(|r| <= qhat) on the other half         K5 coverage counts                    (validation half)
+
+`value` (Gpoints/s) = grid points of the logical [BS,Nt,Nx,Ny] field per second, inputs resident in
+HBM, CUDA-event timed, max over ranks.  `e2e` = the same step through the public API with HOST
+(pinned) inputs streamed to the device in batch chunks and qhat + coverage read back.
+`roofline` is for the dominant kernel (K1): algorithmic bytes (4F+4 = 16 B/point) / its own
+CUDA-event duration vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` times the
+reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host
+threads) on a bounded sample.  With --gpus N (torchrun) the batch axis is sharded: every rank owns
+BS samples (weak scaling); the only exchange is the marginal quantile's score all-to-all.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALPHA = 0.1
+WORKLOADS = {
+    # name: (BS, F, Nt, Nx, Ny, description)
+    "ns": (512, 3, 50, 256, 256, "configs[3]: 2D Navier-Stokes momentum PRE + marginal per-cell CP, BS=512 Nt=50 256x256"),
+    "wave": (1024, 1, 80, 128, 128, "configs[2]: 2D wave PRE + marginal per-cell CP, BS=1024 Nt=80 128x128"),
+}
+
+
+# ----------------------------------------------------------------------------------------
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (recipe in B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 8 for i in range(4) if r[4 + i].lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+def synth_fields_gpu(bs, nf, nt, nx, ny, device, seed, out=None, chunk=16):
+    """oracle/synth.py's smooth-plus-noise fields evaluated on the device (same formula, torch
+    RNG): random-init surrogate outputs, no downloaded data."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    if out is None:
+        out = torch.empty((bs, nf, nt, nx, ny), dtype=torch.float32, device=device)
+    t = torch.linspace(0, 1, nt, device=device).view(1, 1, nt, 1, 1)
+    x = (torch.arange(nx, device=device) / nx).view(1, 1, 1, nx, 1)
+    y = (torch.arange(ny, device=device) / ny).view(1, 1, 1, 1, ny)
+    for b0 in range(0, bs, chunk):
+        b1 = min(bs, b0 + chunk)
+        acc = 0.01 * torch.randn((b1 - b0, nf, nt, nx, ny), device=device, generator=g)
+        for m in range(1, 5):
+            a, phi, psi, lam = (torch.rand((b1 - b0, nf, 1, 1, 1), device=device, generator=g) for _ in range(4))
+            acc += (0.5 + 0.5 * a) * torch.sin(2 * np.pi * (m * x + phi)) * torch.cos(2 * np.pi * (m * y + psi)) \
+                * torch.exp(-(0.1 + 0.9 * lam) * t)
+        out[b0:b1] = acc
+    return out
+
+
+def make_program(workload):
+    import cp_pre_b200
+    from cp_pre_b200 import programs
+    from oracle import synth
+    cp_pre_b200.install()
+    import Utils.ConvOps_2d as C2
+    if workload == "ns":
+        c = synth.NS
+        D = [C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1), C2.ConvOperator(("x", "y"), 2)]
+        return programs.ns_momentum(*D, c["dx"], c["dy"], c["dt"], c["nu"])
+    W = C2.ConvOperator()
+    W.kernel = C2.ConvOperator("t", 2).kernel - synth.WAVE["c2"] * C2.ConvOperator(("x", "y"), 2).kernel
+    return programs.linear(W)
+
+
+class Step:
+    """One pass of the hot path over a device-resident batch (per rank)."""
+
+    def __init__(self, workload, device, world, seed):
+        from cp_pre_b200 import ops
+        from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+        self.ops = ops
+        self.bs, self.nf, self.nt, self.nx, self.ny, _ = WORKLOADS[workload]
+        self.workload, self.device, self.world = workload, device, world
+        self.prog = make_program(workload)
+        self.vars = synth_fields_gpu(self.bs, self.nf, self.nt, self.nx, self.ny, device, seed)
+        self.n_cal = self.bs // 2
+        self.rank_k = calibrate_rank(self.n_cal * world, self.n_cal * world, ALPHA)
+        self.scores = torch.empty((self.bs, self.nt, self.nx, self.ny), dtype=torch.float32, device=device)
+        self.points = self.bs * self.nt * self.nx * self.ny
+        self.interior_cells = (self.nt - 2) * (self.nx - 2) * (self.ny - 2)
+        self.k1_events = []
+
+    def _input(self, v):
+        return v if self.workload == "ns" else v[:, 0]
+
+    def pre(self, v, out, timed=False):
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        self.prog.abs_scores(self._input(v), boundary=True, out=out)
+        if timed:
+            e1.record()
+            self.k1_events.append((e0, e1))
+
+    def calibrate_and_cover(self):
+        from cp_pre_b200 import dist as D
+        cal = self.scores[: self.n_cal]
+        if self.world > 1:
+            qhat = D.marginal_quantiles(cal, [self.rank_k])[0]
+        else:
+            qhat = self.ops.select_ranks(cal, [self.rank_k])[0]
+        # coverage on the validation half, interior cells only: shell cells get half-width -1
+        band = torch.full_like(qhat, -1.0)
+        band[1:-1, 1:-1, 1:-1] = qhat[1:-1, 1:-1, 1:-1]
+        inside = self.ops.inside_count_band(self.scores[self.n_cal:], None, band, 1.0)
+        return qhat, inside.to(torch.int64).sum()
+
+    def run(self, timed=False):
+        self.pre(self.vars, self.scores, timed)
+        return self.calibrate_and_cover()
+
+
+class E2E:
+    """The same step through the public API with HOST inputs: pinned host batch -> chunked,
+    double-buffered H2D on a copy stream overlapped with K1 on the compute stream -> calibration
+    -> qhat + coverage read back to the host."""
+
+    def __init__(self, step: Step, chunk=32):
+        self.s, self.chunk = step, chunk
+        s = step
+        self.host = torch.empty(s.vars.shape, dtype=torch.float32, pin_memory=True)
+        self.host.copy_(s.vars)                            # synthetic host batch (one-off, untimed)
+        self.stage = [torch.empty((chunk,) + tuple(s.vars.shape[1:]), dtype=torch.float32, device=s.device)
+                      for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=s.device)
+        self.q_host = torch.empty((s.nt, s.nx, s.ny), dtype=torch.float32, pin_memory=True)
+        self.h2d_bytes = self.host.numel() * 4
+        self.d2h_bytes = self.q_host.numel() * 4 + 8
+
+    def run(self):
+        s = self.s
+        main = torch.cuda.current_stream(s.device)
+        ready = [torch.cuda.Event() for _ in range(2)]
+        freed = [torch.cuda.Event() for _ in range(2)]
+        for i, b0 in enumerate(range(0, s.bs, self.chunk)):
+            b1 = min(s.bs, b0 + self.chunk)
+            buf = self.stage[i % 2]
+            with torch.cuda.stream(self.copy_stream):
+                if i >= 2:
+                    self.copy_stream.wait_event(freed[i % 2])
+                buf[: b1 - b0].copy_(self.host[b0:b1], non_blocking=True)
+                ready[i % 2].record(self.copy_stream)
+            main.wait_event(ready[i % 2])
+            s.pre(buf[: b1 - b0], s.scores[b0:b1])
+            freed[i % 2].record(main)
+        qhat, inside = s.calibrate_and_cover()
+        self.q_host.copy_(qhat, non_blocking=True)
+        cov = int(inside.item()) / float((s.bs - s.n_cal) * s.interior_cells)    # D2H + sync
+        return cov
+
+
+# ----------------------------------------------------------------------------------------
+def cpu_reference_sample(workload, threads=None, bs_pre=8, nt_cp=6):
+    """The reference's CPU path on a bounded sample of the same workload; returns
+    (Gpoints/s normalised to the whole step, description, seconds)."""
+    from oracle import cpu_oracle as O
+    from oracle import synth, torch_port as TP
+    bs, nf, nt, nx, ny, _ = WORKLOADS[workload]
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    v = torch.from_numpy(synth.fields(99, nf, (bs_pre, nt, nx, ny)))
+    c = synth.NS
+    t0 = time.perf_counter()
+    if workload == "ns":
+        res = TP.ns_momentum(v, c["dx"], c["dy"], c["dt"], c["nu"])
+    else:
+        res = TP.wave(v[:, 0], synth.WAVE["c2"])
+    t_pre = time.perf_counter() - t0
+    pts_pre = bs_pre * nt * nx * ny
+    # calibration / coverage on [n_cal, nt_cp, Nx-2, Ny-2] residual-like scores
+    n_cal = bs // 2
+    rng = np.random.default_rng(0)
+    cal = torch.from_numpy((res.numpy()[:1, :nt_cp].std() * rng.standard_normal((n_cal, nt_cp, nx - 2, ny - 2))).astype(np.float32))
+    val = cal[: n_cal // 2]
+    t0 = time.perf_counter()
+    scores = np.abs(cal.numpy())
+    qhat = O.calibrate(scores, len(scores), ALPHA)
+    t_q = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    O.emp_cov([-qhat, qhat], val.numpy())
+    t_cov = time.perf_counter() - t0
+    P = bs * nt * nx * ny
+    full = t_pre * (P / pts_pre) + t_q * ((P / 2) / scores.size) + t_cov * ((P / 2) / val.numel())
+    desc = (f"PRE on BS={bs_pre} of {bs} ({t_pre:.2f}s); np.abs+np.quantile on [{n_cal},{nt_cp},{nx-2},{ny-2}] "
+            f"({t_q:.2f}s); emp_cov on [{n_cal//2},{nt_cp},{nx-2},{ny-2}] ({t_cov:.2f}s); per-unit times scaled to the full step")
+    return P / full / 1e9, desc, t_pre + t_q + t_cov, threads
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port: same
+    torch/NumPy calls, all host threads), each step a bounded sample.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    W = args.warmup
+    for _ in range(min(W, 1)):
+        cpu_reference_sample(args.workload, bs_pre=2, nt_cp=2)
+    vals, secs = [], []
+    for _ in range(args.steps):
+        v, desc, s, threads = cpu_reference_sample(args.workload)
+        vals.append(v)
+        secs.append(s)
+    bs, nf, nt, nx, ny, wdesc = WORKLOADS[args.workload]
+    value = float(np.mean(vals))
+    P = bs * nt * nx * ny
+    print(json.dumps({
+        "impl": "reference", "metric": "PRE+marginal-CP throughput", "value": value, "unit": "Gpoints/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": W, "ms_per_step": 1e3 * P / (value * 1e9),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wdesc, "fields": nf, "alpha": ALPHA},
+        "cpu_baseline": {"value": value, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc},
+        "e2e": {"value": value, "unit": "Gpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ----------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    from cp_pre_b200 import _lib, dist as D
+    rank, world, device = D.init_from_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
+    W, K = max(args.warmup, 3), args.steps
+    step = Step(args.workload, device, world, seed=1234 + rank)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(W):
+        qhat, inside = step.run()
+    barrier()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(device.index or 0) as clk:
+        barrier()
+        e0.record()
+        for _ in range(K):
+            qhat, inside = step.run(timed=True)
+        e1.record()
+        barrier()
+    launches = _lib.launch_count() - l0
+    ms = e0.elapsed_time(e1) / K
+    k1_ms = float(np.mean([a.elapsed_time(b) for a, b in step.k1_events]))
+    t = torch.tensor([ms, k1_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms, k1_ms = float(t[0]), float(t[1])
+    tot_inside, tot_cells = D.allreduce_counts(int(inside.item()), (step.bs - step.n_cal) * step.interior_cells,
+                                               device=device)
+    coverage = tot_inside / tot_cells
+    P_all = step.points * world
+    value = P_all / (ms * 1e-3) / 1e9
+
+    # end-to-end through the public API with host inputs
+    e2e = None
+    if not args.no_e2e:
+        ee = E2E(step)
+        for _ in range(2):
+            ee.run()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ke = max(2, min(K, 5))
+        for _ in range(ke):
+            ee.run()
+        b.record()
+        barrier()
+        t = torch.tensor([a.elapsed_time(b) / ke], dtype=torch.float64, device=device)
+        if world > 1:
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        e2e = {"value": P_all / (float(t[0]) * 1e-3) / 1e9, "unit": "Gpoints/s", "h2d_bytes_per_step": ee.h2d_bytes * world,
+               "d2h_bytes_per_step": ee.d2h_bytes * world, "ms_per_step": float(t[0]),
+               "path": "pinned host batch -> 32-sample double-buffered H2D overlapped with K1 -> K3/K5 -> qhat+coverage D2H"}
+        del ee
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        bpp = 4 * step.nf + 4
+        achieved = bpp * step.points / (k1_ms * 1e-3) / 1e9
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            v, desc, secs, threads = cpu_reference_sample(args.workload)
+            cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc}
+        print(json.dumps({
+            "metric": "PRE+marginal-CP throughput", "value": value, "unit": "Gpoints/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][5], "fields": step.nf, "alpha": ALPHA,
+                       "per_gpu_batch": step.bs, "global_batch": step.bs * world, "sharding": "batch axis",
+                       "l2": f"inputs ({step.vars.numel() * 4 / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
+                       "empirical_coverage": coverage, "target_coverage": 1 - ALPHA},
+            "roofline": {"bound": "hbm", "kernel": "star_kernel<NS_MOMENTUM> (K1: TMA stencil + |.| epilogue, STORE)"
+                         if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "bytes_per_point": bpp,
+                         "kernel_ms": k1_ms, "kernel_gpoints_s": step.points / (k1_ms * 1e-3) / 1e9,
+                         "share_of_step": k1_ms / ms},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+        }))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -91,7 +91,8 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
                 pads: Sequence[Sequence[int]], scalars: Sequence[float] = (), *,
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
                 ref: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None,
-                path: int = L.PATH_AUTO, canonicalise: bool = True) -> torch.Tensor:
+                path: int = L.PATH_AUTO, canonicalise: bool = True,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Runs one fused residual program.
 
     fields   CUDA fp32 tensors, all of logical shape [B, N2, N1, N0], any strides (views welcome)
@@ -174,7 +175,13 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         keep.append(weight)
     with torch.cuda.device(dev):
         if mode == L.EPI_STORE:
-            out = torch.empty((B, *O), dtype=torch.float32, device=dev)
+            if out is None:
+                out = torch.empty((B, *O), dtype=torch.float32, device=dev)
+            else:      # caller-owned destination (e.g. a batch slice of a larger score tensor)
+                if perm != [0, 1, 2]:
+                    out = out.permute([0] + [1 + d for d in perm])
+                if tuple(out.shape) != (B, *O) or out.dtype != torch.float32 or out.device != dev:
+                    raise ValueError(f"out must be a float32 {(B, *O)} tensor on {dev}")
             epi.d_out = out.data_ptr() if out.numel() else 0
             for d in range(4):
                 epi.out_stride[d] = out.stride(d)

@@ -83,12 +83,13 @@ class ResidualProgram:
     __call__ = residual
 
     # -- fused epilogues ----------------------------------------------------------------
-    def abs_scores(self, vars_, ref=None, boundary=False):
+    def abs_scores(self, vars_, ref=None, boundary=False, out=None):
         """|residual - ref| (the marginal nonconformity score) in one pass.  ``ref`` is a FULL
-        residual field (boundary=True form) or None."""
+        residual field (boundary=True form) or None; ``out`` an optional caller-owned FULL-size
+        CUDA destination (e.g. a batch slice of a larger score tensor)."""
         staged = ops.Staged(vars_)
         r = None if ref is None else self._unsq(ops.to_cuda(ref))
-        full = self._run(vars_, flags=L.FLAG_ABS, ref=r)
+        full = self._run(vars_, flags=L.FLAG_ABS, ref=r, out=self._unsq(out))
         if self.nd == 2:
             full = full.squeeze(2)
         return staged.back(full if boundary else self._crop(full))

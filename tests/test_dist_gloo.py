@@ -1,0 +1,110 @@
+"""world_size-2 gloo tests (CPU) of the multi-GPU orchestration in cp_pre_b200/dist.py.  The CUDA
+kernels are replaced by the oracle's NumPy implementations through the injection points, so only
+the host logic (sharding, Chan merge, radix passes + all-reduce, all-to-all transposition) runs."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import cpu_oracle as O
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _np_hist(x, prefix, mask, shift, hist):
+    keys = O.float_order_key(x.numpy().reshape(-1))
+    sel = (keys & np.uint32(mask)) == np.uint32(prefix)
+    h = np.bincount((keys[sel] >> np.uint32(shift)) & np.uint32(255), minlength=256)
+    hist += torch.from_numpy(h.astype(np.int32))
+    return hist
+
+
+def _np_select(scores, ranks):
+    s = scores.numpy()
+    return torch.from_numpy(np.stack([O.select_rank(s, r) for r in ranks]))
+
+
+def _np_moments(a, b):
+    x = a.numpy().astype(np.float64) - (0 if b is None else b.numpy().astype(np.float64))
+    x = x.reshape(x.shape[0], -1)
+    return torch.from_numpy(x.mean(0)), torch.from_numpy(((x - x.mean(0)) ** 2).sum(0))
+
+
+def _np_std(m2, count, eps, want_inv):
+    sd = (torch.sqrt(m2 / count) + eps).float()
+    return (sd, 1.0 / sd) if want_inv else sd
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from cp_pre_b200 import dist as D
+    r, w, dev = D.init_from_env("gloo")
+    assert (r, w, dev.type) == (rank, world, "cpu")
+    rng = np.random.default_rng(123)                       # same stream on both ranks
+    full = (rng.standard_normal((40, 6, 7)) * 2 + 1).astype(np.float32)
+    lo, hi = D.shard_range(40, rank, world)
+    mine = torch.from_numpy(full[lo:hi])
+    res = {}
+    # global modulation = std over the union of both shards
+    sd, inv = D.global_cell_std(mine, None, 1e-6, moments_fn=_np_moments, std_fn=_np_std)
+    res["std_err"] = float(np.max(np.abs(sd.numpy() - (np.std(full, axis=0) + 1e-6))))
+    # joint quantile, both exchange forms
+    scores = np.abs(full).reshape(40, -1).max(axis=1)
+    my_scores = torch.from_numpy(scores[lo:hi])
+    want = np.sort(scores)
+    for k in (0, 13, 39):
+        assert D.joint_quantile_hist(my_scores, k, hist_fn=_np_hist) == float(want[k])
+        got = D.joint_quantile_gather(my_scores, [k], select_fn=_np_select)
+        assert float(got[0]) == float(want[k])
+    nan_scores = my_scores.clone()
+    if rank == 1:
+        nan_scores[0] = float("nan")
+    assert np.isnan(D.joint_quantile_hist(nan_scores, 5, hist_fn=_np_hist))
+    with pytest.raises(ValueError):
+        D.joint_quantile_hist(my_scores, 40, hist_fn=_np_hist)
+    # marginal per-cell quantiles through the all-to-all (42 cells: exercises the padding to a
+    # multiple of the world size when world == 4; divisible when world == 2)
+    q = D.marginal_quantiles(torch.from_numpy(np.abs(full[lo:hi])), [5, 20, 36], select_fn=_np_select)
+    ref = np.sort(np.abs(full), axis=0)[[5, 20, 36]]
+    res["marginal_equal"] = bool(np.array_equal(q.numpy(), ref))
+    odd = np.abs(full[:, :, :5])                           # 30 cells -> not divisible by 4 either way
+    q = D.marginal_quantiles(torch.from_numpy(odd[lo:hi]).contiguous(), [7], select_fn=_np_select)
+    res["marginal_odd_equal"] = bool(np.array_equal(q.numpy(), np.sort(odd, axis=0)[[7]]))
+    res["counts"] = D.allreduce_counts(rank + 1, 10)
+    out[rank] = res
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_calibration_orchestration(world):
+    port = _free_port()
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_worker, args=(world, port, out), nprocs=world, join=True)
+        assert len(out) == world
+        for rank in range(world):
+            r = out[rank]
+            assert r["std_err"] < 1e-6
+            assert r["marginal_equal"] and r["marginal_odd_equal"]
+            assert r["counts"] == [world * (world + 1) // 2, 10 * world]
+
+
+def test_shard_range_partitions_exactly():
+    from cp_pre_b200.dist import shard_range
+    for total in (0, 1, 7, 512, 2048):
+        for world in (1, 2, 3, 8):
+            spans = [shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1

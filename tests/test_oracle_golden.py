@@ -272,3 +272,17 @@ def test_float_order_key_is_monotone():
     k = O.float_order_key(x)
     assert np.all(np.diff(k.astype(np.int64)) >= 0)
     assert O.float_order_key(np.float32(np.nan)) > k[-1]
+
+
+def test_torch_port_matches_reference():
+    """The timed CPU baseline (oracle/torch_port.py) reproduces the reference's outputs."""
+    import torch
+    from oracle import synth, torch_port as TP
+    g = load_golden("residuals")
+    n, c = synth.NS, synth.BURGERS
+    assert_close_rel(TP.ns_momentum(torch.from_numpy(g["ns|vars"]), n["dx"], n["dy"], n["dt"], n["nu"],
+                                    boundary=True).numpy(), g["ns|mom"], 1e-6)
+    assert_close_rel(TP.wave(torch.from_numpy(g["wave|u"][:, 0]), 0.25).numpy(), g["wave|res"], 1e-6)
+    assert_close_rel(TP.burgers(torch.from_numpy(g["burgers|u"]), c["dx"], c["dt"], c["nu"], True).numpy(),
+                     g["burgers|res"], 1e-6)
+    assert_close_rel(TP.mhd_momentum(torch.from_numpy(g["mhd|vars"]), boundary=True).numpy(), g["mhd|momentum"], 1e-6)
