@@ -83,11 +83,8 @@ joint_score_kernel(const float* __restrict__ a, int64_t as, const float* __restr
 }
 
 // ------------------------------------------------------------------------------------------
-// K3a: per-cell multi-rank select -- column tile in shared memory, one thread per cell,
-// data-independent bitonic network on order-preserving uint32 keys (threads never interact,
-// so no barriers inside the sort; column c of the tile lives in bank c: conflict-free).
+// K3: order statistics along the sample axis
 // ------------------------------------------------------------------------------------------
-constexpr int kSortCells = 32;       // cells (threads) per CTA -> 128-byte row segments
 constexpr int kMaxRanks = 32;
 
 struct RankList {
@@ -95,44 +92,153 @@ struct RankList {
     int32_t r[kMaxRanks];
 };
 
-__global__ void __launch_bounds__(kSortCells)
-select_sort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int32_t npow2, int64_t cells,
-                   RankList ranks, float* __restrict__ out) {
-    extern __shared__ uint32_t keys[];   // [npow2][kSortCells]
-    const int lane = threadIdx.x;
-    const int64_t c = (int64_t)blockIdx.x * kSortCells + lane;
-    const bool live = c < cells;
-    bool has_nan = false;
-    for (int i = 0; i < npow2; ++i) {
-        uint32_t k = 0xffffffffu;        // padding sorts last
-        if (live && i < n) {
-            const uint32_t bits = __float_as_uint(__ldg(x + (int64_t)i * xs + c));
-            has_nan |= (bits & 0x7fffffffu) > 0x7f800000u;
-            k = float_to_key(bits);
+// K3r: per-cell multi-rank select, register-resident bitonic network (the fast path, n <= 2048).
+// A CTA stages a [N samples x TC cells] tile of order-preserving uint32 keys in shared memory
+// with fully coalesced row loads, then every cell's column is spread over L lanes x R registers
+// (N = L*R = next power of two >= n, padding keys sort last).  The network is the all-ascending
+// bitonic form (each merge level starts with a "flip" comparator i <-> i^(k-1), then plain
+// half-cleaners), so no comparator direction depends on the lane: strides below R are
+// register-register min/max pairs with compile-time indices, strides >= R are one SHFL.BFLY plus
+// one min-or-max.  After the sort the element of rank k sits in lane k / R, register k % R, so
+// any number of ranks costs one sort.  Shared-memory rows are padded to TC+1 words: both the
+// row-wise fill and the column-wise read-out are bank-conflict free.
+template <int R>
+__device__ __forceinline__ void ce_regs(uint32_t (&k)[R], int a, int b) {
+    const uint32_t lo = min(k[a], k[b]), hi = max(k[a], k[b]);
+    k[a] = lo;
+    k[b] = hi;
+}
+
+template <int L, int R>
+__device__ __forceinline__ void bitonic_sort_regs(uint32_t (&k)[R], const int j) {
+    constexpr int N = L * R;
+#pragma unroll
+    for (int size = 2; size <= N; size <<= 1) {
+        // flip step: partner = s ^ (size-1), s = j*R + r
+        if (size <= R) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if ((r & (size >> 1)) == 0) ce_regs<R>(k, r, r ^ (size - 1));
+        } else {
+            const int lm = size / R - 1;                     // lane xor mask (all lane bits of the block)
+            const bool lower = (j & (size / R / 2)) == 0;    // this lane holds the lower half
+            uint32_t o[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) o[r] = __shfl_xor_sync(0xffffffffu, k[R - 1 - r], lm);
+#pragma unroll
+            for (int r = 0; r < R; ++r) k[r] = lower ? min(k[r], o[r]) : max(k[r], o[r]);
         }
-        keys[i * kSortCells + lane] = k;
-    }
-    for (int size = 2; size <= npow2; size <<= 1) {
-        for (int stride = size >> 1; stride > 0; stride >>= 1) {
-#pragma unroll 4
-            for (int t = 0; t < (npow2 >> 1); ++t) {
-                const int lo = ((t & ~(stride - 1)) << 1) | (t & (stride - 1));
-                const int hi = lo | stride;
-                const bool up = (lo & size) == 0;
-                const uint32_t a = keys[lo * kSortCells + lane];
-                const uint32_t b = keys[hi * kSortCells + lane];
-                const bool sw = up ? (a > b) : (a < b);
-                keys[lo * kSortCells + lane] = sw ? b : a;
-                keys[hi * kSortCells + lane] = sw ? a : b;
+        // half-cleaners
+#pragma unroll
+        for (int stride = size >> 2; stride > 0; stride >>= 1) {
+            if (stride < R) {
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if ((r & stride) == 0) ce_regs<R>(k, r, r | stride);
+            } else {
+                const int lm = stride / R;
+                const bool lower = (j & lm) == 0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const uint32_t o = __shfl_xor_sync(0xffffffffu, k[r], lm);
+                    k[r] = lower ? min(k[r], o) : max(k[r], o);
+                }
             }
         }
     }
-    if (!live) return;
-    for (int r = 0; r < ranks.n; ++r) {
-        const uint32_t k = keys[ranks.r[r] * kSortCells + lane];
-        out[(int64_t)r * cells + c] = has_nan ? __uint_as_float(0x7fc00000u)
-                                              : __uint_as_float(key_to_float_bits(k));
+}
+
+template <int L, int R, int TC>
+__global__ void __launch_bounds__(TC * L)
+select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells, RankList ranks,
+                      float* __restrict__ out) {
+    constexpr int N = L * R;
+    constexpr int THREADS = TC * L;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int CW = 32 / L;              // cells handled by one warp
+    constexpr int LD = TC + 1;              // padded row length (words)
+    constexpr int RPW = 32 / TC;            // tile rows covered by one warp-wide load (1 or 2)
+    static_assert(L >= 1 && L <= 32 && (TC == 32 || TC == 16) && CW * WARPS == TC, "bad tiling");
+    extern __shared__ uint32_t tile[];      // [N][LD] keys, then TC NaN flags
+    uint32_t* nanflag = tile + N * LD;
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int64_t c0 = (int64_t)blockIdx.x * TC;
+    if (tid < TC) nanflag[tid] = 0u;
+
+    // fill: warp w takes rows (w*RPW + lane/TC) + WARPS*RPW*i, column lane % TC
+    {
+        const int col = lane % TC;
+        const bool live = c0 + col < cells;
+        const float* px = x + c0 + col;
+        bool nan = false;
+#pragma unroll 8
+        for (int row = w * RPW + lane / TC; row < N; row += WARPS * RPW) {
+            uint32_t key = 0xffffffffu;     // padding sorts last
+            if (live && row < n) {
+                const uint32_t bits = __float_as_uint(__ldg(px + (int64_t)row * xs));
+                nan |= (bits & 0x7fffffffu) > 0x7f800000u;
+                key = float_to_key(bits);
+            }
+            tile[row * LD + col] = key;
+        }
+        __syncthreads();                    // flags zeroed before anyone raises one
+        if (nan) nanflag[col] = 1u;
     }
+    __syncthreads();
+
+    // read-out: lane = i*L + j; cell-in-tile ct = w + WARPS*i; sample rows r*L + j
+    const int j = lane % L, i = lane / L;
+    const int ct = w + WARPS * i;
+    uint32_t k[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) k[r] = tile[(r * L + j) * LD + ct];
+    const bool has_nan = nanflag[ct] != 0u;
+
+    bitonic_sort_regs<L, R>(k, j);
+
+    const int64_t c = c0 + ct;
+    for (int q = 0; q < ranks.n; ++q) {
+        const int kq = ranks.r[q];
+        const int rq = kq % R;
+        uint32_t v = k[0];
+#pragma unroll
+        for (int r = 1; r < R; ++r) v = (rq == r) ? k[r] : v;
+        if (kq / R == j && c < cells)
+            out[(int64_t)q * cells + c] = has_nan ? __uint_as_float(0x7fc00000u)
+                                                  : __uint_as_float(key_to_float_bits(v));
+    }
+}
+
+template <int L, int R, int TC>
+int launch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
+                   cudaStream_t st) {
+    constexpr int N = L * R;
+    const size_t smem = ((size_t)N * (TC + 1) + TC) * sizeof(uint32_t);
+    auto kern = select_regsort_kernel<L, R, TC>;
+    static bool configured = false;
+    if (!configured) {
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    const int64_t blocks = (cells + TC - 1) / TC;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    kern<<<(unsigned)blocks, TC * L, smem, st>>>(x, xs, (int32_t)n, cells, rl, out);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+// n <= 2048: pick the smallest network that holds n keys.  Returns -1 when n is too large.
+int dispatch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
+                     cudaStream_t st) {
+    if (n <= 32) return launch_regsort<1, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 64) return launch_regsort<2, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 128) return launch_regsort<4, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 256) return launch_regsort<8, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 512) return launch_regsort<16, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 1024) return launch_regsort<32, 32, 32>(x, xs, n, cells, rl, out, st);
+    if (n <= 2048) return launch_regsort<32, 64, 16>(x, xs, n, cells, rl, out, st);
+    return -1;
 }
 
 // K3b: per-cell single-rank radix select straight from global memory (any n).  8 passes of
@@ -295,23 +401,13 @@ int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int
             rl.r[r] = h_ranks[r0 + r];
         }
         float* out = d_out + (int64_t)r0 * cells;
-        int npow2 = 1;
-        while (npow2 < n) npow2 <<= 1;
-        const size_t smem = (size_t)npow2 * kSortCells * sizeof(uint32_t);
-        if (smem <= 128 * 1024) {
-            static size_t configured = 0;
-            if (smem > configured) {
-                CPPRE_CHECK_CUDA(cudaFuncSetAttribute(select_sort_kernel,
-                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                configured = smem;
-            }
-            const int64_t blocks = (cells + kSortCells - 1) / kSortCells;
-            select_sort_kernel<<<(unsigned)blocks, kSortCells, smem, st>>>(d_scores, row_stride, (int)n, npow2,
-                                                                          cells, rl, out);
-        } else {
-            const int64_t blocks = (cells + kThreads - 1) / kThreads;
-            select_radix_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d_scores, row_stride, n, cells, rl, out);
+        if (n <= 2048) {
+            const int rc = dispatch_regsort(d_scores, row_stride, n, cells, rl, out, st);
+            if (rc != CPPRE_OK) return rc;
+            continue;
         }
+        const int64_t blocks = (cells + kThreads - 1) / kThreads;
+        select_radix_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d_scores, row_stride, n, cells, rl, out);
         CPPRE_CHECK_LAUNCH();
     }
     return CPPRE_OK;

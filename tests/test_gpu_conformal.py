@@ -45,7 +45,10 @@ def test_helpers_against_reference_inline_twins_golden():
 
 
 @pytest.mark.parametrize("n,cells", [(20, (7,)), (100, (5, 33)), (256, (3, 10, 20)), (500, (40,)), (1000, (9,)),
-                                     (1, (4,)), (1500, (70,))])
+                                     (1, (4,)), (1500, (70,)), (2, (1,)), (31, (65,)), (32, (32,)), (33, (31,)),
+                                     (64, (3, 11)), (65, (100,)), (128, (97,)), (129, (33,)), (257, (34,)),
+                                     (512, (48,)), (513, (17,)), (1024, (33,)), (1025, (19,)), (2048, (21,)),
+                                     (2049, (5,)), (3000, (3,))])
 def test_calibrate_is_bit_exact_per_cell(n, cells):
     rng = np.random.default_rng(n)
     s = np.abs(rng.standard_normal((n,) + cells)).astype(np.float32)
@@ -65,6 +68,29 @@ def test_calibrate_is_bit_exact_per_cell(n, cells):
         many = calibrate_many(cuda(s), n, ok)
         for i, a in enumerate(ok):
             np.testing.assert_array_equal(many[i].cpu().numpy(), O.calibrate(s, n, a))
+
+
+@pytest.mark.parametrize("n", [7, 100, 256, 300, 2048])
+def test_select_ranks_every_rank_signed_values_nan_and_strided_rows(n):
+    """Every order statistic at once (one sort serves all ranks), signed values, +-inf, NaN
+    columns, and a row stride larger than the cell count (a column slice of a wider tensor)."""
+    rng = np.random.default_rng(100 + n)
+    cells = 77
+    wide = (rng.standard_normal((n, cells + 13)) * 5).astype(np.float32)
+    wide[rng.integers(0, n, 3), 5] = np.inf
+    wide[rng.integers(0, n, 3), 6] = -np.inf
+    wide[rng.integers(0, n), 9] = np.nan
+    wide[:, 11] = 1.5                                   # all ties
+    wide[:, 12] = -0.0
+    t = cuda(wide)[:, 3:3 + cells]
+    ref = np.sort(wide[:, 3:3 + cells], axis=0)
+    ranks = list(range(n)) if n <= 300 else [0, 1, 31, 32, 33, 1023, 1024, 1025, n - 2, n - 1]
+    for r0 in range(0, len(ranks), 40):                 # > kMaxRanks per call exercises the chunking
+        rr = ranks[r0:r0 + 40]
+        got = ops.select_ranks(t, rr).cpu().numpy()
+        want = ref[rr]
+        want[:, np.isnan(ref).any(axis=0)] = np.nan
+        np.testing.assert_array_equal(got, want)
 
 
 def test_calibrate_scalar_joint_form_negative_values_and_nan():
