@@ -7,15 +7,16 @@ Workload (default): BASELINE.json configs[3] -- 2-D Navier-Stokes vector PRE (mo
 the live ConvOperator kernels) + marginal per-cell CP, BS=512, Nt=50, 256x256, fp32, the shape the
 north_star target is quoted on.  One "step" = one pass of the hot path over one synthetic batch:
 
-    scores = |R_momentum(u,v,p)|                         K1 fused TMA stencil + |.| epilogue   (all BS samples)
-    qhat   = per-cell ceil((n+1)(1-a))/n quantile        K3 order statistics                   (calibration half)
-    cov    = mean(|r| <= qhat) on the other half         K5 coverage counts                    (validation half)
+    scores = |R_momentum(u,v,p)|                         K1 fused TMA stencil + |.| epilogue, STORE  (calibration half)
+    qhat   = per-cell ceil((n+1)(1-a))/n quantile        K3 order statistics                         (calibration half)
+    cov    = mean(-qhat <= R <= qhat) on the other half  K1 again, COVER epilogue: residuals and sets
+                                                         of the validation half are never written    (validation half)
 
 `value` (Gpoints/s) = grid points of the logical [BS,Nt,Nx,Ny] field per second, inputs resident in
 HBM, CUDA-event timed, max over ranks.  `e2e` = the same step through the public API with HOST
 (pinned) inputs streamed to the device in batch chunks and qhat + coverage read back.
 `roofline` is for the dominant kernel (K1): algorithmic bytes (4F+4 = 16 B/point) / its own
-CUDA-event duration vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` times the
+CUDA-event duration (STORE launch over the calibration half) vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` times the
 reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host
 threads) on a bounded sample.  With --gpus N (torchrun) the batch axis is sharded: every rank owns
 BS samples (weak scaling); the only exchange is the marginal quantile's score all-to-all.
@@ -127,7 +128,11 @@ def make_program(workload):
 
 
 class Step:
-    """One pass of the hot path over a device-resident batch (per rank)."""
+    """One pass of the hot path over a device-resident batch (per rank):
+        K1 STORE  |R(cal half)|            -> scores [n_cal, Nt, Nx, Ny]
+        K3        per-cell quantile        -> qhat   [Nt, Nx, Ny]
+        K1 COVER  -qhat <= R(val half) <= qhat counted per sample (interior cells); the validation
+                  residuals and the prediction sets are never written."""
 
     def __init__(self, workload, device, world, seed):
         from cp_pre_b200 import ops
@@ -139,39 +144,41 @@ class Step:
         self.vars = synth_fields_gpu(self.bs, self.nf, self.nt, self.nx, self.ny, device, seed)
         self.n_cal = self.bs // 2
         self.rank_k = calibrate_rank(self.n_cal * world, self.n_cal * world, ALPHA)
-        self.scores = torch.empty((self.bs, self.nt, self.nx, self.ny), dtype=torch.float32, device=device)
+        self.scores = torch.empty((self.n_cal, self.nt, self.nx, self.ny), dtype=torch.float32, device=device)
         self.points = self.bs * self.nt * self.nx * self.ny
         self.interior_cells = (self.nt - 2) * (self.nx - 2) * (self.ny - 2)
-        self.k1_events = []
+        self.k1_events, self.k1c_events = [], []
 
     def _input(self, v):
         return v if self.workload == "ns" else v[:, 0]
 
-    def pre(self, v, out, timed=False):
-        if timed:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-        self.prog.abs_scores(self._input(v), boundary=True, out=out)
-        if timed:
-            e1.record()
-            self.k1_events.append((e0, e1))
+    def _timed(self, fn, sink, timed):
+        if not timed:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        sink.append((e0, e1))
+        return out
 
-    def calibrate_and_cover(self):
+    def pre_cal(self, v, out, timed=False):
+        return self._timed(lambda: self.prog.abs_scores(self._input(v), boundary=True, out=out), self.k1_events, timed)
+
+    def quantile(self):
         from cp_pre_b200 import dist as D
-        cal = self.scores[: self.n_cal]
         if self.world > 1:
-            qhat = D.marginal_quantiles(cal, [self.rank_k])[0]
-        else:
-            qhat = self.ops.select_ranks(cal, [self.rank_k])[0]
-        # coverage on the validation half, interior cells only: shell cells get half-width -1
-        band = torch.full_like(qhat, -1.0)
-        band[1:-1, 1:-1, 1:-1] = qhat[1:-1, 1:-1, 1:-1]
-        inside = self.ops.inside_count_band(self.scores[self.n_cal:], None, band, 1.0)
-        return qhat, inside.to(torch.int64).sum()
+            return D.marginal_quantiles(self.scores, [self.rank_k])[0]
+        return self.ops.select_ranks(self.scores, [self.rank_k])[0]
+
+    def cover_val(self, v, qhat, timed=False):
+        return self._timed(lambda: self.prog.coverage_counts(self._input(v), 1.0, half=qhat), self.k1c_events, timed)
 
     def run(self, timed=False):
-        self.pre(self.vars, self.scores, timed)
-        return self.calibrate_and_cover()
+        self.pre_cal(self.vars[: self.n_cal], self.scores, timed)
+        qhat = self.quantile()
+        inside = self.cover_val(self.vars[self.n_cal:], qhat, timed)
+        return qhat, inside.to(torch.int64).sum()
 
 
 class E2E:
@@ -196,6 +203,7 @@ class E2E:
         main = torch.cuda.current_stream(s.device)
         ready = [torch.cuda.Event() for _ in range(2)]
         freed = [torch.cuda.Event() for _ in range(2)]
+        qhat, inside = None, []
         for i, b0 in enumerate(range(0, s.bs, self.chunk)):
             b1 = min(s.bs, b0 + self.chunk)
             buf = self.stage[i % 2]
@@ -204,12 +212,17 @@ class E2E:
                     self.copy_stream.wait_event(freed[i % 2])
                 buf[: b1 - b0].copy_(self.host[b0:b1], non_blocking=True)
                 ready[i % 2].record(self.copy_stream)
+            if b0 == s.n_cal:                          # calibration half is on the device: qhat
+                qhat = s.quantile()
             main.wait_event(ready[i % 2])
-            s.pre(buf[: b1 - b0], s.scores[b0:b1])
+            if b0 < s.n_cal:
+                s.pre_cal(buf[: b1 - b0], s.scores[b0:b1])
+            else:
+                inside.append(s.cover_val(buf[: b1 - b0], qhat))
             freed[i % 2].record(main)
-        qhat, inside = s.calibrate_and_cover()
         self.q_host.copy_(qhat, non_blocking=True)
-        cov = int(inside.item()) / float((s.bs - s.n_cal) * s.interior_cells)    # D2H + sync
+        total = torch.cat(inside).to(torch.int64).sum()
+        cov = int(total.item()) / float((s.bs - s.n_cal) * s.interior_cells)    # D2H + sync
         return cov
 
 
@@ -316,10 +329,11 @@ def main():
     launches = _lib.launch_count() - l0
     ms = e0.elapsed_time(e1) / K
     k1_ms = float(np.mean([a.elapsed_time(b) for a, b in step.k1_events]))
-    t = torch.tensor([ms, k1_ms], dtype=torch.float64, device=device)
+    k1c_ms = float(np.mean([a.elapsed_time(b) for a, b in step.k1c_events]))
+    t = torch.tensor([ms, k1_ms, k1c_ms], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    ms, k1_ms = float(t[0]), float(t[1])
+    ms, k1_ms, k1c_ms = float(t[0]), float(t[1]), float(t[2])
     tot_inside, tot_cells = D.allreduce_counts(int(inside.item()), (step.bs - step.n_cal) * step.interior_cells,
                                                device=device)
     coverage = tot_inside / tot_cells
@@ -351,7 +365,10 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         bpp = 4 * step.nf + 4
-        achieved = bpp * step.points / (k1_ms * 1e-3) / 1e9
+        k1_pts = step.n_cal * step.nt * step.nx * step.ny          # points one K1 STORE launch processes
+        k1c_pts = step.points - k1_pts
+        achieved = bpp * k1_pts / (k1_ms * 1e-3) / 1e9
+        cover_gbs = 4 * step.nf * k1c_pts / (k1c_ms * 1e-3) / 1e9
         cpu = None
         if world == 1 and not args.no_cpu:
             v, desc, secs, threads = cpu_reference_sample(args.workload)
@@ -368,8 +385,11 @@ def main():
                          if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "bytes_per_point": bpp,
-                         "kernel_ms": k1_ms, "kernel_gpoints_s": step.points / (k1_ms * 1e-3) / 1e9,
-                         "share_of_step": k1_ms / ms},
+                         "kernel_ms": k1_ms, "kernel_gpoints_s": k1_pts / (k1_ms * 1e-3) / 1e9,
+                         "points_per_launch": k1_pts, "share_of_step": k1_ms / ms,
+                         "cover_kernel": {"what": "same K1 kernel, COVER epilogue (no residual written), validation half",
+                                          "bytes_per_point": 4 * step.nf, "kernel_ms": k1c_ms, "achieved": cover_gbs,
+                                          "frac": cover_gbs / peak, "share_of_step": k1c_ms / ms}},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
         }))
     if world > 1:

@@ -24,7 +24,7 @@ PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS
                  PROG_MHD_CONTINUITY: 3, PROG_MHD_MOMENTUM: 3, PROG_MHD_ENERGY: 3,
                  PROG_MHD_INDUCTION: 3, PROG_MHD_GAUSS: 3}
 
-EPI_STORE, EPI_SCORE = 0, 1
+EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1
 FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2 = 1, 2, 4, 8
 PATH_AUTO, PATH_GENERIC, PATH_TMA = 0, 1, 2
@@ -45,7 +45,7 @@ class Program(C.Structure):
 
 class Epilogue(C.Structure):
     _fields_ = [("mode", C.c_int32), ("flags", C.c_int32), ("reduce", C.c_int32),
-                ("reserved", C.c_int32), ("d_ref", C.c_void_p), ("ref_stride", C.c_int64 * 4),
+                ("band_q", C.c_float), ("d_ref", C.c_void_p), ("ref_stride", C.c_int64 * 4),
                 ("d_weight", C.c_void_p), ("d_out", C.c_void_p), ("out_stride", C.c_int64 * 4),
                 ("d_scores", C.c_void_p)]
 

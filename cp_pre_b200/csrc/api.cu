@@ -93,8 +93,8 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
                                 fields[f].stride[2], fields[f].stride[3]};
     }
     memcpy(P.scalars, prog->scalars, sizeof(P.scalars));
-    CPPRE_REQUIRE(epi->mode == CPPRE_EPI_STORE || epi->mode == CPPRE_EPI_SCORE, CPPRE_ERR_BAD_ARG,
-                  "unknown epilogue mode %d", epi->mode);
+    CPPRE_REQUIRE(epi->mode == CPPRE_EPI_STORE || epi->mode == CPPRE_EPI_SCORE || epi->mode == CPPRE_EPI_COVER,
+                  CPPRE_ERR_BAD_ARG, "unknown epilogue mode %d", epi->mode);
     P.epi.mode = epi->mode;
     P.epi.flags = epi->flags;
     P.epi.reduce = epi->reduce;
@@ -110,9 +110,13 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
     P.epi.o1 = epi->out_stride[2];
     P.epi.o0 = epi->out_stride[3];
     P.epi.scores = epi->d_scores;
+    P.epi.band_q = epi->band_q;
     const bool empty_out = (int64_t)P.g.B * P.g.O2 * P.g.O1 * P.g.O0 == 0;
     if (epi->mode == CPPRE_EPI_STORE) {
         CPPRE_REQUIRE(epi->d_out != nullptr || empty_out, CPPRE_ERR_BAD_ARG, "STORE epilogue without d_out");
+    } else if (epi->mode == CPPRE_EPI_COVER) {
+        CPPRE_REQUIRE(epi->d_scores != nullptr || P.g.B == 0, CPPRE_ERR_BAD_ARG,
+                      "COVER epilogue without d_scores");
     } else {
         CPPRE_REQUIRE(epi->d_scores != nullptr || P.g.B == 0, CPPRE_ERR_BAD_ARG,
                       "SCORE epilogue without d_scores");
@@ -149,7 +153,7 @@ int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
     int rc = prepare(prog, shape, fields, epi, &P);
     if (rc != CPPRE_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (P.epi.mode == CPPRE_EPI_SCORE && P.g.B > 0) {
+    if (P.epi.mode != CPPRE_EPI_STORE && P.g.B > 0) {
         CPPRE_CHECK_CUDA(cudaMemsetAsync(P.epi.scores, 0, sizeof(float) * (size_t)P.g.B, st));
     }
     if ((int64_t)P.g.B * P.g.O2 * P.g.O1 * P.g.O0 == 0) {  // empty input: nothing to launch

@@ -87,6 +87,7 @@ struct EpiDev {
     float* out;
     int64_t ob, o2, o1, o0;
     float* scores;
+    float band_q;
 };
 
 struct Geometry {
@@ -110,8 +111,20 @@ int program_slots(int kind);
 
 int launch_generic(const Prepared& P, cudaStream_t stream);
 // returns 1 when eligible (and fills nothing), 0 otherwise
-int tma_eligible(const cppre_program_t* prog, const Prepared& P);
-int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+int tma_eligible_store(const cppre_program_t* prog, const Prepared& P);
+int tma_eligible_score(const cppre_program_t* prog, const Prepared& P);
+int tma_eligible_cover(const cppre_program_t* prog, const Prepared& P);
+int launch_tma_store(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+int launch_tma_score(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+int launch_tma_cover(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
+    return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store(prog, P)
+         : P.epi.mode == CPPRE_EPI_SCORE ? tma_eligible_score(prog, P) : tma_eligible_cover(prog, P);
+}
+inline int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
+    return P.epi.mode == CPPRE_EPI_STORE ? launch_tma_store(prog, P, stream)
+         : P.epi.mode == CPPRE_EPI_SCORE ? launch_tma_score(prog, P, stream) : launch_tma_cover(prog, P, stream);
+}
 
 // ---- score reductions ------------------------------------------------------------------
 // Non-negative floats (after |.|) are ordered like their bit patterns, and a NaN (sign

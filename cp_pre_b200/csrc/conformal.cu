@@ -3,6 +3,8 @@
 //
 // Layout: score / residual tensors are [n, cells] with cells contiguous, so "thread = cell,
 // loop over samples" gives fully coalesced 128-byte warp accesses on every row.
+#include <initializer_list>
+
 #include "common.cuh"
 
 namespace cppre {
@@ -10,48 +12,89 @@ namespace {
 
 constexpr int kThreads = 256;
 
+// V consecutive floats per thread: V = 4 (one 128-bit load) when every row is 16-byte aligned,
+// V = 1 otherwise.
+template <int V>
+__device__ __forceinline__ void ldv(const float* p, float (&v)[V]) {
+    if constexpr (V == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+        v[0] = __ldg(p);
+    }
+}
+
+bool vec4_ok(int64_t cells, std::initializer_list<const void*> ptrs, std::initializer_list<int64_t> strides) {
+    if (cells % 4) return false;
+    for (const void* q : ptrs)
+        if (reinterpret_cast<uintptr_t>(q) & 15u) return false;
+    for (int64_t st : strides)
+        if (st % 4) return false;
+    return true;
+}
+
 // ------------------------------------------------------------------------------------------
-// K2: Welford in fp64, one thread per cell
+// K2: shifted-sum moments in fp64, V cells per thread, 4 samples in flight per load stream
 // ------------------------------------------------------------------------------------------
+template <int V>
 __global__ void __launch_bounds__(kThreads)
 cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
                     int64_t n, int64_t cells, double* __restrict__ mean, double* __restrict__ m2) {
-    const int64_t c = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t c = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * V;
     if (c >= cells) return;
     const float* pa = a + c;
     const float* pb = b ? b + c : nullptr;
-    if (n == 0) { mean[c] = 0.0; m2[c] = 0.0; return; }
+    if (n == 0) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) { mean[c + e] = 0.0; m2[c + e] = 0.0; }
+        return;
+    }
     // shifted sums in fp64: d = x - x_0, so sum(d^2) - sum(d)^2/n does not cancel unless the
     // column mean is > 1e6 standard deviations away from its first sample
-    float x0 = __ldg(pa);
-    if (pb) x0 = __fsub_rn(x0, __ldg(pb));
-    const double k = (double)x0;
-    double s1 = 0.0, s2 = 0.0;
+    auto sample = [&](int64_t i, float (&x)[V]) {
+        ldv<V>(pa + i * as, x);
+        if (pb) {
+            float y[V];
+            ldv<V>(pb + i * bs, y);
+#pragma unroll
+            for (int e = 0; e < V; ++e) x[e] = __fsub_rn(x[e], y[e]);
+        }
+    };
+    float x0[V];
+    sample(0, x0);
+    double s1[V], s2[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) { s1[e] = 0.0; s2[e] = 0.0; }
     int64_t i = 0;
-    for (; i + 4 <= n; i += 4) {   // 4 independent loads in flight per thread
-        float x[4];
+    for (; i + 4 <= n; i += 4) {
+        float x[4][V];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            x[u] = __ldg(pa + (i + u) * as);
-            if (pb) x[u] = __fsub_rn(x[u], __ldg(pb + (i + u) * bs));
-        }
+        for (int u = 0; u < 4; ++u) sample(i + u, x[u]);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const double d = (double)x[u] - k;
-            s1 += d;
-            s2 = fma(d, d, s2);
-        }
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const double d = (double)x[u][e] - (double)x0[e];
+                s1[e] += d;
+                s2[e] = fma(d, d, s2[e]);
+            }
     }
     for (; i < n; ++i) {
-        float x = __ldg(pa + i * as);
-        if (pb) x = __fsub_rn(x, __ldg(pb + i * bs));
-        const double d = (double)x - k;
-        s1 += d;
-        s2 = fma(d, d, s2);
+        float x[V];
+        sample(i, x);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const double d = (double)x[e] - (double)x0[e];
+            s1[e] += d;
+            s2[e] = fma(d, d, s2[e]);
+        }
     }
-    mean[c] = k + s1 / (double)n;
-    const double v = s2 - s1 * s1 / (double)n;
-    m2[c] = v > 0.0 ? v : (v == v ? 0.0 : v);   // clamp round-off negatives, keep NaN
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        mean[c + e] = (double)x0[e] + s1[e] / (double)n;
+        const double v = s2[e] - s1[e] * s1[e] / (double)n;
+        m2[c + e] = v > 0.0 ? v : (v == v ? 0.0 : v);   // clamp round-off negatives, keep NaN
+    }
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -64,19 +107,32 @@ cell_std_kernel(const double* __restrict__ m2, double count, float add_eps, int6
     if (inv) inv[c] = __fdiv_rn(1.0f, v);
 }
 
-// scores[i] = max_c |a-b| / mod  -- one block row per sample, grid-stride over cells
+// scores[i] = max_c |a-b| / mod  -- `chunks` blocks per sample, V cells per thread per trip
+template <int V>
 __global__ void __launch_bounds__(kThreads)
 joint_score_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
                    const float* __restrict__ mod, int64_t cells, int32_t chunks, float* scores) {
     const int64_t i = blockIdx.x / chunks;
     const int chunk = blockIdx.x % chunks;
     uint32_t m = 0u;
-    for (int64_t c = (int64_t)chunk * kThreads + threadIdx.x; c < cells; c += (int64_t)chunks * kThreads) {
-        float x = __ldg(a + i * as + c);
-        if (b) x = __fsub_rn(x, __ldg(b + i * bs + c));
-        const float v = __fdiv_rn(fabsf(x), __ldg(mod + c));
-        // |x|/mod is >= 0 or NaN for mod > 0; fabsf clears a sign a negative mod would give
-        m = max(m, score_bits(fabsf(v)));
+    const int64_t step = (int64_t)chunks * kThreads * V;
+#pragma unroll 4
+    for (int64_t c = ((int64_t)chunk * kThreads + threadIdx.x) * V; c < cells; c += step) {
+        float x[V], w[V];
+        ldv<V>(a + i * as + c, x);
+        ldv<V>(mod + c, w);
+        if (b) {
+            float y[V];
+            ldv<V>(b + i * bs + c, y);
+#pragma unroll
+            for (int e = 0; e < V; ++e) x[e] = __fsub_rn(x[e], y[e]);
+        }
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            // |x|/mod is >= 0 or NaN for mod > 0; fabsf clears a sign a negative mod would give
+            const float v = __fdiv_rn(fabsf(x[e]), w[e]);
+            m = max(m, score_bits(fabsf(v)));
+        }
     }
     m = __reduce_max_sync(0xffffffffu, m);
     if ((threadIdx.x & 31) == 0 && m) atomicMax(reinterpret_cast<unsigned int*>(scores) + i, m);
@@ -109,43 +165,53 @@ __device__ __forceinline__ void ce_regs(uint32_t (&k)[R], int a, int b) {
     k[b] = hi;
 }
 
-template <int L, int R>
-__device__ __forceinline__ void bitonic_sort_regs(uint32_t (&k)[R], const int j) {
-    constexpr int N = L * R;
-#pragma unroll
-    for (int size = 2; size <= N; size <<= 1) {
-        // flip step: partner = s ^ (size-1), s = j*R + r
-        if (size <= R) {
+// Levels and strides are template parameters (not unrolled loops) so that every register index
+// is a compile-time constant even in the 64-register variant.
+template <int L, int R, int STRIDE>
+__device__ __forceinline__ void half_cleaners(uint32_t (&k)[R], const int j) {
+    if constexpr (STRIDE > 0) {
+        if constexpr (STRIDE < R) {
 #pragma unroll
             for (int r = 0; r < R; ++r)
-                if ((r & (size >> 1)) == 0) ce_regs<R>(k, r, r ^ (size - 1));
+                if ((r & STRIDE) == 0) ce_regs<R>(k, r, r | STRIDE);
         } else {
-            const int lm = size / R - 1;                     // lane xor mask (all lane bits of the block)
-            const bool lower = (j & (size / R / 2)) == 0;    // this lane holds the lower half
+            constexpr int lm = STRIDE / R;
+            const bool lower = (j & lm) == 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint32_t o = __shfl_xor_sync(0xffffffffu, k[r], lm);
+                k[r] = lower ? min(k[r], o) : max(k[r], o);
+            }
+        }
+        half_cleaners<L, R, STRIDE / 2>(k, j);
+    }
+}
+
+template <int L, int R, int SIZE>
+__device__ __forceinline__ void bitonic_levels(uint32_t (&k)[R], const int j) {
+    if constexpr (SIZE <= L * R) {
+        // flip step: partner = s ^ (SIZE-1), s = j*R + r
+        if constexpr (SIZE <= R) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if ((r & (SIZE >> 1)) == 0) ce_regs<R>(k, r, r ^ (SIZE - 1));
+        } else {
+            constexpr int lm = SIZE / R - 1;                 // lane xor mask (all lane bits of the block)
+            const bool lower = (j & (SIZE / R / 2)) == 0;    // this lane holds the lower half
             uint32_t o[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) o[r] = __shfl_xor_sync(0xffffffffu, k[R - 1 - r], lm);
 #pragma unroll
             for (int r = 0; r < R; ++r) k[r] = lower ? min(k[r], o[r]) : max(k[r], o[r]);
         }
-        // half-cleaners
-#pragma unroll
-        for (int stride = size >> 2; stride > 0; stride >>= 1) {
-            if (stride < R) {
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    if ((r & stride) == 0) ce_regs<R>(k, r, r | stride);
-            } else {
-                const int lm = stride / R;
-                const bool lower = (j & lm) == 0;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const uint32_t o = __shfl_xor_sync(0xffffffffu, k[r], lm);
-                    k[r] = lower ? min(k[r], o) : max(k[r], o);
-                }
-            }
-        }
+        half_cleaners<L, R, SIZE / 4>(k, j);
+        bitonic_levels<L, R, SIZE * 2>(k, j);
     }
+}
+
+template <int L, int R>
+__device__ __forceinline__ void bitonic_sort_regs(uint32_t (&k)[R], const int j) {
+    bitonic_levels<L, R, 2>(k, j);
 }
 
 template <int L, int R, int TC>
@@ -193,20 +259,22 @@ select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_
     uint32_t k[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) k[r] = tile[(r * L + j) * LD + ct];
-    const bool has_nan = nanflag[ct] != 0u;
-
     bitonic_sort_regs<L, R>(k, j);
 
-    const int64_t c = c0 + ct;
-    for (int q = 0; q < ranks.n; ++q) {
-        const int kq = ranks.r[q];
-        const int rq = kq % R;
-        uint32_t v = k[0];
+    // write the sorted columns back (same conflict-free mapping as the read-out), then one
+    // thread per cell picks every requested rank: rank k sits at lane k / R, register k % R
+    __syncthreads();                        // every warp has its column in registers
 #pragma unroll
-        for (int r = 1; r < R; ++r) v = (rq == r) ? k[r] : v;
-        if (kq / R == j && c < cells)
-            out[(int64_t)q * cells + c] = has_nan ? __uint_as_float(0x7fc00000u)
-                                                  : __uint_as_float(key_to_float_bits(v));
+    for (int r = 0; r < R; ++r) tile[(r * L + j) * LD + ct] = k[r];
+    __syncthreads();
+    if (tid < TC && c0 + tid < cells) {
+        const bool has_nan = nanflag[tid] != 0u;
+        for (int q = 0; q < ranks.n; ++q) {
+            const int kq = ranks.r[q];
+            const uint32_t v = tile[((kq % R) * L + kq / R) * LD + tid];
+            out[(int64_t)q * cells + c0 + tid] = has_nan ? __uint_as_float(0x7fc00000u)
+                                                         : __uint_as_float(key_to_float_bits(v));
+        }
     }
 }
 
@@ -301,7 +369,7 @@ radix_hist_kernel(const float* __restrict__ x, int64_t n, uint32_t prefix, uint3
 // ------------------------------------------------------------------------------------------
 // K5: coverage
 // ------------------------------------------------------------------------------------------
-template <bool BAND>
+template <bool BAND, int V>
 __global__ void __launch_bounds__(kThreads)
 inside_kernel(const float* __restrict__ y, int64_t ys, const float* __restrict__ p0, int64_t s0,
               const float* __restrict__ p1, int64_t s1, float q, int64_t cells, int32_t chunks,
@@ -309,28 +377,38 @@ inside_kernel(const float* __restrict__ y, int64_t ys, const float* __restrict__
     const int64_t i = blockIdx.x / chunks;
     const int chunk = blockIdx.x % chunks;
     uint32_t cnt = 0u;
-    for (int64_t c = (int64_t)chunk * kThreads + threadIdx.x; c < cells; c += (int64_t)chunks * kThreads) {
-        const float v = __ldg(y + i * ys + c);
-        float lo, hi;
+    const int64_t step = (int64_t)chunks * kThreads * V;
+#pragma unroll 4
+    for (int64_t c = ((int64_t)chunk * kThreads + threadIdx.x) * V; c < cells; c += step) {
+        float v[V], lo[V], hi[V];
+        ldv<V>(y + i * ys + c, v);
         if (BAND) {   // p0 = centre (or null), p1 = half width (or null); separately rounded ops
-            const float ctr = p0 ? __ldg(p0 + i * s0 + c) : 0.0f;
-            const float h = p1 ? __fmul_rn(q, __ldg(p1 + c)) : q;
-            lo = __fsub_rn(ctr, h);
-            hi = __fadd_rn(ctr, h);
+            float ctr[V], h[V];
+#pragma unroll
+            for (int e = 0; e < V; ++e) { ctr[e] = 0.0f; h[e] = q; }
+            if (p0) ldv<V>(p0 + i * s0 + c, ctr);
+            if (p1) {
+                ldv<V>(p1 + c, h);
+#pragma unroll
+                for (int e = 0; e < V; ++e) h[e] = __fmul_rn(q, h[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < V; ++e) { lo[e] = __fsub_rn(ctr[e], h[e]); hi[e] = __fadd_rn(ctr[e], h[e]); }
         } else {
-            lo = __ldg(p0 + i * s0 + c);
-            hi = __ldg(p1 + i * s1 + c);
+            ldv<V>(p0 + i * s0 + c, lo);
+            ldv<V>(p1 + i * s1 + c, hi);
         }
-        cnt += (v >= lo && v <= hi) ? 1u : 0u;
+#pragma unroll
+        for (int e = 0; e < V; ++e) cnt += (v[e] >= lo[e] && v[e] <= hi[e]) ? 1u : 0u;
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(inside + i, cnt);
 }
 
 int chunks_for(int64_t n, int64_t cells) {
-    // enough blocks to fill the machine a few times, never more than one block per 256 cells
+    // enough blocks to fill the machine a few times, never less than 16 cells per thread
     int64_t want = (148 * 16 + n - 1) / (n > 0 ? n : 1);
-    const int64_t cap = (cells + kThreads - 1) / kThreads;
+    const int64_t cap = (cells + kThreads * 16 - 1) / (kThreads * 16);   // >= 16 cells per thread
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     return (int)want;
@@ -348,9 +426,15 @@ int cppre_cell_moments(const float* d_a, int64_t as, const float* d_b, int64_t b
     CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
     if (cells == 0) return CPPRE_OK;
     CPPRE_REQUIRE(d_mean && d_m2 && (d_a || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
-    const int64_t blocks = (cells + kThreads - 1) / kThreads;
-    cell_moments_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
-                                                                               d_mean, d_m2);
+    if (vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0})) {
+        const int64_t blocks = (cells / 4 + kThreads - 1) / kThreads;
+        cell_moments_kernel<4><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
+                                                                                      d_mean, d_m2);
+    } else {
+        const int64_t blocks = (cells + kThreads - 1) / kThreads;
+        cell_moments_kernel<1><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
+                                                                                      d_mean, d_m2);
+    }
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }
@@ -377,8 +461,12 @@ int cppre_joint_score(const float* d_a, int64_t as, const float* d_b, int64_t bs
     if (cells == 0) return CPPRE_OK;
     const int chunks = chunks_for(n, cells);
     CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    joint_score_kernel<<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
-                                                                   d_scores);
+    if (vec4_ok(cells, {d_a, d_b, d_mod}, {as, d_b ? bs : 0}))
+        joint_score_kernel<4><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
+                                                                          d_scores);
+    else
+        joint_score_kernel<1><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
+                                                                          d_scores);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }
@@ -435,8 +523,12 @@ int cppre_inside_count(const float* d_y, int64_t ys, const float* d_lo, int64_t 
     if (cells == 0) return CPPRE_OK;
     const int chunks = chunks_for(n, cells);
     CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    inside_kernel<false><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_lo, los, d_hi, his, 0.0f, cells,
-                                                                     chunks, d_inside);
+    if (vec4_ok(cells, {d_y, d_lo, d_hi}, {ys, los, his}))
+        inside_kernel<false, 4><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_lo, los, d_hi, his, 0.0f,
+                                                                            cells, chunks, d_inside);
+    else
+        inside_kernel<false, 1><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_lo, los, d_hi, his, 0.0f,
+                                                                            cells, chunks, d_inside);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }
@@ -452,8 +544,12 @@ int cppre_inside_count_band(const float* d_y, int64_t ys, const float* d_centre,
     if (cells == 0) return CPPRE_OK;
     const int chunks = chunks_for(n, cells);
     CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    inside_kernel<true><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_centre, cs, d_half, 0, q, cells,
-                                                                    chunks, d_inside);
+    if (vec4_ok(cells, {d_y, d_centre, d_half}, {ys, d_centre ? cs : 0}))
+        inside_kernel<true, 4><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_centre, cs, d_half, 0, q, cells,
+                                                                           chunks, d_inside);
+    else
+        inside_kernel<true, 1><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_y, ys, d_centre, cs, d_half, 0, q, cells,
+                                                                           chunks, d_inside);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

@@ -67,9 +67,15 @@ generic_kernel(const __grid_constant__ GenericParams p) {
 #pragma unroll
         for (int f = 0; f < Prog<KIND>::NF; ++f) c.base[f] = p.f[f].p + (int64_t)b * p.f[f].sb;
         v = Prog<KIND>::template eval<0>(c, p.scalars);
-        if (p.e.ref) v -= __ldg(p.e.ref + b * p.e.rb + o2 * p.e.r2 + o1 * p.e.r1 + o0 * p.e.r0);
-        if (p.e.flags & CPPRE_FLAG_ABS) v = fabsf(v);
-        if (p.e.weight) v *= __ldg(p.e.weight + cell);
+        const float rf = p.e.ref ? __ldg(p.e.ref + b * p.e.rb + o2 * p.e.r2 + o1 * p.e.r1 + o0 * p.e.r0) : 0.0f;
+        if (p.e.mode == CPPRE_EPI_COVER) {
+            const float h = p.e.weight ? __fmul_rn(p.e.band_q, __ldg(p.e.weight + cell)) : p.e.band_q;
+            v = (v >= __fsub_rn(rf, h) && v <= __fadd_rn(rf, h)) ? 1.0f : 0.0f;
+        } else {
+            if (p.e.ref) v = __fsub_rn(v, rf);
+            if (p.e.flags & CPPRE_FLAG_ABS) v = fabsf(v);
+            if (p.e.weight) v = __fmul_rn(v, __ldg(p.e.weight + cell));
+        }
         if (p.e.mode == CPPRE_EPI_STORE) {
             p.e.out[b * p.e.ob + o2 * p.e.o2 + o1 * p.e.o1 + o0 * p.e.o0] = v;
         } else {
@@ -79,7 +85,10 @@ generic_kernel(const __grid_constant__ GenericParams p) {
             if ((p.e.flags & CPPRE_FLAG_INTERIOR_2) && (o2 == 0 || o2 == p.g.O2 - 1)) counted = false;
         }
     }
-    if (p.e.mode == CPPRE_EPI_SCORE) {
+    if (p.e.mode == CPPRE_EPI_COVER) {
+        const uint32_t cnt = __reduce_add_sync(0xffffffffu, (counted && v != 0.0f) ? 1u : 0u);
+        if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(reinterpret_cast<unsigned int*>(p.e.scores) + b, cnt);
+    } else if (p.e.mode == CPPRE_EPI_SCORE) {
         if (p.e.reduce == CPPRE_REDUCE_MAX) {
             uint32_t m = counted ? score_bits(v) : 0u;
             m = __reduce_max_sync(0xffffffffu, m);

@@ -20,6 +20,10 @@
 // (1/modulation), then either a 128-bit coalesced store or a per-sample max/sum kept in
 // registers, reduced with redux.sync / shuffles and one atomic per warp -- the Joint score
 // never materialises the residual tensor.
+//
+// This file is the body of three translation units (stencil_tma_store.cu / _score.cu /
+// _cover.cu): each defines CPPRE_TMA_MODE (the epilogue mode, a compile-time constant of the
+// kernel) and CPPRE_TMA_SUFFIX (the suffix of the two functions exported to api.cu).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -128,10 +132,13 @@ struct StarCtx {
     }
 };
 
-template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS>
+template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS, int MODE>
 __global__ void __launch_bounds__(kThreads)
 star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int NF = Prog<KIND>::NF;
+    constexpr bool STORE = MODE == CPPRE_EPI_STORE;
+    constexpr bool SCORE = MODE == CPPRE_EPI_SCORE;
+    constexpr bool COVER = MODE == CPPRE_EPI_COVER;
     constexpr int TX = kWarps * RX;               // rows per tile
     constexpr int HALO = BATCH_ROWS ? 0 : 1;      // row halo only when rows are a stencil axis
     constexpr int SR = TX + 2 * HALO;             // smem rows per tile
@@ -213,37 +220,55 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
 
     const int y = col0 + 4 * tc;                   // first column of this thread
     const bool col_live = y < p.N0;                // N0 % 4 == 0: a float4 is all in or all out
-    const bool score = p.e.mode == CPPRE_EPI_SCORE;
     const bool rmax = p.e.reduce == CPPRE_REDUCE_MAX;
     const bool in0 = (p.e.flags & CPPRE_FLAG_INTERIOR_0) != 0;
     const bool in1 = (p.e.flags & CPPRE_FLAG_INTERIOR_1) != 0;
     const bool in2 = (p.e.flags & CPPRE_FLAG_INTERIOR_2) != 0;
-    const bool do_abs = (p.e.flags & CPPRE_FLAG_ABS) != 0;
-    // SCORE mode: which of the four columns count (y == 0 / y == N0-1 dropped by INTERIOR_0)
-    const bool skip_first = score && in0 && y == 0;
-    const bool skip_last = score && in0 && y + 3 == p.N0 - 1;
-    uint32_t acc_max[RX];
-    float acc_sum[RX];
+    // |.| as a bit mask: one LOP3 per value, no branch
+    const uint32_t abs_mask = (p.e.flags & CPPRE_FLAG_ABS) ? 0x7fffffffu : 0xffffffffu;
+    // reducing modes: which of the four columns count (y == 0 / y == N0-1 dropped by INTERIOR_0)
+    const bool skip_first = !STORE && in0 && y == 0;
+    const bool skip_last = !STORE && in0 && y + 3 == p.N0 - 1;
+    uint32_t acc_u[RX];                            // SCORE/max: running max of the bit images; COVER: count
+    float acc_f[RX];                               // SCORE/sum
 #pragma unroll
-    for (int j = 0; j < RX; ++j) { acc_max[j] = 0u; acc_sum[j] = 0.0f; }
-
-    const StarCtx<NF, RX, MASKS> ctx{p.coef, prev, cur, next, xm, xp, ym, yp};
+    for (int j = 0; j < RX; ++j) { acc_u[j] = 0u; acc_f[j] = 0.0f; }
+    const bool has_ref = p.e.ref != nullptr, has_w = p.e.weight != nullptr;
 
     int stage = 0;
     int nstage = p.stages > 1 ? 1 : 0;
     uint32_t nphase = p.stages > 1 ? 0u : 1u;      // parity of the barrier guarding plane t+1
-    uint32_t phase = 0;
-    for (int t = 0; t < NPL; ++t) {
+
+    // One time step.  (P, C, N) are the register planes holding t-1, t, t+1; the caller rotates
+    // the three arrays by NAME (the loop below is unrolled by three), so no register is moved.
+    auto step = [&](const int t, float (&P)[NF][RX][4], float (&C)[NF][RX][4], float (&N)[NF][RX][4]) {
+        // epilogue operands first: their L2 latency overlaps the barrier wait and the stencil math
+        float4 rq[RX], wq[RX];
+#pragma unroll
+        for (int j = 0; j < RX; ++j) {
+            rq[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            wq[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+            const int row = row0 + tr * RX + j;
+            if (col_live && row < p.R) {
+                const int b = BATCH_ROWS ? row : outer;
+                const int x = BATCH_ROWS ? 0 : row;
+                if (has_ref)
+                    rq[j] = __ldg(reinterpret_cast<const float4*>(
+                        p.e.ref + (int64_t)b * p.e.rb + (int64_t)t * p.e.r2 + (int64_t)x * p.e.r1 + y));
+                if (has_w)
+                    wq[j] = __ldg(reinterpret_cast<const float4*>(p.e.weight + ((int64_t)t * p.N1 + x) * p.N0 + y));
+            }
+        }
         if (t + 1 < NPL) {
             mbar_wait(bars + 8u * nstage, nphase);
-            load_centres(next, nstage);
+            load_centres(N, nstage);
         } else {
 #pragma unroll
             for (int f = 0; f < NF; ++f)
 #pragma unroll
                 for (int j = 0; j < RX; ++j)
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) next[f][j][i] = 0.0f;
+                    for (int i = 0; i < 4; ++i) N[f][j][i] = 0.0f;
         }
         // x+-1 rows and y+-1 edge cells of plane t
 #pragma unroll
@@ -264,8 +289,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 yp[f][j] = tl[j * kTWP + 4];
             }
         }
+        const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
 
-        const bool plane_live = !(score && in2 && (t == 0 || t == NPL - 1));
+        const bool plane_live = STORE || !(in2 && (t == 0 || t == NPL - 1));
         if (plane_live && col_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
@@ -278,35 +304,43 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                     r[1] = Prog<KIND>::template eval<4 * j + 1>(ctx, p.scalars);
                     r[2] = Prog<KIND>::template eval<4 * j + 2>(ctx, p.scalars);
                     r[3] = Prog<KIND>::template eval<4 * j + 3>(ctx, p.scalars);
-                    if (p.e.ref) {
-                        const float4 q = __ldg(reinterpret_cast<const float4*>(
-                            p.e.ref + (int64_t)b * p.e.rb + (int64_t)t * p.e.r2 + (int64_t)x * p.e.r1 + y));
-                        r[0] -= q.x; r[1] -= q.y; r[2] -= q.z; r[3] -= q.w;
-                    }
-                    if (do_abs) {
+                    const float rr[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
+                    const float ww[4] = {wq[j].x, wq[j].y, wq[j].z, wq[j].w};
+                    if constexpr (COVER) {
+                        // lo = c - q*h, hi = c + q*h with NumPy's separately rounded fp32 ops
+                        const bool row_in = !(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1));
+                        uint32_t cnt = 0u;
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) r[i] = fabsf(r[i]);
-                    }
-                    if (p.e.weight) {
-                        const float4 w = __ldg(reinterpret_cast<const float4*>(
-                            p.e.weight + ((int64_t)t * p.N1 + x) * p.N0 + y));
-                        r[0] *= w.x; r[1] *= w.y; r[2] *= w.z; r[3] *= w.w;
-                    }
-                    if (!score) {
-                        float4 o = make_float4(r[0], r[1], r[2], r[3]);
-                        *reinterpret_cast<float4*>(p.e.out + (int64_t)b * p.e.ob + (int64_t)t * p.e.o2 +
-                                                   (int64_t)x * p.e.o1 + y) = o;
-                    } else if (!(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1))) {
-                        if (rmax) {
-                            uint32_t m = max(score_bits(r[1]), score_bits(r[2]));
-                            if (!skip_first) m = max(m, score_bits(r[0]));
-                            if (!skip_last) m = max(m, score_bits(r[3]));
-                            acc_max[j] = max(acc_max[j], m);
-                        } else {
-                            float s = r[1] + r[2];
-                            if (!skip_first) s += r[0];
-                            if (!skip_last) s += r[3];
-                            acc_sum[j] += s;
+                        for (int i = 0; i < 4; ++i) {
+                            const float h = has_w ? __fmul_rn(p.e.band_q, ww[i]) : p.e.band_q;
+                            const float lo = __fsub_rn(rr[i], h), hi = __fadd_rn(rr[i], h);
+                            const bool in = r[i] >= lo && r[i] <= hi;
+                            const bool counted = !((i == 0 && skip_first) || (i == 3 && skip_last));
+                            cnt += (in && counted) ? 1u : 0u;
+                        }
+                        acc_u[j] += row_in ? cnt : 0u;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            float v = has_ref ? __fsub_rn(r[i], rr[i]) : r[i];
+                            v = __uint_as_float(__float_as_uint(v) & abs_mask);
+                            r[i] = has_w ? __fmul_rn(v, ww[i]) : v;
+                        }
+                        if constexpr (STORE) {
+                            *reinterpret_cast<float4*>(p.e.out + (int64_t)b * p.e.ob + (int64_t)t * p.e.o2 +
+                                                       (int64_t)x * p.e.o1 + y) = make_float4(r[0], r[1], r[2], r[3]);
+                        } else if (!(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1))) {
+                            if (rmax) {
+                                uint32_t m = max(score_bits(r[1]), score_bits(r[2]));
+                                if (!skip_first) m = max(m, score_bits(r[0]));
+                                if (!skip_last) m = max(m, score_bits(r[3]));
+                                acc_u[j] = max(acc_u[j], m);
+                            } else {
+                                float s = r[1] + r[2];
+                                if (!skip_first) s += r[0];
+                                if (!skip_last) s += r[3];
+                                acc_f[j] += s;
+                            }
                         }
                     }
                 }
@@ -314,30 +348,30 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         }
         __syncthreads();                            // every warp is done reading ring slot `stage`
         if (tid == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
-        // rotate the register pipeline and the ring cursors
-#pragma unroll
-        for (int f = 0; f < NF; ++f)
-#pragma unroll
-            for (int j = 0; j < RX; ++j)
-#pragma unroll
-                for (int i = 0; i < 4; ++i) { prev[f][j][i] = cur[f][j][i]; cur[f][j][i] = next[f][j][i]; }
         stage = nstage;
-        phase = nphase;
         if (++nstage == p.stages) { nstage = 0; nphase ^= 1u; }
-    }
-    (void)phase;
+    };
 
-    if (score) {
+    for (int t = 0; t < NPL; t += 3) {
+        step(t, prev, cur, next);
+        if (t + 1 < NPL) step(t + 1, cur, next, prev);
+        if (t + 2 < NPL) step(t + 2, next, prev, cur);
+    }
+
+    if constexpr (!STORE) {
         static_for<RX>([&](auto J) {
             constexpr int j = decltype(J)::value;
             const int row = row0 + tr * RX + j;
             const int b = BATCH_ROWS ? row : outer;
             const bool ok = row < p.R;               // warp-uniform (one warp per tile row)
-            if (rmax) {
-                const uint32_t m = __reduce_max_sync(0xffffffffu, acc_max[j]);
+            if constexpr (COVER) {
+                const uint32_t c = __reduce_add_sync(0xffffffffu, acc_u[j]);
+                if (tc == 0 && ok && c) atomicAdd(reinterpret_cast<unsigned int*>(p.e.scores) + b, c);
+            } else if (rmax) {
+                const uint32_t m = __reduce_max_sync(0xffffffffu, acc_u[j]);
                 if (tc == 0 && ok && m) atomicMax(reinterpret_cast<unsigned int*>(p.e.scores) + b, m);
             } else {
-                float s = acc_sum[j];
+                float s = acc_f[j];
 #pragma unroll
                 for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
                 if (tc == 0 && ok) atomicAdd(p.e.scores + b, s);
@@ -418,7 +452,7 @@ bool layout_ok(const Prepared& P, bool batch_rows) {
             return false;
     }
     const EpiDev& e = P.epi;
-    if (e.mode == CPPRE_EPI_STORE) {
+    if (CPPRE_TMA_MODE == CPPRE_EPI_STORE) {
         if (!aligned16(e.out) || e.o0 != 1) return false;
         if ((g.N1 > 1 && e.o1 % 4) || (g.N2 > 1 && e.o2 % 4) || (g.B > 1 && e.ob % 4)) return false;
     }
@@ -497,7 +531,7 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     const size_t smem = stages * per_stage + 8 * kMaxStages + 128;
     CPPRE_REQUIRE(smem <= 227 * 1024, CPPRE_ERR_UNSUPPORTED, "tile ring of %zu bytes exceeds shared memory", smem);
 
-    auto kern = star_kernel<KIND, BR, RX, MASKS>;
+    auto kern = star_kernel<KIND, BR, RX, MASKS, CPPRE_TMA_MODE>;
     static size_t configured = 0;   // per instantiation
     if (smem > configured) {
         CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -580,7 +614,7 @@ const Variant* pick(int kind, const StarHost& H, const Geometry& g) {
     int want = preferred_rx();
     if (want <= 0) {
         const int R = H.batch_rows ? g.B : g.N1;
-        want = R >= 16 ? 2 : 1;
+        want = (R >= 16 && (CPPRE_TMA_MODE == CPPRE_EPI_STORE || H.batch_rows)) ? 2 : 1;
     }
     for (const Variant& v : kVariants) {
         if (v.kind != kind || v.batch_rows != H.batch_rows) continue;
@@ -594,7 +628,10 @@ const Variant* pick(int kind, const StarHost& H, const Geometry& g) {
 
 }  // namespace
 
-int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
+#define CPPRE_CAT_(a, b) a##b
+#define CPPRE_CAT(a, b) CPPRE_CAT_(a, b)
+
+int CPPRE_CAT(tma_eligible_, CPPRE_TMA_SUFFIX)(const cppre_program_t* prog, const Prepared& P) {
     StarHost H;
     if (!classify(prog, P, &H)) return 0;
     if (!layout_ok(P, H.batch_rows)) return 0;
@@ -602,7 +639,7 @@ int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
     return pick(P.kind, H, P.g) != nullptr;
 }
 
-int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t st) {
+int CPPRE_CAT(launch_tma_, CPPRE_TMA_SUFFIX)(const cppre_program_t* prog, const Prepared& P, cudaStream_t st) {
     StarHost H;
     CPPRE_REQUIRE(classify(prog, P, &H) && layout_ok(P, H.batch_rows), CPPRE_ERR_UNSUPPORTED,
                   "request does not qualify for the TMA star kernel");

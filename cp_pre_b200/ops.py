@@ -92,13 +92,14 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
                 ref: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None,
                 path: int = L.PATH_AUTO, canonicalise: bool = True,
-                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, band_q: float = 0.0) -> torch.Tensor:
     """Runs one fused residual program.
 
     fields   CUDA fp32 tensors, all of logical shape [B, N2, N1, N0], any strides (views welcome)
     kernels  one dense fp32 ndarray [k2, k1, k0] per derivative slot (cross-correlation taps)
     pads     per-slot zero padding (p2, p1, p0)
-    Returns the [B, O2, O1, O0] field (STORE) or the [B] scores (SCORE).
+    Returns the [B, O2, O1, O0] field (STORE), the [B] fp32 scores (SCORE) or the [B] int32
+    counts of cells with ref - band_q*weight <= residual <= ref + band_q*weight (COVER).
     """
     lib = L.load()
     require_cuda()
@@ -157,7 +158,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         for d in range(4):
             fl[i].stride[d] = f.stride(d)
     epi = L.Epilogue()
-    epi.mode, epi.flags, epi.reduce = mode, flags, reduce
+    epi.mode, epi.flags, epi.reduce, epi.band_q = mode, flags, reduce, float(band_q)
     dev = f0.device
     keep = []
     if ref is not None:
@@ -186,7 +187,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
             for d in range(4):
                 epi.out_stride[d] = out.stride(d)
         else:
-            out = torch.empty((B,), dtype=torch.float32, device=dev)
+            out = torch.empty((B,), dtype=torch.float32 if mode == L.EPI_SCORE else torch.int32, device=dev)
             epi.d_scores = out.data_ptr() if B else 0
         shape = (C.c_int64 * 4)(B, N2, N1, N0)
         L.check(lib.cppre_residual(C.byref(prog), shape, fl, C.byref(epi), int(path), _stream(dev)))

@@ -106,6 +106,29 @@ class ResidualProgram:
         return staged.back(out)
 
 
+    def coverage_counts(self, vars_, q, half=None, centre=None, interior=True):
+        """Per-sample number of cells with centre - q*half <= residual(vars) <= centre + q*half,
+        int32 [BS]; neither the residual of ``vars_`` nor the prediction sets are written.
+        ``half`` ([Nt,Nx(,Ny)], e.g. qhat per cell with q=1, or the modulation with q=qhat) and
+        ``centre`` ([BS,Nt,...], e.g. the predicted residual) are FULL-size; None = 1 / 0.
+        With ``interior`` the shell cells the reference crops are not counted
+        [ref: Marginal/NS_Residuals_CP.py:311-312,336-337; Joint/NS_Residuals_CP.py:312,336]."""
+        staged = ops.Staged(vars_)
+        w = None if half is None else self._unsq(ops.to_cuda(half))
+        r = None if centre is None else self._unsq(ops.to_cuda(centre))
+        out = self._run(vars_, mode=L.EPI_COVER, flags=self._interior_flags() if interior else 0,
+                        weight=w, ref=r, band_q=float(q))
+        return staged.back(out)
+
+    def interior_cells(self, vars_shape):
+        """Number of cells the ``interior`` crop keeps for an input of this shape."""
+        dims = vars_shape[-3:] if self.nd == 3 else vars_shape[-2:]
+        n = 1
+        for d in dims:
+            n *= max(int(d) - 2, 0)
+        return n
+
+
 # ---------------------------------------------------------------------------------------
 # factories (argument meaning = the variables of the reference scripts)
 # ---------------------------------------------------------------------------------------

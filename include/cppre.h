@@ -98,9 +98,18 @@ typedef struct cppre_program {
  *   SCORE: scores[b] = reduce_cells(v)          replaces ncf_metric_joint (max of |a-b|/mod)
  *                                               Joint/NS_Residuals_CP.py:306 and the residual
  *                                               tensor it consumed
- * INTERIOR_d excludes index 0 and N_d-1 of axis d from SCORE reductions (the reference's
+ *   COVER: counts[b] = #{cell : c - q*h <= r <= c + q*h}  (uint32, written through d_scores)
+ *          with c = ref[b,cell] (0 if no d_ref), h = weight[cell] (1 if no d_weight), q = band_q;
+ *          r is the raw residual (FLAG_ABS ignored); lo/hi are evaluated with separately
+ *          rounded fp32 multiply / subtract / add, exactly as NumPy evaluates
+ *          [pred_res - qhat*modulation, pred_res + qhat*modulation].  The prediction sets and the
+ *          residual tensor of the validation samples are never materialised.
+ *                                               replaces residual + sets + emp_cov / emp_cov_joint /
+ *                                               filter_sims_joint  Joint/NS_Residuals_CP.py:312,336,
+ *                                               Marginal/NS_Residuals_CP.py:311-312,336-337
+ * INTERIOR_d excludes index 0 and N_d-1 of axis d from SCORE / COVER reductions (the reference's
  * [...,1:-1,1:-1,1:-1] crop, Joint/Wave_Residuals_CP.py:184).  */
-enum { CPPRE_EPI_STORE = 0, CPPRE_EPI_SCORE = 1 };
+enum { CPPRE_EPI_STORE = 0, CPPRE_EPI_SCORE = 1, CPPRE_EPI_COVER = 2 };
 enum { CPPRE_REDUCE_MAX = 0, CPPRE_REDUCE_SUM = 1 };
 enum {
     CPPRE_FLAG_ABS = 1,
@@ -116,13 +125,13 @@ typedef struct cppre_epilogue {
     int32_t mode;   /* CPPRE_EPI_* */
     int32_t flags;  /* CPPRE_FLAG_* */
     int32_t reduce; /* CPPRE_REDUCE_* (SCORE only) */
-    int32_t reserved;
+    float band_q;   /* COVER: q */
     const float* d_ref;    /* optional [B, O2, O1, O0] with ref_stride, or NULL */
     int64_t ref_stride[4];
     const float* d_weight; /* optional contiguous [O2, O1, O0], or NULL */
     float* d_out;          /* STORE: [B, O2, O1, O0] with out_stride */
     int64_t out_stride[4];
-    float* d_scores;       /* SCORE: [B] contiguous, overwritten */
+    float* d_scores;       /* SCORE: [B] fp32 / COVER: [B] uint32; contiguous, overwritten */
 } cppre_epilogue_t;
 
 /* ---- library state -------------------------------------------------------------------- */

@@ -227,6 +227,56 @@ def test_fused_joint_score_epilogue(path, shape):
     assert np.isnan(s[1]) and not np.isnan(np.delete(s, 1)).any()
 
 
+@pytest.mark.parametrize("path", [L.PATH_GENERIC, L.PATH_TMA])
+def test_fused_coverage_epilogue_counts_are_exact(path):
+    """COVER epilogue: per-sample count of cells with c - q*h <= R(vars) <= c + q*h, the sets and
+    the residual never written.  Given the kernel's own residual (STORE epilogue, same arithmetic)
+    the counts equal NumPy's evaluation of the reference expressions bit for bit
+    [ref: Joint/NS_Residuals_CP.py:312,336; Marginal/NS_Residuals_CP.py:311-312]."""
+    o, n = _programs_2d(), synth.NS
+    shape = (10, 7, 24, 132)
+    v = synth.fields(51, 3, shape)
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    prog.path = path
+    res = prog.residual(cuda(v), boundary=True).cpu().numpy()
+    assert_close_rel(res, O.residual_ns_momentum(v[:, 0], v[:, 1], v[:, 2], n["dx"], n["dy"], n["dt"], n["nu"],
+                                                 O.ops_2d()), TOL, "residual")
+    rng = np.random.default_rng(3)
+    inner = (slice(None), slice(1, -1), slice(1, -1), slice(1, -1))
+    scale = np.float32(np.abs(res[inner]).std())
+    half = (scale * rng.uniform(0.2, 2.0, shape[1:])).astype(np.float32)
+    centre = (res + scale * rng.standard_normal(res.shape)).astype(np.float32)
+    q = np.float32(0.83)
+    for use_c in (False, True):
+        for use_h in (False, True):
+            c = centre if use_c else np.zeros_like(res)
+            hh = (q * half).astype(np.float32) if use_h else np.full(half.shape, q, np.float32)
+            lo, hi = (c - hh).astype(np.float32), (c + hh).astype(np.float32)
+            ins = (res >= lo) & (res <= hi)
+            got = prog.coverage_counts(cuda(v), float(q), cuda(half) if use_h else None, cuda(centre) if use_c else None)
+            assert got.dtype == torch.int32 and got.shape == (shape[0],)
+            np.testing.assert_array_equal(got.cpu().numpy(), ins[inner].sum(axis=(1, 2, 3)), f"c={use_c} h={use_h}")
+            got = prog.coverage_counts(cuda(v), float(q), cuda(half) if use_h else None, cuda(centre) if use_c else None,
+                                       interior=False)
+            np.testing.assert_array_equal(got.cpu().numpy(), ins.sum(axis=(1, 2, 3)))
+    assert prog.interior_cells(v.shape) == 5 * 22 * 130
+    # marginal data-free form: emp_cov([-qhat, qhat], res) with a per-cell qhat, q = 1
+    qhat = half
+    got = prog.coverage_counts(cuda(v), 1.0, cuda(qhat)).cpu().numpy()
+    np.testing.assert_array_equal(got, ((res >= -qhat) & (res <= qhat))[inner].sum(axis=(1, 2, 3)))
+    # 1-D + time (batch-rows tiles)
+    m1 = _mods()["1d"]
+    cb = synth.BURGERS
+    u = synth.fields(52, 1, (37, 12, 260))[:, 0]
+    pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                          cb["dx"], cb["dt"], cb["nu"])
+    pb.path = path
+    rb = pb.residual(cuda(u), boundary=True).cpu().numpy()
+    hb = (np.abs(rb).mean() * rng.uniform(0.5, 2.0, rb.shape[1:])).astype(np.float32)
+    got = pb.coverage_counts(cuda(u), 1.0, cuda(hb)).cpu().numpy()
+    np.testing.assert_array_equal(got, ((rb >= -hb) & (rb <= hb))[:, 1:-1, 1:-1].sum(axis=(1, 2)))
+
+
 def test_fused_score_1d_batch_rows_mode():
     m1 = _mods()["1d"]
     c = synth.BURGERS
