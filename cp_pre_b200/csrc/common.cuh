@@ -110,20 +110,30 @@ int program_fields(int kind);
 int program_slots(int kind);
 
 int launch_generic(const Prepared& P, cudaStream_t stream);
-// returns 1 when eligible (and fills nothing), 0 otherwise
-int tma_eligible_store(const cppre_program_t* prog, const Prepared& P);
-int tma_eligible_score(const cppre_program_t* prog, const Prepared& P);
-int tma_eligible_cover(const cppre_program_t* prog, const Prepared& P);
-int launch_tma_store(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
-int launch_tma_score(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
-int launch_tma_cover(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+// returns 1 when eligible (and fills nothing), 0 otherwise.  One translation unit per
+// (epilogue mode, compiled-in operand set); "dyn" handles any operand combination.
+#define CPPRE_TMA_TU(sfx)                                                   \
+    int tma_eligible_##sfx(const cppre_program_t* prog, const Prepared& P); \
+    int launch_tma_##sfx(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+CPPRE_TMA_TU(store_dyn) CPPRE_TMA_TU(store_plain)
+CPPRE_TMA_TU(score_dyn) CPPRE_TMA_TU(score_plain) CPPRE_TMA_TU(score_w)
+CPPRE_TMA_TU(cover_dyn) CPPRE_TMA_TU(cover_w)
+#undef CPPRE_TMA_TU
 inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
-    return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store(prog, P)
-         : P.epi.mode == CPPRE_EPI_SCORE ? tma_eligible_score(prog, P) : tma_eligible_cover(prog, P);
+    return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store_dyn(prog, P)
+         : P.epi.mode == CPPRE_EPI_SCORE ? tma_eligible_score_dyn(prog, P) : tma_eligible_cover_dyn(prog, P);
 }
 inline int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
-    return P.epi.mode == CPPRE_EPI_STORE ? launch_tma_store(prog, P, stream)
-         : P.epi.mode == CPPRE_EPI_SCORE ? launch_tma_score(prog, P, stream) : launch_tma_cover(prog, P, stream);
+    const int oper = (P.epi.ref ? 1 : 0) | (P.epi.weight ? 2 : 0);
+    switch (P.epi.mode) {
+        case CPPRE_EPI_STORE:
+            return oper == 0 ? launch_tma_store_plain(prog, P, stream) : launch_tma_store_dyn(prog, P, stream);
+        case CPPRE_EPI_SCORE:
+            return oper == 0 ? launch_tma_score_plain(prog, P, stream)
+                 : oper == 2 ? launch_tma_score_w(prog, P, stream) : launch_tma_score_dyn(prog, P, stream);
+        default:
+            return oper == 2 ? launch_tma_cover_w(prog, P, stream) : launch_tma_cover_dyn(prog, P, stream);
+    }
 }
 
 // ---- score reductions ------------------------------------------------------------------

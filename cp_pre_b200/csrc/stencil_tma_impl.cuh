@@ -21,9 +21,10 @@
 // registers, reduced with redux.sync / shuffles and one atomic per warp -- the Joint score
 // never materialises the residual tensor.
 //
-// This file is the body of three translation units (stencil_tma_store.cu / _score.cu /
-// _cover.cu): each defines CPPRE_TMA_MODE (the epilogue mode, a compile-time constant of the
-// kernel) and CPPRE_TMA_SUFFIX (the suffix of the two functions exported to api.cu).
+// This file is the body of several translation units (stencil_tma_<mode>_<oper>.cu): each
+// defines CPPRE_TMA_MODE (the epilogue mode), CPPRE_TMA_OPER (which optional epilogue operands
+// exist: -1 = decided at run time, else bit 0 = ref, bit 1 = weight, compiled in) and
+// CPPRE_TMA_SUFFIX (the suffix of the two functions exported to api.cu).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -132,7 +133,21 @@ struct StarCtx {
     }
 };
 
-template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS, int MODE>
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float lds32(uint32_t a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+
+// OPER: which optional epilogue operands exist, known at compile time (bit 0 = ref, bit 1 =
+// weight) or -1 = decided at run time (any combination; a few predicated instructions more).
+template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS, int MODE, int OPER>
 __global__ void __launch_bounds__(kThreads)
 star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int NF = Prog<KIND>::NF;
@@ -143,12 +158,16 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int HALO = BATCH_ROWS ? 0 : 1;      // row halo only when rows are a stencil axis
     constexpr int SR = TX + 2 * HALO;             // smem rows per tile
     constexpr uint32_t BOX_BYTES = (uint32_t)(SR * kTWP * sizeof(float));
+    constexpr uint32_t BUF_BYTES = (BOX_BYTES + 127u) & ~127u;   // one (stage, field) tile
+    constexpr uint32_t STAGE_BYTES = NF * BUF_BYTES;
+    constexpr uint32_t ROW_BYTES = kTWP * sizeof(float);
+    (void)SCORE;
 
+    // Shared memory is addressed by 32-bit shared-window addresses only (ld.shared / TMA /
+    // mbarrier), so no generic-address arithmetic is left in the time loop.
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t raw = smem_u32(smem_raw);
-    const uint32_t base = (raw + 127u) & ~127u;   // TMA destinations must be 128-byte aligned
-    uint8_t* const sm = smem_raw + (base - raw);
-    const uint32_t bars = base + (uint32_t)p.stages * NF * p.buf_bytes;  // mbarriers follow the ring
+    const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;   // TMA destinations: 128-byte aligned
+    const uint32_t bars = base + (uint32_t)p.stages * STAGE_BYTES;  // mbarriers follow the ring
 
     const int tid = threadIdx.x;
     const int tc = tid & (kTPR - 1);
@@ -177,7 +196,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         mbar_expect_tx(bar, BOX_BYTES * NF);
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
-            const uint32_t dst = base + (uint32_t)(stage * NF + f) * p.buf_bytes;
+            const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * BUF_BYTES;
             if constexpr (BATCH_ROWS)   // map dims (N0, N2, B, 1): tile rows are samples
                 tma_load_4d(dst, &p.map[f], bar, col0 - 4, plane, row0, 0);
             else                        // map dims (N0, N1, N2, B)
@@ -198,25 +217,20 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) prev[f][j][i] = 0.0f;
 
-    // word offset of this thread's first centre cell inside a tile
-    const int cell_off = (HALO + tr * RX) * kTWP + 4 + 4 * tc;
-    auto tile = [&](int stage, int f) -> const float* {
-        return reinterpret_cast<const float*>(sm + (size_t)(stage * NF + f) * p.buf_bytes);
-    };
-    auto load_centres = [&](float (&dst)[NF][RX][4], int stage) {
+    // shared address of this thread's first centre cell in ring slot 0
+    const uint32_t cell0 = base + (uint32_t)(((HALO + tr * RX) * kTWP + 4 + 4 * tc) * sizeof(float));
+    auto load_centres = [&](float (&dst)[NF][RX][4], uint32_t a) {
 #pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            const float* t = tile(stage, f) + cell_off;
+        for (int f = 0; f < NF; ++f)
 #pragma unroll
             for (int j = 0; j < RX; ++j) {
-                const float4 v = *reinterpret_cast<const float4*>(t + j * kTWP);
+                const float4 v = lds128(a + f * BUF_BYTES + j * ROW_BYTES);
                 dst[f][j][0] = v.x; dst[f][j][1] = v.y; dst[f][j][2] = v.z; dst[f][j][3] = v.w;
             }
-        }
     };
 
     mbar_wait(bars, 0);
-    load_centres(cur, 0);
+    load_centres(cur, cell0);
 
     const int y = col0 + 4 * tc;                   // first column of this thread
     const bool col_live = y < p.N0;                // N0 % 4 == 0: a float4 is all in or all out
@@ -229,15 +243,45 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     // reducing modes: which of the four columns count (y == 0 / y == N0-1 dropped by INTERIOR_0)
     const bool skip_first = !STORE && in0 && y == 0;
     const bool skip_last = !STORE && in0 && y + 3 == p.N0 - 1;
+    const bool has_ref = OPER < 0 ? (p.e.ref != nullptr) : ((OPER & 1) != 0);
+    const bool has_w = OPER < 0 ? (p.e.weight != nullptr) : ((OPER & 2) != 0);
+
+    // Per-thread row state, fixed over the time loop: which of the RX rows exist (live) and
+    // which of them count in a reduction (cnt: not on the x-shell when INTERIOR_1 is set).
+    // Epilogue operands are walked with one pointer each, advanced by the plane stride.
+    const int row_first = row0 + tr * RX;
+    uint32_t live = 0u, cnt_rows = 0u;
+#pragma unroll
+    for (int j = 0; j < RX; ++j) {
+        const int row = row_first + j;
+        if (col_live && row < p.R) {
+            live |= 1u << j;
+            if (!(in1 && !BATCH_ROWS && (row == 0 || row == p.N1 - 1))) cnt_rows |= 1u << j;
+        }
+    }
+    const int b0 = BATCH_ROWS ? row_first : outer;
+    const int x0 = BATCH_ROWS ? 0 : row_first;
+    const int64_t ref_row = BATCH_ROWS ? p.e.rb : p.e.r1;
+    const int64_t out_row = BATCH_ROWS ? p.e.ob : p.e.o1;
+    const int64_t w_row = BATCH_ROWS ? 0 : p.N0;
+    const int64_t w_plane = (int64_t)p.N1 * p.N0;
+    const float* refp = has_ref ? p.e.ref + (int64_t)b0 * p.e.rb + (int64_t)x0 * p.e.r1 + y : nullptr;
+    const float* wp = has_w ? p.e.weight + (int64_t)x0 * p.N0 + y : nullptr;
+    float* outp = STORE ? p.e.out + (int64_t)b0 * p.e.ob + (int64_t)x0 * p.e.o1 + y : nullptr;
+
     uint32_t acc_u[RX];                            // SCORE/max: running max of the bit images; COVER: count
     float acc_f[RX];                               // SCORE/sum
 #pragma unroll
     for (int j = 0; j < RX; ++j) { acc_u[j] = 0u; acc_f[j] = 0.0f; }
-    const bool has_ref = p.e.ref != nullptr, has_w = p.e.weight != nullptr;
 
+    // ring state: slot index (for the producer), shared addresses of this thread's cell in the
+    // slots holding planes t and t+1, barrier address and parity guarding plane t+1
     int stage = 0;
     int nstage = p.stages > 1 ? 1 : 0;
-    uint32_t nphase = p.stages > 1 ? 0u : 1u;      // parity of the barrier guarding plane t+1
+    uint32_t cur_a = cell0;
+    uint32_t nxt_a = cell0 + (p.stages > 1 ? STAGE_BYTES : 0u);
+    uint32_t nbar = bars + (p.stages > 1 ? 8u : 0u);
+    uint32_t nphase = p.stages > 1 ? 0u : 1u;
 
     // One time step.  (P, C, N) are the register planes holding t-1, t, t+1; the caller rotates
     // the three arrays by NAME (the loop below is unrolled by three), so no register is moved.
@@ -248,20 +292,16 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         for (int j = 0; j < RX; ++j) {
             rq[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             wq[j] = make_float4(1.f, 1.f, 1.f, 1.f);
-            const int row = row0 + tr * RX + j;
-            if (col_live && row < p.R) {
-                const int b = BATCH_ROWS ? row : outer;
-                const int x = BATCH_ROWS ? 0 : row;
-                if (has_ref)
-                    rq[j] = __ldg(reinterpret_cast<const float4*>(
-                        p.e.ref + (int64_t)b * p.e.rb + (int64_t)t * p.e.r2 + (int64_t)x * p.e.r1 + y));
-                if (has_w)
-                    wq[j] = __ldg(reinterpret_cast<const float4*>(p.e.weight + ((int64_t)t * p.N1 + x) * p.N0 + y));
+            if (live & (1u << j)) {
+                if (has_ref) rq[j] = __ldg(reinterpret_cast<const float4*>(refp + j * ref_row));
+                if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * w_row));
             }
         }
+        if (has_ref) refp += p.e.r2;
+        if (has_w) wp += w_plane;
         if (t + 1 < NPL) {
-            mbar_wait(bars + 8u * nstage, nphase);
-            load_centres(N, nstage);
+            mbar_wait(nbar, nphase);
+            load_centres(N, nxt_a);
         } else {
 #pragma unroll
             for (int f = 0; f < NF; ++f)
@@ -273,32 +313,29 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         // x+-1 rows and y+-1 edge cells of plane t
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
-            const float* tl = tile(stage, f) + cell_off;
+            const uint32_t a = cur_a + f * BUF_BYTES;
             if constexpr (!BATCH_ROWS) {
-                const float4 a = *reinterpret_cast<const float4*>(tl - kTWP);
-                const float4 b = *reinterpret_cast<const float4*>(tl + RX * kTWP);
-                xm[f][0] = a.x; xm[f][1] = a.y; xm[f][2] = a.z; xm[f][3] = a.w;
-                xp[f][0] = b.x; xp[f][1] = b.y; xp[f][2] = b.z; xp[f][3] = b.w;
+                const float4 lo = lds128(a - ROW_BYTES);
+                const float4 hi = lds128(a + RX * ROW_BYTES);
+                xm[f][0] = lo.x; xm[f][1] = lo.y; xm[f][2] = lo.z; xm[f][3] = lo.w;
+                xp[f][0] = hi.x; xp[f][1] = hi.y; xp[f][2] = hi.z; xp[f][3] = hi.w;
             } else {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) { xm[f][i] = 0.0f; xp[f][i] = 0.0f; }
             }
 #pragma unroll
             for (int j = 0; j < RX; ++j) {
-                ym[f][j] = tl[j * kTWP - 1];
-                yp[f][j] = tl[j * kTWP + 4];
+                ym[f][j] = lds32(a + j * ROW_BYTES - 4u);
+                yp[f][j] = lds32(a + j * ROW_BYTES + 16u);
             }
         }
         const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
 
         const bool plane_live = STORE || !(in2 && (t == 0 || t == NPL - 1));
-        if (plane_live && col_live) {
+        if (plane_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
-                const int row = row0 + tr * RX + j;
-                if (row < p.R) {
-                    const int b = BATCH_ROWS ? row : outer;
-                    const int x = BATCH_ROWS ? 0 : row;
+                if (live & (1u << j)) {
                     float r[4];
                     r[0] = Prog<KIND>::template eval<4 * j + 0>(ctx, p.scalars);
                     r[1] = Prog<KIND>::template eval<4 * j + 1>(ctx, p.scalars);
@@ -308,17 +345,17 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                     const float ww[4] = {wq[j].x, wq[j].y, wq[j].z, wq[j].w};
                     if constexpr (COVER) {
                         // lo = c - q*h, hi = c + q*h with NumPy's separately rounded fp32 ops
-                        const bool row_in = !(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1));
                         uint32_t cnt = 0u;
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const float h = has_w ? __fmul_rn(p.e.band_q, ww[i]) : p.e.band_q;
-                            const float lo = __fsub_rn(rr[i], h), hi = __fadd_rn(rr[i], h);
+                            const float lo = has_ref ? __fsub_rn(rr[i], h) : -h;
+                            const float hi = has_ref ? __fadd_rn(rr[i], h) : h;
                             const bool in = r[i] >= lo && r[i] <= hi;
                             const bool counted = !((i == 0 && skip_first) || (i == 3 && skip_last));
                             cnt += (in && counted) ? 1u : 0u;
                         }
-                        acc_u[j] += row_in ? cnt : 0u;
+                        acc_u[j] += (cnt_rows & (1u << j)) ? cnt : 0u;
                     } else {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
@@ -327,9 +364,8 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                             r[i] = has_w ? __fmul_rn(v, ww[i]) : v;
                         }
                         if constexpr (STORE) {
-                            *reinterpret_cast<float4*>(p.e.out + (int64_t)b * p.e.ob + (int64_t)t * p.e.o2 +
-                                                       (int64_t)x * p.e.o1 + y) = make_float4(r[0], r[1], r[2], r[3]);
-                        } else if (!(in1 && !BATCH_ROWS && (x == 0 || x == p.N1 - 1))) {
+                            *reinterpret_cast<float4*>(outp + j * out_row) = make_float4(r[0], r[1], r[2], r[3]);
+                        } else if (cnt_rows & (1u << j)) {
                             if (rmax) {
                                 uint32_t m = max(score_bits(r[1]), score_bits(r[2]));
                                 if (!skip_first) m = max(m, score_bits(r[0]));
@@ -346,10 +382,14 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 }
             });
         }
+        if constexpr (STORE) outp += p.e.o2;
         __syncthreads();                            // every warp is done reading ring slot `stage`
         if (tid == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
         stage = nstage;
-        if (++nstage == p.stages) { nstage = 0; nphase ^= 1u; }
+        cur_a = nxt_a;
+        nxt_a += STAGE_BYTES;
+        nbar += 8u;
+        if (++nstage == p.stages) { nstage = 0; nxt_a = cell0; nbar = bars; nphase ^= 1u; }
     };
 
     for (int t = 0; t < NPL; t += 3) {
@@ -361,7 +401,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     if constexpr (!STORE) {
         static_for<RX>([&](auto J) {
             constexpr int j = decltype(J)::value;
-            const int row = row0 + tr * RX + j;
+            const int row = row_first + j;
             const int b = BATCH_ROWS ? row : outer;
             const bool ok = row < p.R;               // warp-uniform (one warp per tile row)
             if constexpr (COVER) {
@@ -531,7 +571,7 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     const size_t smem = stages * per_stage + 8 * kMaxStages + 128;
     CPPRE_REQUIRE(smem <= 227 * 1024, CPPRE_ERR_UNSUPPORTED, "tile ring of %zu bytes exceeds shared memory", smem);
 
-    auto kern = star_kernel<KIND, BR, RX, MASKS, CPPRE_TMA_MODE>;
+    auto kern = star_kernel<KIND, BR, RX, MASKS, CPPRE_TMA_MODE, CPPRE_TMA_OPER>;
     static size_t configured = 0;   // per instantiation
     if (smem > configured) {
         CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -1,0 +1,5 @@
+// K1 TMA star kernel, SCORE epilogue, operands weight only (see stencil_tma_impl.cuh).
+#define CPPRE_TMA_MODE CPPRE_EPI_SCORE
+#define CPPRE_TMA_OPER 2
+#define CPPRE_TMA_SUFFIX score_w
+#include "stencil_tma_impl.cuh"

@@ -93,6 +93,32 @@ def test_select_ranks_every_rank_signed_values_nan_and_strided_rows(n):
         np.testing.assert_array_equal(got, want)
 
 
+@pytest.mark.parametrize("n", [65, 100, 256, 300, 1000, 3000])
+def test_select_ranks_near_one_end_streaming_topk_windows(n):
+    """Ranks within 8 / 16 / 32 of either end take the streaming top-K kernel (K3t): every window
+    size, both ends, n not a multiple of the window, +-inf, ties, NaNs of either sign, strided rows."""
+    rng = np.random.default_rng(7 * n)
+    cells = 150
+    wide = (rng.standard_normal((n, cells + 9)) * 3).astype(np.float32)
+    wide[rng.integers(0, n, 2), 4] = np.inf
+    wide[rng.integers(0, n, 2), 5] = -np.inf
+    wide[rng.integers(0, n), 6] = np.nan
+    wide[rng.integers(0, n), 7] = np.float32(np.nan) * np.float32(-1)          # sign bit set
+    wide.view(np.uint32)[rng.integers(0, n), 8] = 0xffc00001                      # negative quiet NaN payload
+    wide[:, 10] = 2.5
+    wide[: n // 2, 11] = -1.0
+    t = cuda(wide)[:, 2:2 + cells]
+    ref = np.sort(wide[:, 2:2 + cells], axis=0)
+    nan_cols = np.isnan(ref).any(axis=0)
+    assert nan_cols.sum() == 3
+    for w in (1, 8, 9, 16, 17, 32):
+        for rr in (list(range(n - w, n)), list(range(w)), [n - w], [w - 1], [n - 1, n - w]):
+            got = ops.select_ranks(t, rr).cpu().numpy()
+            want = ref[rr]
+            want[:, nan_cols] = np.nan
+            np.testing.assert_array_equal(got, want, err_msg=f"n={n} window={w} ranks={rr[:3]}..")
+
+
 def test_calibrate_scalar_joint_form_negative_values_and_nan():
     rng = np.random.default_rng(0)
     for n in (19, 512, 4096, 5000):
