@@ -3,6 +3,7 @@
 //
 // Layout: score / residual tensors are [n, cells] with cells contiguous, so "thread = cell,
 // loop over samples" gives fully coalesced 128-byte warp accesses on every row.
+#include <cstdlib>
 #include <initializer_list>
 
 #include "common.cuh"
@@ -309,6 +310,73 @@ int dispatch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const
     return -1;
 }
 
+// Batcher's odd-even merge sort on R registers (ascending), every index a compile-time
+// constant: 19 / 63 / 191 comparators for R = 8 / 16 / 32 against the bitonic network's
+// 24 / 80 / 240.  Used where no lane crossing is needed (K3t).
+//
+// Compare-exchange flavours.  VIMNMX issues on the ALU pipe only (one warp instruction per two
+// cycles per scheduler), which is what bounds a register sorting network.  The "B" flavour keeps
+// the min on the ALU pipe and rebuilds the max on the FMA pipe as a + b - min(a, b) -- exact in
+// modular uint32 arithmetic -- with two IMADs, so a mix of the two flavours keeps both pipes busy.
+// `one` is the constant 1 passed as a kernel argument: a literal would let ptxas fold the two
+// multiply-adds into one ALU-pipe IADD3, which is exactly what this flavour is there to avoid.
+__device__ __forceinline__ void ce_mix(uint32_t& a, uint32_t& b, const bool fma_flavour, const uint32_t one) {
+    const uint32_t lo = min(a, b);
+    if (fma_flavour) {
+        const uint32_t t = a * one + b;              // IMAD
+        const uint32_t hi = lo * (0u - one) + t;     // IMAD: t - lo
+        a = lo;
+        b = hi;
+    } else {
+        const uint32_t hi = max(a, b);
+        a = lo;
+        b = hi;
+    }
+}
+
+template <int R, int MIX>
+struct OddEven {
+    // comparator counter -> flavour: MIX of every 3 comparators take the FMA-pipe flavour
+    template <int LO, int N, int STRIDE>
+    __device__ __forceinline__ static void merge(uint32_t (&k)[R], int& n_ce, const uint32_t one) {
+        constexpr int STEP = STRIDE * 2;
+        if constexpr (STEP < N) {
+            merge<LO, N, STEP>(k, n_ce, one);
+            merge<LO + STRIDE, N, STEP>(k, n_ce, one);
+#pragma unroll
+            for (int i = LO + STRIDE; i + STRIDE < LO + N; i += STEP) {
+                ce_mix(k[i], k[i + STRIDE], (n_ce % 3) < MIX, one);
+                ++n_ce;
+            }
+        } else {
+            ce_mix(k[LO], k[LO + STRIDE], (n_ce % 3) < MIX, one);
+            ++n_ce;
+        }
+    }
+    template <int LO, int N>
+    __device__ __forceinline__ static void sort(uint32_t (&k)[R], int& n_ce, const uint32_t one) {
+        if constexpr (N > 1) {
+            sort<LO, N / 2>(k, n_ce, one);
+            sort<LO + N / 2, N / 2>(k, n_ce, one);
+            merge<LO, N, 1>(k, n_ce, one);
+        }
+    }
+};
+
+// bitonic merge (input bitonic, output ascending) with the same flavour mix
+template <int R, int MIX, int STRIDE>
+__device__ __forceinline__ void bitonic_merge_mix(uint32_t (&k)[R], int& n_ce, const uint32_t one) {
+    if constexpr (STRIDE > 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if ((r & STRIDE) == 0) {
+                ce_mix(k[r], k[r | STRIDE], (n_ce % 3) < MIX, one);
+                ++n_ce;
+            }
+        bitonic_merge_mix<R, MIX, STRIDE / 2>(k, n_ce, one);
+    }
+}
+
 // K3t: per-cell order statistics near one END of the sorted column (the calibration case:
 // alpha = 0.1 on n = 256 asks for the 24th largest).  One lane owns one cell -- a warp row load
 // is 128 contiguous bytes, a CTA row 512 -- and streams its column in chunks of K samples:
@@ -318,10 +386,10 @@ int dispatch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const
 // is ~21 min/max operations for K = 32 against ~42 for the full sort, with no shared memory and
 // no cross-lane traffic.  FROM_BOTTOM complements the keys, so "K largest" selects the K
 // smallest.  Rank k of n lives at T[K - n + k] (top) / T[K - 1 - k] (bottom).
-template <int K, bool FROM_BOTTOM>
+template <int K, bool FROM_BOTTOM, int MIX>
 __global__ void __launch_bounds__(128)
 select_topk_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells, RankList ranks,
-                   float* __restrict__ out) {
+                   float* __restrict__ out, const uint32_t one) {
     const int64_t c = (int64_t)blockIdx.x * 128 + threadIdx.x;
     if (c >= cells) return;
     const float* px = x + c;
@@ -352,14 +420,16 @@ select_topk_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t c
             }
         }
     };
+    int n_ce = 0;                                    // compile-time after unrolling: picks the CE flavour
     load_chunk(T, n);
-    bitonic_sort_regs<1, K>(T, 0);
+    OddEven<K, MIX>::template sort<0, K>(T, n_ce, one);
     for (int base = K; base < n; base += K) {
         load_chunk(C, n - base);
-        bitonic_sort_regs<1, K>(C, 0);
+        n_ce = 0;
+        OddEven<K, MIX>::template sort<0, K>(C, n_ce, one);
 #pragma unroll
         for (int i = 0; i < K; ++i) T[i] = max(T[i], C[K - 1 - i]);
-        half_cleaners<1, K, K / 2>(T, 0);
+        bitonic_merge_mix<K, MIX, K / 2>(T, n_ce, one);
     }
     const bool nan = T[K - 1] > 0xff800000u || kmin < 0x007fffffu;
     for (int q = 0; q < ranks.n; ++q) {
@@ -372,12 +442,27 @@ select_topk_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t c
     }
 }
 
+int topk_mix() {   // CPPRE_TOPK_MIX=0..3: comparators out of every 3 that use the FMA-pipe flavour
+    static int mix = -1;
+    if (mix < 0) {
+        const char* e = getenv("CPPRE_TOPK_MIX");
+        mix = e ? atoi(e) : 2;
+        if (mix < 0 || mix > 3) mix = 2;
+    }
+    return mix;
+}
+
 template <int K, bool FROM_BOTTOM>
 int launch_topk(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
                 cudaStream_t st) {
     const int64_t blocks = (cells + 127) / 128;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    select_topk_kernel<K, FROM_BOTTOM><<<(unsigned)blocks, 128, 0, st>>>(x, xs, (int32_t)n, cells, rl, out);
+    switch (topk_mix()) {
+        case 0: select_topk_kernel<K, FROM_BOTTOM, 0><<<(unsigned)blocks, 128, 0, st>>>(x, xs, (int32_t)n, cells, rl, out, 1u); break;
+        case 1: select_topk_kernel<K, FROM_BOTTOM, 1><<<(unsigned)blocks, 128, 0, st>>>(x, xs, (int32_t)n, cells, rl, out, 1u); break;
+        case 3: select_topk_kernel<K, FROM_BOTTOM, 3><<<(unsigned)blocks, 128, 0, st>>>(x, xs, (int32_t)n, cells, rl, out, 1u); break;
+        default: select_topk_kernel<K, FROM_BOTTOM, 2><<<(unsigned)blocks, 128, 0, st>>>(x, xs, (int32_t)n, cells, rl, out, 1u); break;
+    }
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

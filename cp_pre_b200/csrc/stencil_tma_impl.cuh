@@ -148,7 +148,7 @@ __device__ __forceinline__ float lds32(uint32_t a) {
 // OPER: which optional epilogue operands exist, known at compile time (bit 0 = ref, bit 1 =
 // weight) or -1 = decided at run time (any combination; a few predicated instructions more).
 template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS, int MODE, int OPER>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int NF = Prog<KIND>::NF;
     constexpr bool STORE = MODE == CPPRE_EPI_STORE;
@@ -286,19 +286,19 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     // One time step.  (P, C, N) are the register planes holding t-1, t, t+1; the caller rotates
     // the three arrays by NAME (the loop below is unrolled by three), so no register is moved.
     auto step = [&](const int t, float (&P)[NF][RX][4], float (&C)[NF][RX][4], float (&N)[NF][RX][4]) {
-        // epilogue operands first: their L2 latency overlaps the barrier wait and the stencil math
+        // epilogue operands of row 0 first (their L2 latency overlaps the barrier wait and the
+        // stencil math); row j+1's are requested just before row j is evaluated
         float4 rq[RX], wq[RX];
-#pragma unroll
-        for (int j = 0; j < RX; ++j) {
+        auto fetch_operands = [&](auto J) {
+            constexpr int j = decltype(J)::value;
             rq[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             wq[j] = make_float4(1.f, 1.f, 1.f, 1.f);
             if (live & (1u << j)) {
                 if (has_ref) rq[j] = __ldg(reinterpret_cast<const float4*>(refp + j * ref_row));
                 if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * w_row));
             }
-        }
-        if (has_ref) refp += p.e.r2;
-        if (has_w) wp += w_plane;
+        };
+        fetch_operands(std::integral_constant<int, 0>{});
         if (t + 1 < NPL) {
             mbar_wait(nbar, nphase);
             load_centres(N, nxt_a);
@@ -310,31 +310,38 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) N[f][j][i] = 0.0f;
         }
-        // x+-1 rows and y+-1 edge cells of plane t
+        // x+-1 rows and y+-1 edge cells of plane t are fetched just before the row that needs
+        // them (row_halo below), which keeps their registers live for one row only
+        auto row_halo = [&](auto J) {
+            constexpr int j = decltype(J)::value;
 #pragma unroll
-        for (int f = 0; f < NF; ++f) {
-            const uint32_t a = cur_a + f * BUF_BYTES;
-            if constexpr (!BATCH_ROWS) {
-                const float4 lo = lds128(a - ROW_BYTES);
-                const float4 hi = lds128(a + RX * ROW_BYTES);
-                xm[f][0] = lo.x; xm[f][1] = lo.y; xm[f][2] = lo.z; xm[f][3] = lo.w;
-                xp[f][0] = hi.x; xp[f][1] = hi.y; xp[f][2] = hi.z; xp[f][3] = hi.w;
-            } else {
+            for (int f = 0; f < NF; ++f) {
+                const uint32_t a = cur_a + f * BUF_BYTES;
+                if constexpr (!BATCH_ROWS) {
+                    if constexpr (j == 0) {
+                        const float4 lo = lds128(a - ROW_BYTES);
+                        xm[f][0] = lo.x; xm[f][1] = lo.y; xm[f][2] = lo.z; xm[f][3] = lo.w;
+                    }
+                    if constexpr (j == RX - 1) {
+                        const float4 hi = lds128(a + RX * ROW_BYTES);
+                        xp[f][0] = hi.x; xp[f][1] = hi.y; xp[f][2] = hi.z; xp[f][3] = hi.w;
+                    }
+                } else if constexpr (j == 0) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) { xm[f][i] = 0.0f; xp[f][i] = 0.0f; }
-            }
-#pragma unroll
-            for (int j = 0; j < RX; ++j) {
+                    for (int i = 0; i < 4; ++i) { xm[f][i] = 0.0f; xp[f][i] = 0.0f; }
+                }
                 ym[f][j] = lds32(a + j * ROW_BYTES - 4u);
                 yp[f][j] = lds32(a + j * ROW_BYTES + 16u);
             }
-        }
+        };
         const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
 
         const bool plane_live = STORE || !(in2 && (t == 0 || t == NPL - 1));
         if (plane_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
+                row_halo(J);
+                if constexpr (j + 1 < RX) fetch_operands(std::integral_constant<int, j + 1>{});
                 if (live & (1u << j)) {
                     float r[4];
                     r[0] = Prog<KIND>::template eval<4 * j + 0>(ctx, p.scalars);
@@ -383,6 +390,8 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
             });
         }
         if constexpr (STORE) outp += p.e.o2;
+        if (has_ref) refp += p.e.r2;
+        if (has_w) wp += w_plane;
         __syncthreads();                            // every warp is done reading ring slot `stage`
         if (tid == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
         stage = nstage;
@@ -654,7 +663,7 @@ const Variant* pick(int kind, const StarHost& H, const Geometry& g) {
     int want = preferred_rx();
     if (want <= 0) {
         const int R = H.batch_rows ? g.B : g.N1;
-        want = (R >= 16 && (CPPRE_TMA_MODE == CPPRE_EPI_STORE || H.batch_rows)) ? 2 : 1;
+        want = R >= 16 ? 2 : 1;
     }
     for (const Variant& v : kVariants) {
         if (v.kind != kind || v.batch_rows != H.batch_rows) continue;

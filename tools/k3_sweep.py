@@ -27,14 +27,15 @@ def main():
     dev = torch.device("cuda")
     g = torch.Generator(device=dev).manual_seed(0)
     cells = 50 * 256 * 256
-    for n in (32, 64, 128, 256, 512, 1024, 2048):
+    ns = [int(v) for v in sys.argv[1].split(',')] if len(sys.argv) > 1 else (32, 64, 128, 256, 512, 1024, 2048)
+    for n in ns:
         c = cells if n <= 512 else cells // 4
         s = torch.rand((n, c), device=dev, generator=g)
         for nr, ranks in ((1, [int(0.9 * n)]), (10, [int(q * (n - 1)) for q in np.linspace(0.05, 0.95, 10)])):
             ms = timeit(lambda: ops.select_ranks(s, ranks))
             print(json.dumps({"op": "select_ranks", "n": n, "cells": c, "ranks": nr, "ms": round(ms, 3),
                               "Gscores_s": round(n * c / ms / 1e6, 1), "GBs": round(4 * n * c / ms / 1e6, 0)}), flush=True)
-        if n == 256:
+        if n == 256 and len(sys.argv) <= 1:
             q = ops.select_ranks(s, [230])[0]
             ms = timeit(lambda: ops.inside_count_band(s, None, q, 1.0))
             print(json.dumps({"op": "inside_count_band", "n": n, "cells": c, "ms": round(ms, 3),
