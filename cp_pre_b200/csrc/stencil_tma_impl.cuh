@@ -88,6 +88,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
+// Named barriers 1..stages (one per ring slot): consumers signal "done reading this slot" without
+// blocking, the warp whose turn it is to refill the slot waits for all of them.
+__device__ __forceinline__ void bar_arrive(uint32_t id, uint32_t threads) {
+    asm volatile("barrier.cta.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void bar_sync(uint32_t id, uint32_t threads) {
+    asm volatile("barrier.cta.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
                                             int c0, int c1, int c2, int c3) {
     asm volatile(
@@ -277,6 +285,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     // ring state: slot index (for the producer), shared addresses of this thread's cell in the
     // slots holding planes t and t+1, barrier address and parity guarding plane t+1
     int stage = 0;
+    int wturn = 0;                                 // warp that refills the slot freed by this step
     int nstage = p.stages > 1 ? 1 : 0;
     uint32_t cur_a = cell0;
     uint32_t nxt_a = cell0 + (p.stages > 1 ? STAGE_BYTES : 0u);
@@ -336,11 +345,19 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         };
         const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
 
+        // Slot `stage` (plane t) is read for the last time by the halo loads of the last row.
+        // Every warp but the refiller of this step signals that on the slot's named barrier and
+        // carries on; nobody waits at the end of a step, so warps drift apart by up to the ring
+        // depth and the scheduler always has math to issue while other warps wait for data.
+        const bool refiller = tr == wturn;
         const bool plane_live = STORE || !(in2 && (t == 0 || t == NPL - 1));
+        if (!plane_live && !refiller) bar_arrive(stage + 1, kThreads);
         if (plane_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
                 row_halo(J);
+                if constexpr (j == RX - 1)
+                    if (!refiller) bar_arrive(stage + 1, kThreads);
                 if constexpr (j + 1 < RX) fetch_operands(std::integral_constant<int, j + 1>{});
                 if (live & (1u << j)) {
                     float r[4];
@@ -356,9 +373,15 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const float h = has_w ? __fmul_rn(p.e.band_q, ww[i]) : p.e.band_q;
-                            const float lo = has_ref ? __fsub_rn(rr[i], h) : -h;
-                            const float hi = has_ref ? __fadd_rn(rr[i], h) : h;
-                            const bool in = r[i] >= lo && r[i] <= hi;
+                            bool in;
+                            if (has_ref) {
+                                const float lo = __fsub_rn(rr[i], h), hi = __fadd_rn(rr[i], h);
+                                in = r[i] >= lo && r[i] <= hi;
+                            } else {
+                                // centre 0: -h <= r <= h is |r| <= h for every h (NaN and h < 0
+                                // make both forms false), one compare instead of two
+                                in = fabsf(r[i]) <= h;
+                            }
                             const bool counted = !((i == 0 && skip_first) || (i == 3 && skip_last));
                             cnt += (in && counted) ? 1u : 0u;
                         }
@@ -392,8 +415,11 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         if constexpr (STORE) outp += p.e.o2;
         if (has_ref) refp += p.e.r2;
         if (has_w) wp += w_plane;
-        __syncthreads();                            // every warp is done reading ring slot `stage`
-        if (tid == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
+        if (refiller) {                             // wait until every warp is done with slot `stage`
+            bar_sync(stage + 1, kThreads);
+            if (tc == 0 && t + p.stages < NPL) issue(t + p.stages, stage);
+        }
+        wturn = (wturn + 1) & (kWarps - 1);
         stage = nstage;
         cur_a = nxt_a;
         nxt_a += STAGE_BYTES;
@@ -584,6 +610,8 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     static size_t configured = 0;   // per instantiation
     if (smem > configured) {
         CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                              cudaSharedmemCarveoutMaxShared));
         configured = smem;
     }
     const int64_t blocks = (int64_t)sp.col_tiles * sp.row_tiles * (BR ? 1 : g.B);
