@@ -13,9 +13,9 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_be
 cat $O/${TAG}_bench_ref.json
 SHORT="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
 timeout 300 $SHORT > $O/${TAG}_plain.log 2>&1 &&
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 700 -c 600 --csv --log-file $O/${TAG}_launches.csv $SHORT > $O/${TAG}_ncu_list.log 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 400 --csv --log-file $O/${TAG}_launches.csv $SHORT > $O/${TAG}_ncu_list.log 2>&1
 echo "ncu list exit $?"
 timeout 300 $SHORT > $O/${TAG}_plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'star_kernel|select_' -s 9 -c 3 -o $O/${TAG}_prof $SHORT > $O/${TAG}_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'star_kernel|select_' -s 9 -c 3 -o $O/${TAG}_prof $SHORT > $O/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $O
