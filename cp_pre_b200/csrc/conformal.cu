@@ -215,10 +215,24 @@ __device__ __forceinline__ void bitonic_sort_regs(uint32_t (&k)[R], const int j)
     bitonic_levels<L, R, 2>(k, j);
 }
 
-template <int L, int R, int TC>
+struct PerCell {            // optional per-cell rank for the regsort kernel (cnt == nullptr: unused)
+    const int32_t* cnt;     // [cells] #above (low 24 bits) + NaN flags (bits 24..)
+    int32_t kt;
+    uint32_t* overflow;     // counter, shared with K3w
+    int32_t* overflow_cells;
+    int32_t overflow_cap;
+    int64_t cell_offset;    // global index of this call's first cell (for the overflow list)
+};
+
+// COMPACT (the owner's side of the multi-GPU marginal quantile): the rows are candidate blocks
+// that are mostly -inf padding.  The fill drops the padding and packs each column's real
+// candidates to the front of the tile (shared-memory atomics hand out the positions), so a
+// network of N = L*R keys serves several times as many rows; a column with more than N real
+// candidates is reported on the overflow list and redone by the caller.
+template <int L, int R, int TC, bool COMPACT>
 __global__ void __launch_bounds__(TC * L)
 select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells, RankList ranks,
-                      float* __restrict__ out) {
+                      float* __restrict__ out, const PerCell pc) {
     constexpr int N = L * R;
     constexpr int THREADS = TC * L;
     constexpr int WARPS = THREADS / 32;
@@ -239,18 +253,30 @@ select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_
         const bool live = c0 + col < cells;
         const float* px = x + c0 + col;
         bool nan = false;
-#pragma unroll 8
-        for (int row = w * RPW + lane / TC; row < N; row += WARPS * RPW) {
-            uint32_t key = 0xffffffffu;     // padding sorts last
-            if (live && row < n) {
+        if constexpr (COMPACT) {
+            for (int e = tid; e < N * LD; e += THREADS) tile[e] = 0u;      // padding sorts first
+            __syncthreads();
+            for (int row = w * RPW + lane / TC; row < n; row += WARPS * RPW) {
+                if (!live) continue;
                 const uint32_t bits = __float_as_uint(__ldg(px + (int64_t)row * xs));
-                nan |= (bits & 0x7fffffffu) > 0x7f800000u;
-                key = float_to_key(bits);
+                if (bits == 0xff800000u) continue;                         // -inf: K3w padding
+                const uint32_t pos = atomicAdd(&nanflag[col], 1u);         // nanflag doubles as the column count
+                if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits);
             }
-            tile[row * LD + col] = key;
+        } else {
+#pragma unroll 8
+            for (int row = w * RPW + lane / TC; row < N; row += WARPS * RPW) {
+                uint32_t key = 0xffffffffu;     // padding sorts last
+                if (live && row < n) {
+                    const uint32_t bits = __float_as_uint(__ldg(px + (int64_t)row * xs));
+                    nan |= (bits & 0x7fffffffu) > 0x7f800000u;
+                    key = float_to_key(bits);
+                }
+                tile[row * LD + col] = key;
+            }
         }
         __syncthreads();                    // flags zeroed before anyone raises one
-        if (nan) nanflag[col] = 1u;
+        if (!COMPACT && nan) nanflag[col] = 1u;
     }
     __syncthreads();
 
@@ -268,7 +294,25 @@ select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_
 #pragma unroll
     for (int r = 0; r < R; ++r) tile[(r * L + j) * LD + ct] = k[r];
     __syncthreads();
-    if (tid < TC && c0 + tid < cells) {
+    if (tid < TC && c0 + tid < cells && pc.cnt != nullptr) {
+        // per-cell form (multi-GPU marginal quantile): the (kt - #above)-th largest candidate; the
+        // summed NaN flags of all ranks ride in the bits above 24
+        const int32_t packed = pc.cnt[c0 + tid];
+        const int want = pc.kt - (packed & 0xffffff);
+        const int have = COMPACT ? (int)nanflag[tid] : n;      // real candidates in this column
+        bool nan = (packed >> 24) != 0;
+        if (!nan && (want < 1 || want > n || have > N)) {
+            const uint32_t at = atomicAdd(pc.overflow, 1u);
+            if (at < (uint32_t)pc.overflow_cap) pc.overflow_cells[at] = (int32_t)(pc.cell_offset + c0 + tid);
+            nan = true;
+        }
+        // ascending position of the want-th largest; COMPACT: padding sorts first, and a rank
+        // below the real candidates lands in the dropped -inf padding
+        const int kq = nan ? 0 : (COMPACT ? N : n) - want;
+        uint32_t v = tile[((kq % R) * L + kq / R) * LD + tid];
+        if (COMPACT && want > have) v = 0x007fffffu;           // key(-inf)
+        out[c0 + tid] = nan ? __uint_as_float(0x7fc00000u) : __uint_as_float(key_to_float_bits(v));
+    } else if (tid < TC && c0 + tid < cells) {
         const bool has_nan = nanflag[tid] != 0u;
         for (int q = 0; q < ranks.n; ++q) {
             const int kq = ranks.r[q];
@@ -279,12 +323,12 @@ select_regsort_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_
     }
 }
 
-template <int L, int R, int TC>
+template <int L, int R, int TC, bool COMPACT = false>
 int launch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
-                   cudaStream_t st) {
+                   cudaStream_t st, const PerCell pc) {
     constexpr int N = L * R;
     const size_t smem = ((size_t)N * (TC + 1) + TC) * sizeof(uint32_t);
-    auto kern = select_regsort_kernel<L, R, TC>;
+    auto kern = select_regsort_kernel<L, R, TC, COMPACT>;
     static bool configured = false;
     if (!configured) {
         CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -292,22 +336,37 @@ int launch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const R
     }
     const int64_t blocks = (cells + TC - 1) / TC;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    kern<<<(unsigned)blocks, TC * L, smem, st>>>(x, xs, (int32_t)n, cells, rl, out);
+    kern<<<(unsigned)blocks, TC * L, smem, st>>>(x, xs, (int32_t)n, cells, rl, out, pc);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }
 
 // n <= 2048: pick the smallest network that holds n keys.  Returns -1 when n is too large.
 int dispatch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
-                     cudaStream_t st) {
-    if (n <= 32) return launch_regsort<1, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 64) return launch_regsort<2, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 128) return launch_regsort<4, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 256) return launch_regsort<8, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 512) return launch_regsort<16, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 1024) return launch_regsort<32, 32, 32>(x, xs, n, cells, rl, out, st);
-    if (n <= 2048) return launch_regsort<32, 64, 16>(x, xs, n, cells, rl, out, st);
+                     cudaStream_t st, const PerCell pc = PerCell{nullptr, 0, nullptr, nullptr, 0, 0}) {
+    if (n <= 32) return launch_regsort<1, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 64) return launch_regsort<2, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 128) return launch_regsort<4, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 256) return launch_regsort<8, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 512) return launch_regsort<16, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 1024) return launch_regsort<32, 32, 32>(x, xs, n, cells, rl, out, st, pc);
+    if (n <= 2048) return launch_regsort<32, 64, 16>(x, xs, n, cells, rl, out, st, pc);
     return -1;
+}
+
+// Owner-side select over padded candidate blocks: network of `net` keys (a power of two chosen
+// by the caller from the expected number of real candidates per cell), any number of rows.
+int dispatch_compact(int net, const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
+                     cudaStream_t st, const PerCell pc) {
+    switch (net) {
+        case 32: return launch_regsort<1, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        case 64: return launch_regsort<2, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        case 128: return launch_regsort<4, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        case 256: return launch_regsort<8, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        case 512: return launch_regsort<16, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        case 1024: return launch_regsort<32, 32, 32, true>(x, xs, n, cells, rl, out, st, pc);
+        default: return -1;
+    }
 }
 
 // Batcher's odd-even merge sort on R registers (ascending), every index a compile-time
@@ -485,6 +544,69 @@ int dispatch_topk(const float* x, int64_t xs, int64_t n, int64_t cells, const Ra
     if (need <= 16)
         return top ? launch_topk<16, false>(x, xs, n, cells, rl, out, st) : launch_topk<16, true>(x, xs, n, cells, rl, out, st);
     return top ? launch_topk<32, false>(x, xs, n, cells, rl, out, st) : launch_topk<32, true>(x, xs, n, cells, rl, out, st);
+}
+
+// K3w: window compaction, the second pass of the multi-GPU marginal quantile.  Every rank knows
+// a per-cell interval [lo, hi] (ordered int32 keys, all-reduced) that contains the global
+// quantile.  One lane owns one cell and streams its column once: counts the samples above hi and
+// collects the samples inside the interval into W slots (staged in shared memory, slot-major, so
+// the final write-out is coalesced).  Only those W candidates per cell and rank are exchanged
+// instead of the whole score column.  Output blocks are laid out [cells/slab][W][slab] -- the
+// send buffer of the all-to-all that moves slab r to rank r -- in sample order, -inf padded.
+// cnt[c] = #{x > hi} + (hi is a NaN key, i.e. some rank holds a NaN in this cell ? 1 << 24 : 0).
+__device__ __forceinline__ uint32_t ordered_key(float v) {
+    const uint32_t bits = __float_as_uint(v);
+    return bits ^ ((uint32_t)((int32_t)bits >> 31) | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(128)
+window_compact_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells,
+                      const int32_t* __restrict__ lo, const int32_t* __restrict__ hi, int32_t W, int64_t slab,
+                      float* __restrict__ win, int32_t* __restrict__ cnt, uint32_t* overflow,
+                      int32_t* __restrict__ overflow_cells, int32_t overflow_cap) {
+    extern __shared__ float slots[];                 // [W][128]
+    const int tid = threadIdx.x;
+    const int64_t c = (int64_t)blockIdx.x * 128 + tid;
+    if (c >= cells) return;
+    const uint32_t klo = (uint32_t)lo[c] ^ 0x80000000u, khi = (uint32_t)hi[c] ^ 0x80000000u;
+    const uint32_t span = khi - klo;                 // lo <= hi by construction
+    const bool open = khi > 0xff800000u || klo > khi;   // hi is a NaN key (a rank saw a NaN): result is NaN anyway
+    const float* px = x + c;
+    // a NaN anywhere in this cell shows up as `open` on every rank: the local order statistic of
+    // the rank that holds it is NaN, and NaN keys win the MAX all-reduce that produced hi
+    uint32_t above = 0u, inside = 0u;
+    auto take = [&](float v) {
+        const uint32_t key = ordered_key(v);
+        above += key > khi ? 1u : 0u;
+        if (key - klo <= span && !open) {
+            if (inside < (uint32_t)W) slots[inside * 128 + tid] = v;
+            ++inside;
+        }
+    };
+    int32_t i = 0;
+    for (; i + 8 <= n; i += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { v[u] = __ldg(px); px += xs; }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) take(v[u]);
+    }
+    for (; i < n; ++i) { take(__ldg(px)); px += xs; }
+    if (inside > (uint32_t)W) {                      // reported, with the cell index: the caller redoes these exactly
+        const uint32_t at = atomicAdd(overflow, 1u);
+        if (at < (uint32_t)overflow_cap) overflow_cells[at] = (int32_t)c;
+        inside = (uint32_t)W;
+    }
+    cnt[c] = (int32_t)(above | (open ? 1u << 24 : 0u));
+    float* dst = win + (c / slab) * (int64_t)W * slab + c % slab;
+    for (int s = 0; s < W; ++s)
+        dst[(int64_t)s * slab] = (uint32_t)s < inside ? slots[s * 128 + tid] : __uint_as_float(0xff800000u);
+}
+
+__global__ void __launch_bounds__(kThreads)
+ordered_keys_kernel(const float* __restrict__ x, int64_t n, int32_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i < n) out[i] = (int32_t)(ordered_key(x[i]) ^ 0x80000000u);
 }
 
 // K3b: per-cell single-rank radix select straight from global memory (any n).  8 passes of
@@ -684,6 +806,66 @@ int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int
         CPPRE_CHECK_LAUNCH();
     }
     return CPPRE_OK;
+}
+
+int cppre_ordered_keys(const float* d_x, int64_t n, int32_t* d_out, void* stream) {
+    CPPRE_REQUIRE(n >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    if (n == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_x && d_out, CPPRE_ERR_BAD_ARG, "null pointer");
+    const int64_t blocks = (n + kThreads - 1) / kThreads;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    ordered_keys_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_x, n, d_out);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                         const int32_t* d_lo, const int32_t* d_hi, int32_t slots, int64_t slab,
+                         float* d_win, int32_t* d_cnt, uint32_t* d_overflow, int32_t* d_overflow_cells,
+                         int32_t overflow_cap, void* stream) {
+    CPPRE_REQUIRE(cells < (int64_t(1) << 31) && overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells),
+                  CPPRE_ERR_BAD_ARG, "bad overflow list");
+    CPPRE_REQUIRE(n >= 0 && cells >= 0 && slots >= 1 && slots <= 96 && slab >= 1, CPPRE_ERR_BAD_ARG,
+                  "bad size (n=%lld cells=%lld slots=%d slab=%lld)", (long long)n, (long long)cells, slots,
+                  (long long)slab);
+    CPPRE_REQUIRE(n < (int64_t(1) << 24), CPPRE_ERR_UNSUPPORTED, "n too large for the packed count");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE((d_scores || n == 0) && d_lo && d_hi && d_win && d_cnt && d_overflow, CPPRE_ERR_BAD_ARG,
+                  "null pointer");
+    const int64_t blocks = (cells + 127) / 128;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    const size_t smem = (size_t)slots * 128 * sizeof(float);
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem));
+        configured = smem;
+    }
+    window_compact_kernel<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
+        d_scores, row_stride, (int32_t)n, cells, d_lo, d_hi, slots, slab, d_win, d_cnt, d_overflow,
+        d_overflow_cells, overflow_cap);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows, int64_t cells,
+                          const int32_t* d_cnt, int32_t kt, int32_t network, float* d_out,
+                          uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap,
+                          int64_t cell_offset, void* stream) {
+    CPPRE_REQUIRE(rows >= 1 && cells >= 0 && rows < (int64_t(1) << 31), CPPRE_ERR_BAD_ARG, "bad size");
+    CPPRE_REQUIRE(overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells), CPPRE_ERR_BAD_ARG, "bad overflow list");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_cand && d_cnt && d_out && d_overflow, CPPRE_ERR_BAD_ARG, "null pointer");
+    RankList rl;
+    rl.n = 1;
+    rl.r[0] = 0;
+    const PerCell pc{d_cnt, kt, d_overflow, d_overflow_cells, overflow_cap, cell_offset};
+    const int rc = network > 0
+                       ? dispatch_compact(network, d_cand, row_stride, rows, cells, rl, d_out, (cudaStream_t)stream, pc)
+                       : dispatch_regsort(d_cand, row_stride, rows, cells, rl, d_out, (cudaStream_t)stream, pc);
+    CPPRE_REQUIRE(rc >= 0, CPPRE_ERR_UNSUPPORTED, "unsupported candidate select (rows=%lld network=%d)",
+                  (long long)rows, network);
+    return rc;
 }
 
 int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,

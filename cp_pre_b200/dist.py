@@ -10,9 +10,13 @@ halo and no data-path collective.  Only calibration coupl
             (``joint_quantile_hist``, kernel ``cppre_radix_hist``).  The per-cell modulation (std
             over the GLOBAL batch) is merged Chan-style from per-rank (count, mean, M2) with two
             all-reduces (``global_cell_std``).
-  Marginal  per-cell quantiles over a batch split across ranks: scores are transposed
-            batch-shard -> cell-shard with one all-to-all, each rank selects on its cell slab,
-            the slabs of qhat are all-gathered (``marginal_quantiles``).
+  Marginal  per-cell quantiles over a batch split across ranks (``marginal_quantiles``): every
+            rank selects one local order statistic per cell; their all-reduced min / max bracket
+            the global quantile; one pass over the local scores collects the few samples inside
+            the bracket (K3w); only those candidates cross NVLink (all-to-all, batch-shard ->
+            cell-shard) and the owner of a cell slab picks the answer.  Exact; a cell whose
+            bracket holds more candidates than the window falls back to transposing the whole
+            score tensor.
 
 The kernels are injected (``hist_fn`` / ``select_fn`` / ``moments_fn``) so the orchestration can
 be tested on CPU with the oracle's NumPy implementations; the defaults are the CUDA kernels and
@@ -142,33 +146,136 @@ def joint_quantile_hist(scores: torch.Tensor, rank_k: int, group=None,
 # ---------------------------------------------------------------------------------------
 # Marginal: per-cell quantiles over a batch split across ranks
 # ---------------------------------------------------------------------------------------
-def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
-                       select_fn: Optional[Callable] = None) -> torch.Tensor:
-    """scores: rank-local [n_local, cells...] (same n_local on every rank).  Returns
-    [len(ranks), cells...] quantiles over the global n_local*world samples, on every rank.
-    Cells are padded to a multiple of the world size for the exchange."""
-    if select_fn is None:
-        from . import ops
-        select_fn = ops.select_ranks
+def _cuda_kernels():
+    from . import ops
+    return {"select": ops.select_ranks, "keys": ops.ordered_keys, "window": ops.window_compact,
+            "top": ops.select_from_top}
+
+
+def _exchange_quantiles(scores: torch.Tensor, ranks: Sequence[int], group, select_fn) -> torch.Tensor:
+    """Exact slow path: transpose the WHOLE score tensor batch-shard -> cell-shard with one
+    all-to-all, select on [world*n, slab], all-gather the slabs of qhat."""
     w = _world(group)
-    if w == 1:
-        return select_fn(scores, ranks)
     n = scores.shape[0]
-    cell_shape = tuple(scores.shape[1:])
     flat = scores.reshape(n, -1)
     cells = flat.shape[1]
     slab = (cells + w - 1) // w
     if slab * w != cells:
         flat = torch.nn.functional.pad(flat, (0, slab * w - cells))
-    # batch-shard -> cell-shard: chunk r of the send buffer is this rank's samples of slab r
+    # chunk r of the send buffer is this rank's samples of slab r
     send = flat.reshape(n, w, slab).permute(1, 0, 2).contiguous()
     recv = torch.empty_like(send)
     dist.all_to_all_single(recv, send, group=group)          # recv[r] = rank r's samples of MY slab
     q_slab = select_fn(recv.reshape(w * n, slab), ranks).contiguous()    # [R, slab]
     parts = [torch.empty_like(q_slab) for _ in range(w)]
     dist.all_gather(parts, q_slab, group=group)
-    q = torch.cat(parts, dim=1)[:, :cells]
-    return q.reshape((len(ranks),) + cell_shape)
+    return torch.cat(parts, dim=1)[:, :cells]
+
+
+def _window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int):
+    """One global order statistic per cell, exchanging `slots` candidates per cell and rank
+    instead of the n local samples (include/cppre.h, K3w).  Returns q [cells], or None when more
+    cells overflowed the candidate window than the redo list holds (the caller then transposes
+    the whole tensor).  The few cells whose bracket holds more than `slots` samples on some rank
+    are redone exactly from their full columns (all-gathered).
+
+    With kt = N - rank_k (the kt-th largest of the N = world*n global samples) and
+    J = ceil(kt / world): every rank's J-th largest a_r satisfies min_r a_r <= g <= max_r a_r
+    for the global answer g (>= : each rank holds J samples >= its a_r, so world*J >= kt samples
+    are >= the minimum; <= : a sample above max_r a_r is among the J-1 largest of its rank, so
+    fewer than kt samples exceed the maximum).  g is then the (kt - #{x > hi})-th largest of
+    the samples inside [lo, hi], and only those travel."""
+    w = _world(group)
+    me = dist.get_rank(group)
+    n = scores.shape[0]
+    flat = scores.reshape(n, -1)
+    cells = flat.shape[1]
+    kt = w * n - int(rank_k)
+    J = -(-kt // w)
+    a = kern["keys"](kern["select"](flat, [n - J])[0])        # int32 ordered keys, [cells]
+    lo, hi = a.clone(), a.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    slab = (cells + w - 1) // w
+    dev = scores.device
+    win_over = torch.zeros(1, dtype=torch.int32, device=dev)       # cells whose bracket exceeds `slots`
+    over_cells = torch.full((OVERFLOW_CAP,), -1, dtype=torch.int32, device=dev)
+    win, cnt = kern["window"](flat, lo, hi, slots, slab, win_over, over_cells)    # [w, slots, slab], [w*slab]
+    dist.all_reduce(cnt, group=group)
+    recv = torch.empty_like(win)
+    dist.all_to_all_single(recv, win, group=group)           # recv[r] = rank r's candidates of MY slab
+    n_before = win_over.clone()
+    q_slab = kern["top"](recv.reshape(w * slots, slab), cnt[me * slab:(me + 1) * slab], kt, win_over, over_cells,
+                         me * slab, owner_network(w, slots))
+    parts = [torch.empty_like(q_slab) for _ in range(w)]
+    dist.all_gather(parts, q_slab.contiguous(), group=group)
+    q = torch.cat(parts)[:cells]
+    # overflow bookkeeping, identical on every rank: cells listed by K3w and by the owner's select
+    del n_before
+    counts = [torch.empty_like(win_over) for _ in range(w)]
+    dist.all_gather(counts, win_over, group=group)
+    counts = torch.stack(counts).cpu()
+    if int(counts.sum()) == 0:
+        return q
+    if int(counts.max()) > OVERFLOW_CAP:
+        return None                                          # too many: the caller transposes everything
+    # redo the few overflowing cells from their full columns (exact): union of the rank lists
+    lists = [torch.empty_like(over_cells) for _ in range(w)]
+    dist.all_gather(lists, over_cells, group=group)
+    ids = torch.unique(torch.cat(lists))
+    ids = ids[(ids >= 0) & (ids < cells)].to(torch.int64)
+    cols = flat[:, ids].contiguous()
+    allcols = [torch.empty_like(cols) for _ in range(w)]
+    dist.all_gather(allcols, cols, group=group)
+    q[ids] = kern["select"](torch.cat(allcols), [int(rank_k)])[0].to(q.dtype)
+    return q
+
+
+OVERFLOW_CAP = 8192
+
+
+def owner_network(world: int, slots: int) -> int:
+    """Keys the owner of a cell slab sorts per cell: a power of two above the number of real
+    candidates the union of `world` brackets holds (about 14 per rank at alpha = 0.1, n = 256;
+    the rare cell above it is redone exactly), never more than the candidate rows."""
+    need = max(32, 32 * world)
+    net = 32
+    while net < need and net < world * slots:
+        net *= 2
+    return min(net, 1024)
+
+
+def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
+                       select_fn: Optional[Callable] = None, kernels: Optional[dict] = None,
+                       slots: int = 40, mode: str = "auto") -> torch.Tensor:
+    """scores: rank-local [n_local, cells...] (same n_local on every rank).  Returns
+    [len(ranks), cells...] order statistics over the global n_local*world samples, on every rank.
+
+    mode "auto": candidate-window exchange per rank (`slots` floats per cell and rank over
+    NVLink instead of n_local); cells that overflow the window are redone exactly from their
+    full columns, and past OVERFLOW_CAP such cells the whole tensor is transposed instead
+    (decided collectively, so every process takes the same path); "window" raises instead of
+    transposing; "exchange" always transposes the whole tensor."""
+    w = _world(group)
+    if kernels is None and select_fn is None:
+        kernels = _cuda_kernels()
+    if select_fn is None:
+        select_fn = kernels["select"]
+    if w == 1:
+        return select_fn(scores, ranks)
+    cell_shape = tuple(scores.shape[1:])
+    if mode == "exchange" or kernels is None:
+        q = _exchange_quantiles(scores, ranks, group, select_fn)
+        return q.reshape((len(ranks),) + cell_shape)
+    out = []
+    for k in ranks:
+        q = _window_quantile(scores, k, group, kernels, slots)
+        if q is None:
+            if mode == "window":
+                raise RuntimeError(f"candidate window overflowed in more than {OVERFLOW_CAP} cells (slots={slots})")
+            q = _exchange_quantiles(scores, [k], group, select_fn)[0]
+        out.append(q)
+    return torch.stack(out).reshape((len(ranks),) + cell_shape)
 
 
 def allreduce_counts(*values: int, device=None, group=None):

@@ -267,6 +267,59 @@ def select_ranks(scores: torch.Tensor, ranks: Sequence[int]) -> torch.Tensor:
     return out.reshape((len(ranks),) + tuple(scores.shape[1:]))
 
 
+def ordered_keys(x: torch.Tensor) -> torch.Tensor:
+    """float32 -> int32 keys whose signed order is the float order (NaN with a clear sign bit on top)."""
+    lib = L.load()
+    xc = x.contiguous()
+    out = torch.empty(xc.shape, dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(lib.cppre_ordered_keys(_ptr(xc), xc.numel(), _ptr(out), _stream(x.device)))
+    return out
+
+
+def window_compact(scores: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor, slots: int, slab: int,
+                   overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
+    """Second pass of the multi-GPU marginal quantile (K3w).  scores [n, cells...]; lo / hi int32
+    ordered keys per cell.  Returns (win [blocks, slots, slab] float32, cnt [blocks*slab] int32);
+    ``overflow`` (int32 [1], caller-zeroed) is incremented per cell with more than ``slots``
+    window samples; their indices are written to ``overflow_cells`` (int32 [cap]) at the counter's
+    old value while that is below cap."""
+    lib = L.load()
+    fs, rs = _rows(scores)
+    n, cells = fs.shape
+    cap = 0 if overflow_cells is None else overflow_cells.numel()
+    blocks = (cells + slab - 1) // slab
+    win = torch.empty((blocks, slots, slab), dtype=torch.float32, device=scores.device)
+    cnt = torch.zeros(blocks * slab, dtype=torch.int32, device=scores.device)
+    if blocks * slab != cells:      # padding tail of the last slab: no candidates; flagged like a NaN cell
+        win[-1, :, cells - (blocks - 1) * slab:] = float("-inf")
+        cnt[cells:] = 1 << 24
+    with torch.cuda.device(scores.device):
+        L.check(lib.cppre_window_compact(_ptr(fs), rs, n, cells, _ptr(lo.reshape(-1).contiguous()),
+                                         _ptr(hi.reshape(-1).contiguous()), int(slots), int(slab), _ptr(win),
+                                         _ptr(cnt), _ptr(overflow), _ptr(overflow_cells), cap,
+                                         _stream(scores.device)))
+    return win, cnt
+
+
+def select_from_top(cand: torch.Tensor, cnt: torch.Tensor, kt: int, overflow: torch.Tensor,
+                    overflow_cells: Optional[torch.Tensor] = None, cell_offset: int = 0,
+                    network: int = 0) -> torch.Tensor:
+    """out[c] = the (kt - (cnt[c] & 0xffffff))-th largest of cand[:, c]; NaN where cnt[c] >> 24.
+    ``network`` > 0: pack the non-padding candidates of each cell and sort that many keys only.
+    Cells that cannot be answered are counted in ``overflow`` and listed (cell_offset + c)."""
+    lib = L.load()
+    fc, rs = _rows(cand)
+    rows, cells = fc.shape
+    cap = 0 if overflow_cells is None else overflow_cells.numel()
+    out = torch.empty(cells, dtype=torch.float32, device=cand.device)
+    with torch.cuda.device(cand.device):
+        L.check(lib.cppre_select_from_top(_ptr(fc), rs, rows, cells, _ptr(cnt.contiguous()), int(kt), int(network),
+                                          _ptr(out), _ptr(overflow), _ptr(overflow_cells), cap, int(cell_offset),
+                                          _stream(cand.device)))
+    return out
+
+
 def radix_hist(x: torch.Tensor, prefix: int, mask: int, shift: int, hist: torch.Tensor):
     lib = L.load()
     flat = x.reshape(-1).contiguous()

@@ -185,6 +185,39 @@ int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int
 int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,
                      uint32_t* d_hist, void* stream);
 
+/* ---- K3w: multi-GPU marginal quantile (batch axis sharded over ranks) --------------------
+ * No counterpart in the reference (it is single-process); these three calls replace the naive
+ * all-to-all of the whole score tensor in front of np.quantile (Marginal/NS_Residuals_CP.py:311):
+ *   1. every rank selects two local order statistics per cell (cppre_select_ranks), converts
+ *      them to order-preserving int32 keys (cppre_ordered_keys) and all-reduces MIN / MAX: the
+ *      global quantile of every cell lies in the resulting [lo, hi];
+ *   2. cppre_window_compact streams the local scores once: cnt[c] = #{x > hi} (+ 1<<24 if the
+ *      cell holds a NaN on some rank, i.e. hi is a NaN key) and the local samples inside [lo, hi]
+ *      go into `slots` candidate rows (sample order, -inf padded), laid out
+ *      [cells/slab][slots][slab] = the send buffer of an all-to-all that
+ *      gives rank r the candidates of cell slab r; *d_overflow += #cells with more than `slots`
+ *      samples inside, whose indices go to d_overflow_cells[old counter value] while that is
+ *      below overflow_cap (the caller redoes those few cells from their full columns);
+ *   3. after all-reducing cnt (SUM), the owner of a slab picks, per cell, the
+ *      (kt - (cnt & 0xffffff))-th largest (1-based) of the gathered candidate rows
+ *      (cppre_select_from_top); NaN where cnt >> 24 != 0.  network = 0 sorts all rows (<= 2048);
+ *      network = 32..1024 (a power of two) first drops the -inf padding and packs the real
+ *      candidates of each cell, then sorts `network` keys -- far fewer than rows, since most of
+ *      a block is padding.  A cell whose rank falls outside [1, rows], or that holds more than
+ *      `network` real candidates, is counted in *d_overflow and listed (cell_offset + index) in
+ *      d_overflow_cells like in step 2.
+ * A non-zero overflow counter means the caller must redo the listed cells (or, past the list
+ * capacity, everything) on the exact slow path. */
+int cppre_ordered_keys(const float* d_x, int64_t n, int32_t* d_out, void* stream);
+int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                         const int32_t* d_lo, const int32_t* d_hi, int32_t slots, int64_t slab,
+                         float* d_win, int32_t* d_cnt, uint32_t* d_overflow, int32_t* d_overflow_cells,
+                         int32_t overflow_cap, void* stream);
+int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows, int64_t cells,
+                          const int32_t* d_cnt, int32_t kt, int32_t network, float* d_out,
+                          uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap,
+                          int64_t cell_offset, void* stream);
+
 /* ---- K5: coverage --------------------------------------------------------------------- */
 /* inside[i] = #{ c : lo[i,c] <= y[i,c] <= hi[i,c] }, uint32 per sample, overwritten.
  * lo / hi: row stride 0 broadcasts one [cells] row over all samples.

@@ -483,3 +483,66 @@ def select_rank(scores, rank):
     s = np.sort(np.asarray(scores, dtype=F32), axis=0)
     out = s[rank]
     return np.where(np.isnan(s[-1]), F32(np.nan), out)
+
+
+# --------------------------------------------------------------------------------------
+# multi-GPU marginal quantile: NumPy restatement of the three K3w kernels (include/cppre.h),
+# used as their parity oracle and injected into cp_pre_b200/dist.py by the gloo CPU tests
+# --------------------------------------------------------------------------------------
+def ordered_keys(x):
+    """int32 keys whose signed order is the float32 order (NaN with a clear sign bit on top)."""
+    return (float_order_key(x) ^ np.uint32(0x80000000)).view(np.int32).reshape(np.shape(x))
+
+
+def window_compact(scores, lo, hi, slots, slab):
+    """(win [blocks, slots, slab] -inf padded, cnt [blocks*slab] int32, overflowing cell indices):
+    per cell the first `slots` samples with lo <= key <= hi in row order; cnt = #{key > hi} + (1 << 24 if hi is a NaN key: some rank holds a NaN in this
+    cell).  A NaN `hi` key leaves the cell's window empty."""
+    s = np.asarray(scores, dtype=F32)
+    n = s.shape[0]
+    flat = s.reshape(n, -1)
+    cells = flat.shape[1]
+    keys = ordered_keys(flat).astype(np.int64)
+    lo = np.asarray(lo).reshape(-1).astype(np.int64)
+    hi = np.asarray(hi).reshape(-1).astype(np.int64)
+    blocks = -(-cells // slab)
+    win = np.full((blocks, slots, slab), -np.inf, dtype=F32)
+    cnt = np.zeros(blocks * slab, dtype=np.int32)
+    cnt[cells:] = 1 << 24                    # padding tail of the last slab: flagged like a NaN cell
+    inf_key = int(ordered_keys(np.array([np.inf], dtype=F32))[0])
+    overflow = []
+    for c in range(cells):
+        col = keys[:, c]
+        is_open = bool(hi[c] > inf_key or lo[c] > hi[c])
+        cnt[c] = int((col > hi[c]).sum()) + ((1 << 24) if is_open else 0)
+        if is_open:
+            continue
+        inside = flat[(col >= lo[c]) & (col <= hi[c]), c]
+        if len(inside) > slots:
+            overflow.append(c)
+            inside = inside[:slots]
+        win[c // slab, :len(inside), c % slab] = inside
+    return win, cnt, overflow
+
+
+def select_from_top(cand, cnt, kt, network=0):
+    """(out [cells], overflowing cell indices): the (kt - (cnt & 0xffffff))-th largest of each
+    column; NaN where cnt >> 24 != 0; overflow where that rank is outside [1, rows] or, with
+    network > 0, where the column holds more than `network` candidates other than -inf."""
+    cand = np.asarray(cand, dtype=F32)
+    rows, cells = cand.shape
+    order = np.argsort(float_order_key(cand), axis=0, kind="stable")
+    srt = np.take_along_axis(cand, order, axis=0)
+    out = np.full(cells, np.nan, dtype=F32)
+    overflow = []
+    for c in range(cells):
+        packed = int(cnt[c])
+        if packed >> 24:
+            continue
+        want = kt - (packed & 0xFFFFFF)
+        real = int((cand[:, c] != -np.inf).sum())
+        if want < 1 or want > rows or (network and real > network):
+            overflow.append(c)
+            continue
+        out[c] = srt[rows - want, c]
+    return out, overflow

@@ -32,6 +32,31 @@ def _np_select(scores, ranks):
     return torch.from_numpy(np.stack([O.select_rank(s, r) for r in ranks]))
 
 
+def _np_keys(x):
+    return torch.from_numpy(O.ordered_keys(x.numpy()))
+
+
+def _np_window(scores, lo, hi, slots, slab, overflow, overflow_cells):
+    win, cnt, ov = O.window_compact(scores.numpy(), lo.numpy(), hi.numpy(), slots, slab)
+    for c in ov:
+        if int(overflow) < overflow_cells.numel():
+            overflow_cells[int(overflow)] = c
+        overflow += 1
+    return torch.from_numpy(win), torch.from_numpy(cnt)
+
+
+def _np_top(cand, cnt, kt, overflow, overflow_cells, cell_offset, network):
+    out, ov = O.select_from_top(cand.numpy(), cnt.numpy(), kt, network)
+    for c in ov:
+        if int(overflow) < overflow_cells.numel():
+            overflow_cells[int(overflow)] = cell_offset + c
+        overflow += 1
+    return torch.from_numpy(out)
+
+
+NP_KERNELS = {"select": _np_select, "keys": _np_keys, "window": _np_window, "top": _np_top}
+
+
 def _np_moments(a, b):
     x = a.numpy().astype(np.float64) - (0 if b is None else b.numpy().astype(np.float64))
     x = x.reshape(x.shape[0], -1)
@@ -79,6 +104,33 @@ def _worker(rank, world, port, out):
     odd = np.abs(full[:, :, :5])                           # 30 cells -> not divisible by 4 either way
     q = D.marginal_quantiles(torch.from_numpy(odd[lo:hi]).contiguous(), [7], select_fn=_np_select)
     res["marginal_odd_equal"] = bool(np.array_equal(q.numpy(), np.sort(odd, axis=0)[[7]]))
+    # candidate-window exchange (K3w orchestration): every rank of interest, ties, +-inf, a NaN
+    # column, cells not divisible by the world size; then a window too small for the bracket
+    big = (rng.standard_normal((40 * world, 9, 5)) * 3).astype(np.float32)
+    big[3, 0, 0] = np.inf
+    big[5, 0, 1] = -np.inf
+    big[:, 0, 2] = 1.25
+    big[7, 0, 3] = np.nan
+    n_loc = 40
+    mine_big = torch.from_numpy(big[rank * n_loc:(rank + 1) * n_loc])
+    ref = np.sort(big, axis=0)
+    ref[:, np.isnan(ref).any(axis=0)] = np.nan
+    N = 40 * world
+    ks = [N - 1, N - 5, N - 17, int(0.9 * N), N // 2, 3, 0]
+    q = D.marginal_quantiles(mine_big, ks, kernels=NP_KERNELS, mode="window", slots=40)
+    res["window_equal"] = bool(np.array_equal(q.numpy(), ref[ks], equal_nan=True))
+    # 6 slots: most mid-range brackets overflow and are redone from their full columns
+    q = D.marginal_quantiles(mine_big, ks, kernels=NP_KERNELS, mode="window", slots=6)
+    res["auto_equal"] = bool(np.array_equal(q.numpy(), ref[ks], equal_nan=True))
+    cap, D.OVERFLOW_CAP = D.OVERFLOW_CAP, 3             # a redo list that is too short
+    try:
+        D.marginal_quantiles(mine_big, [N // 2], kernels=NP_KERNELS, mode="window", slots=1)
+        res["overflow_raises"] = False
+    except RuntimeError:
+        res["overflow_raises"] = True
+    q = D.marginal_quantiles(mine_big, [N // 2], kernels=NP_KERNELS, mode="auto", slots=1)
+    res["fallback_equal"] = bool(np.array_equal(q.numpy(), ref[[N // 2]], equal_nan=True))
+    D.OVERFLOW_CAP = cap
     res["counts"] = D.allreduce_counts(rank + 1, 10)
     out[rank] = res
     dist.barrier()
@@ -96,6 +148,7 @@ def test_sharded_calibration_orchestration(world):
             r = out[rank]
             assert r["std_err"] < 1e-6
             assert r["marginal_equal"] and r["marginal_odd_equal"]
+            assert r["window_equal"] and r["auto_equal"] and r["overflow_raises"] and r["fallback_equal"]
             assert r["counts"] == [world * (world + 1) // 2, 10 * world]
 
 

@@ -7,6 +7,7 @@ import torch
 
 import cp_pre_b200
 from conftest import assert_close_rel, load_golden
+from cp_pre_b200 import dist as D
 from cp_pre_b200 import ops, programs
 from oracle import cpu_oracle as O
 from oracle import synth
@@ -239,3 +240,97 @@ def test_joint_and_marginal_pipelines_end_to_end():
     mine = scores.cpu().numpy()
     for i, a in enumerate((0.1, 0.3, 0.5)):
         np.testing.assert_array_equal(qh[i].cpu().numpy(), O.calibrate(mine, len(mine), a))
+
+
+def test_window_kernels_match_the_oracle():
+    """K3w pieces against oracle/cpu_oracle.py: ordered keys, window compaction (counts, NaN flag,
+    slot contents in row order, overflow count, blocked layout with a ragged last slab) and the
+    per-cell select-from-top (NaN flags, out-of-window ranks)."""
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal(1000) * 4).astype(np.float32)
+    x[:6] = [np.inf, -np.inf, np.nan, 0.0, -0.0, -np.float32(np.nan)]
+    np.testing.assert_array_equal(ops.ordered_keys(cuda(x)).cpu().numpy(), O.ordered_keys(x))
+    fin = x[np.isfinite(x)]
+    assert (np.diff(fin[np.argsort(O.ordered_keys(fin), kind="stable")]) >= 0).all()   # key order = float order
+
+    n, cells, slots, slab = 77, 301, 12, 128
+    s = (rng.standard_normal((n, cells)) * 2).astype(np.float32)
+    s[:, 1] = 0.5
+    srt = np.sort(s, axis=0)
+    lo = O.ordered_keys(srt[n - 14])
+    hi = O.ordered_keys(srt[n - 6])
+    lo[2], hi[2] = O.ordered_keys(srt[5, 2:3])[0], O.ordered_keys(srt[40, 2:3])[0]      # 36 inside: overflow
+    hi[4] = O.ordered_keys(np.array([np.nan], dtype=np.float32))[0]                       # a rank saw a NaN
+    want_win, want_cnt, want_ov = O.window_compact(s, lo, hi, slots, slab)
+    ov = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ov_cells = torch.full((8,), -1, dtype=torch.int32, device="cuda")
+    win, cnt = ops.window_compact(cuda(s), cuda(lo), cuda(hi), slots, slab, ov, ov_cells)
+    np.testing.assert_array_equal(cnt.cpu().numpy(), want_cnt)
+    np.testing.assert_array_equal(win.cpu().numpy(), want_win)
+    assert int(ov.item()) == len(want_ov) == 2            # cell 2 and the all-ties cell 1
+    assert sorted(ov_cells.cpu().numpy()[:2].tolist()) == want_ov == [1, 2]
+    assert (cnt.cpu().numpy()[cells:] == 1 << 24).all()   # padding tail of the ragged last slab
+
+    rows, c2 = 96, 210
+    cand = (rng.standard_normal((rows, c2)) * 3).astype(np.float32)
+    cand[rng.integers(0, rows, 40), rng.integers(0, c2, 40)] = -np.inf
+    packed = rng.integers(0, 20, c2).astype(np.int32)
+    packed[7] |= 1 << 24
+    packed[9] = 0                                         # want = kt: fine
+    packed[11] = 25                                       # want < 1: overflow
+    kt = 21
+    want_out, want_ov = O.select_from_top(cand, packed, kt)
+    ov.zero_()
+    ov_cells.fill_(-1)
+    got = ops.select_from_top(cuda(cand), cuda(packed), kt, ov, ov_cells, 1000).cpu().numpy()
+    np.testing.assert_array_equal(got, want_out)
+    assert int(ov.item()) == len(want_ov) >= 1
+    assert sorted(ov_cells.cpu().numpy()[:len(want_ov)].tolist()) == [1000 + c for c in want_ov]
+    # packing form: blocks that are mostly -inf padding, a network smaller than the row count,
+    # a column with more real candidates than the network, a rank that lands in the padding
+    for rows, network in ((80, 32), (160, 64), (320, 128), (320, 256), (40, 32)):
+        cand = np.full((rows, c2), -np.inf, dtype=np.float32)
+        for c in range(c2):
+            m = int(rng.integers(0, min(network, rows) + 1))
+            cand[rng.choice(rows, m, replace=False), c] = (rng.standard_normal(m) * 2).astype(np.float32)
+        cand[:, 3] = np.arange(rows, dtype=np.float32)                        # rows real candidates
+        packed = rng.integers(0, 10, c2).astype(np.int32)
+        packed[5] |= 1 << 24
+        kt = 14
+        want_out, want_ov = O.select_from_top(cand, packed, kt, network)
+        ov.zero_()
+        got = ops.select_from_top(cuda(cand), cuda(packed), kt, ov, ov_cells, 0, network).cpu().numpy()
+        np.testing.assert_array_equal(got, want_out, err_msg=f"rows={rows} network={network}")
+        assert int(ov.item()) == len(want_ov) == (1 if rows > network else 0)
+
+
+@pytest.mark.parametrize("world,n_loc,alpha", [(2, 256, 0.1), (8, 64, 0.1), (4, 100, 0.05), (3, 50, 0.5)])
+def test_window_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alpha):
+    """The multi-GPU marginal quantile with its CUDA kernels, the ranks emulated one after the
+    other on this GPU (collectives done by hand): bit-equal to np.quantile over the union."""
+    rng = np.random.default_rng(world * 1000 + n_loc)
+    cells = 1000
+    full = np.abs(rng.standard_normal((world * n_loc, cells))).astype(np.float32)
+    full[rng.integers(0, world * n_loc, 4), 3] = 0.75
+    N = world * n_loc
+    k = O.calibrate_rank(N, N, alpha)
+    kt, slots = N - k, 32
+    J = -(-kt // world)
+    shards = [cuda(full[r * n_loc:(r + 1) * n_loc]) for r in range(world)]
+    keys = torch.stack([ops.ordered_keys(ops.select_ranks(s, [n_loc - J])[0]) for s in shards])
+    lo, hi = keys.min(0).values, keys.max(0).values
+    slab = -(-cells // world)
+    ov = torch.zeros(1, dtype=torch.int32, device="cuda")
+    cells_ov = torch.full((64,), -1, dtype=torch.int32, device="cuda")
+    wins, cnts = zip(*[ops.window_compact(s, lo, hi, slots, slab, ov, cells_ov) for s in shards])
+    cnt = torch.stack(cnts).sum(0).to(torch.int32)
+    q = []
+    for me in range(world):                                # all-to-all: block `me` of every rank
+        cand = torch.cat([w[me] for w in wins])            # [world*slots, slab]
+        q.append(ops.select_from_top(cand, cnt[me * slab:(me + 1) * slab], kt, ov, cells_ov, me * slab,
+                                     D.owner_network(world, slots)))
+    got = torch.cat(q)[:cells].cpu().numpy()
+    if int(ov.item()) == 0:
+        np.testing.assert_array_equal(got, O.calibrate(full, N, alpha))
+    else:                                                  # a bracket wider than 32 slots is reported, never silent
+        assert alpha == 0.5
