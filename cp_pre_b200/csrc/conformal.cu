@@ -4,6 +4,7 @@
 // Layout: score / residual tensors are [n, cells] with cells contiguous, so "thread = cell,
 // loop over samples" gives fully coalesced 128-byte warp accesses on every row.
 #include <cstdlib>
+#include <cstring>
 #include <initializer_list>
 
 #include "common.cuh"
@@ -559,11 +560,20 @@ __device__ __forceinline__ uint32_t ordered_key(float v) {
     return bits ^ ((uint32_t)((int32_t)bits >> 31) | 0x80000000u);
 }
 
+// Fused exchange: with peers.n > 0 the candidate block of cell slab r is stored straight into
+// rank r's receive buffer (peer memory over NVLink / NVSwitch, base pointers from a symmetric
+// allocation) at [me][W][slab] -- the all-to-all happens inside this kernel, store by store,
+// while the scan of the local scores keeps the SMs busy.
+struct PeerBufs {
+    float* base[16];
+    int32_t n, me;
+};
+
 __global__ void __launch_bounds__(128)
 window_compact_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells,
                       const int32_t* __restrict__ lo, const int32_t* __restrict__ hi, int32_t W, int64_t slab,
                       float* __restrict__ win, int32_t* __restrict__ cnt, uint32_t* overflow,
-                      int32_t* __restrict__ overflow_cells, int32_t overflow_cap) {
+                      int32_t* __restrict__ overflow_cells, int32_t overflow_cap, const PeerBufs peers) {
     extern __shared__ float slots[];                 // [W][128]
     const int tid = threadIdx.x;
     const int64_t c = (int64_t)blockIdx.x * 128 + tid;
@@ -598,7 +608,8 @@ window_compact_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_
         inside = (uint32_t)W;
     }
     cnt[c] = (int32_t)(above | (open ? 1u << 24 : 0u));
-    float* dst = win + (c / slab) * (int64_t)W * slab + c % slab;
+    float* dst = peers.n > 0 ? peers.base[c / slab] + (int64_t)peers.me * W * slab + c % slab
+                             : win + (c / slab) * (int64_t)W * slab + c % slab;
     for (int s = 0; s < W; ++s)
         dst[(int64_t)s * slab] = (uint32_t)s < inside ? slots[s * 128 + tid] : __uint_as_float(0xff800000u);
 }
@@ -822,7 +833,21 @@ int cppre_ordered_keys(const float* d_x, int64_t n, int32_t* d_out, void* stream
 int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
                          const int32_t* d_lo, const int32_t* d_hi, int32_t slots, int64_t slab,
                          float* d_win, int32_t* d_cnt, uint32_t* d_overflow, int32_t* d_overflow_cells,
-                         int32_t overflow_cap, void* stream) {
+                         int32_t overflow_cap, float* const* h_peer_win, int32_t n_peers, int32_t my_rank,
+                         void* stream) {
+    PeerBufs peers;
+    memset(&peers, 0, sizeof(peers));
+    if (h_peer_win != nullptr) {
+        CPPRE_REQUIRE(n_peers >= 1 && n_peers <= 16 && my_rank >= 0 && my_rank < n_peers, CPPRE_ERR_BAD_ARG,
+                      "bad peer list (n=%d me=%d)", n_peers, my_rank);
+        CPPRE_REQUIRE((cells + slab - 1) / slab <= n_peers, CPPRE_ERR_BAD_ARG, "more cell slabs than peers");
+        for (int r = 0; r < n_peers; ++r) {
+            CPPRE_REQUIRE(h_peer_win[r] != nullptr, CPPRE_ERR_BAD_ARG, "peer %d has no buffer", r);
+            peers.base[r] = h_peer_win[r];
+        }
+        peers.n = n_peers;
+        peers.me = my_rank;
+    }
     CPPRE_REQUIRE(cells < (int64_t(1) << 31) && overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells),
                   CPPRE_ERR_BAD_ARG, "bad overflow list");
     CPPRE_REQUIRE(n >= 0 && cells >= 0 && slots >= 1 && slots <= 96 && slab >= 1, CPPRE_ERR_BAD_ARG,
@@ -830,8 +855,8 @@ int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, i
                   (long long)slab);
     CPPRE_REQUIRE(n < (int64_t(1) << 24), CPPRE_ERR_UNSUPPORTED, "n too large for the packed count");
     if (cells == 0) return CPPRE_OK;
-    CPPRE_REQUIRE((d_scores || n == 0) && d_lo && d_hi && d_win && d_cnt && d_overflow, CPPRE_ERR_BAD_ARG,
-                  "null pointer");
+    CPPRE_REQUIRE((d_scores || n == 0) && d_lo && d_hi && (d_win || peers.n > 0) && d_cnt && d_overflow,
+                  CPPRE_ERR_BAD_ARG, "null pointer");
     const int64_t blocks = (cells + 127) / 128;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
     const size_t smem = (size_t)slots * 128 * sizeof(float);
@@ -843,7 +868,7 @@ int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, i
     }
     window_compact_kernel<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
         d_scores, row_stride, (int32_t)n, cells, d_lo, d_hi, slots, slab, d_win, d_cnt, d_overflow,
-        d_overflow_cells, overflow_cap);
+        d_overflow_cells, overflow_cap, peers);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

@@ -149,7 +149,25 @@ def joint_quantile_hist(scores: torch.Tensor, rank_k: int, group=None,
 def _cuda_kernels():
     from . import ops
     return {"select": ops.select_ranks, "keys": ops.ordered_keys, "window": ops.window_compact,
-            "top": ops.select_from_top}
+            "top": ops.select_from_top, "peer_exchange": True}
+
+
+_SYMM = {}
+
+
+def _peer_recv_buffer(world: int, slots: int, slab: int, device, group):
+    """Every rank's candidate receive buffer [world, slots, slab], allocated once from CUDA
+    symmetric memory and mapped into every process of the group: (local tensor, peer base
+    pointers).  K3w stores into the peers' buffers directly (NVLink), no all-to-all call."""
+    import torch.distributed._symmetric_memory as symm
+    name = (group or dist.group.WORLD).group_name
+    key = (name, world, slots, slab, device.index)
+    if key not in _SYMM:
+        t = symm.empty((world, slots, slab), dtype=torch.float32, device=device)
+        hdl = symm.rendezvous(t, name)
+        _SYMM[key] = (t, hdl, [int(p) for p in hdl.buffer_ptrs])
+    t, _, ptrs = _SYMM[key]
+    return t, ptrs
 
 
 def _exchange_quantiles(scores: torch.Tensor, ranks: Sequence[int], group, select_fn) -> torch.Tensor:
@@ -193,25 +211,30 @@ def _window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int)
     kt = w * n - int(rank_k)
     J = -(-kt // w)
     a = kern["keys"](kern["select"](flat, [n - J])[0])        # int32 ordered keys, [cells]
-    lo, hi = a.clone(), a.clone()
-    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
-    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    both = torch.stack([~a, a])                              # one MAX all-reduce: min(a) = ~max(~a)
+    dist.all_reduce(both, op=dist.ReduceOp.MAX, group=group)
+    lo, hi = ~both[0], both[1]
     slab = (cells + w - 1) // w
     dev = scores.device
     win_over = torch.zeros(1, dtype=torch.int32, device=dev)       # cells whose bracket exceeds `slots`
     over_cells = torch.full((OVERFLOW_CAP,), -1, dtype=torch.int32, device=dev)
-    win, cnt = kern["window"](flat, lo, hi, slots, slab, win_over, over_cells)    # [w, slots, slab], [w*slab]
-    dist.all_reduce(cnt, group=group)
-    recv = torch.empty_like(win)
-    dist.all_to_all_single(recv, win, group=group)           # recv[r] = rank r's candidates of MY slab
-    n_before = win_over.clone()
+    if kern.get("peer_exchange") and scores.is_cuda and os.environ.get("CPPRE_PEER_EXCHANGE", "1") != "0":
+        # fused: K3w stores block r straight into rank r's receive buffer over NVLink; the
+        # all-reduce of the counts below is also the barrier that orders those stores
+        recv, ptrs = _peer_recv_buffer(w, slots, slab, dev, group)
+        _, cnt = kern["window"](flat, lo, hi, slots, slab, win_over, over_cells, ptrs, me)
+        dist.all_reduce(cnt, group=group)
+    else:
+        win, cnt = kern["window"](flat, lo, hi, slots, slab, win_over, over_cells)    # [w, slots, slab], [w*slab]
+        dist.all_reduce(cnt, group=group)
+        recv = torch.empty_like(win)
+        dist.all_to_all_single(recv, win, group=group)       # recv[r] = rank r's candidates of MY slab
     q_slab = kern["top"](recv.reshape(w * slots, slab), cnt[me * slab:(me + 1) * slab], kt, win_over, over_cells,
                          me * slab, owner_network(w, slots))
     parts = [torch.empty_like(q_slab) for _ in range(w)]
     dist.all_gather(parts, q_slab.contiguous(), group=group)
     q = torch.cat(parts)[:cells]
     # overflow bookkeeping, identical on every rank: cells listed by K3w and by the owner's select
-    del n_before
     counts = [torch.empty_like(win_over) for _ in range(w)]
     dist.all_gather(counts, win_over, group=group)
     counts = torch.stack(counts).cpu()

@@ -278,27 +278,33 @@ def ordered_keys(x: torch.Tensor) -> torch.Tensor:
 
 
 def window_compact(scores: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor, slots: int, slab: int,
-                   overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
+                   overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None,
+                   peer_ptrs: Optional[Sequence[int]] = None, my_rank: int = 0):
     """Second pass of the multi-GPU marginal quantile (K3w).  scores [n, cells...]; lo / hi int32
     ordered keys per cell.  Returns (win [blocks, slots, slab] float32, cnt [blocks*slab] int32);
     ``overflow`` (int32 [1], caller-zeroed) is incremented per cell with more than ``slots``
     window samples; their indices are written to ``overflow_cells`` (int32 [cap]) at the counter's
-    old value while that is below cap."""
+    old value while that is below cap.  With ``peer_ptrs`` (every rank's receive buffer
+    [world, slots, slab], mapped here) block r is stored straight into rank r's buffer at
+    [my_rank] -- the exchange is fused into the kernel -- and ``win`` is returned as None."""
     lib = L.load()
     fs, rs = _rows(scores)
     n, cells = fs.shape
     cap = 0 if overflow_cells is None else overflow_cells.numel()
     blocks = (cells + slab - 1) // slab
-    win = torch.empty((blocks, slots, slab), dtype=torch.float32, device=scores.device)
+    fused = peer_ptrs is not None
+    win = None if fused else torch.empty((blocks, slots, slab), dtype=torch.float32, device=scores.device)
     cnt = torch.zeros(blocks * slab, dtype=torch.int32, device=scores.device)
     if blocks * slab != cells:      # padding tail of the last slab: no candidates; flagged like a NaN cell
-        win[-1, :, cells - (blocks - 1) * slab:] = float("-inf")
+        if not fused:               # (fused: the owner never reads a flagged cell's candidates)
+            win[-1, :, cells - (blocks - 1) * slab:] = float("-inf")
         cnt[cells:] = 1 << 24
+    peers = (C.c_void_p * len(peer_ptrs))(*peer_ptrs) if fused else None
     with torch.cuda.device(scores.device):
         L.check(lib.cppre_window_compact(_ptr(fs), rs, n, cells, _ptr(lo.reshape(-1).contiguous()),
                                          _ptr(hi.reshape(-1).contiguous()), int(slots), int(slab), _ptr(win),
-                                         _ptr(cnt), _ptr(overflow), _ptr(overflow_cells), cap,
-                                         _stream(scores.device)))
+                                         _ptr(cnt), _ptr(overflow), _ptr(overflow_cells), cap, peers,
+                                         len(peer_ptrs) if fused else 0, int(my_rank), _stream(scores.device)))
     return win, cnt
 
 

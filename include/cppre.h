@@ -197,7 +197,12 @@ int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask
  *      [cells/slab][slots][slab] = the send buffer of an all-to-all that
  *      gives rank r the candidates of cell slab r; *d_overflow += #cells with more than `slots`
  *      samples inside, whose indices go to d_overflow_cells[old counter value] while that is
- *      below overflow_cap (the caller redoes those few cells from their full columns);
+ *      below overflow_cap (the caller redoes those few cells from their full columns).
+ *      FUSED EXCHANGE: with h_peer_win (HOST array of n_peers device pointers, each rank's
+ *      [n_peers][slots][slab] receive buffer mapped into this process, e.g. from a CUDA
+ *      symmetric-memory allocation) the block of slab r is stored directly into
+ *      h_peer_win[r][my_rank] over NVLink and d_win is not used: the all-to-all is part of the
+ *      kernel.  The all-reduce of cnt that follows orders those stores before the owner reads;
  *   3. after all-reducing cnt (SUM), the owner of a slab picks, per cell, the
  *      (kt - (cnt & 0xffffff))-th largest (1-based) of the gathered candidate rows
  *      (cppre_select_from_top); NaN where cnt >> 24 != 0.  network = 0 sorts all rows (<= 2048);
@@ -212,7 +217,8 @@ int cppre_ordered_keys(const float* d_x, int64_t n, int32_t* d_out, void* stream
 int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
                          const int32_t* d_lo, const int32_t* d_hi, int32_t slots, int64_t slab,
                          float* d_win, int32_t* d_cnt, uint32_t* d_overflow, int32_t* d_overflow_cells,
-                         int32_t overflow_cap, void* stream);
+                         int32_t overflow_cap, float* const* h_peer_win, int32_t n_peers, int32_t my_rank,
+                         void* stream);
 int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows, int64_t cells,
                           const int32_t* d_cnt, int32_t kt, int32_t network, float* d_out,
                           uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap,
