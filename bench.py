@@ -53,6 +53,20 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def k1_traffic(workload):
+    """DRAM bytes per K1 STORE launch from the committed `ncu --set full` capture (dram__bytes_read.sum +
+    dram__bytes_write.sum), or None when no capture of this workload is committed."""
+    p = os.path.join(ROOT, "profiles", "r01_k1_traffic.json")
+    try:
+        d = json.load(open(p))
+        if d.get("workload") == workload:
+            return {"bytes": d["dram_bytes_read"] + d["dram_bytes_write"], "read": d["dram_bytes_read"],
+                    "write": d["dram_bytes_write"], "algorithmic": d["algorithmic_bytes"], "source": d["source"]}
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (recipe in B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -303,6 +317,8 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly one JSON line: NCCL's version banner / debug output goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     from cp_pre_b200 import _lib, dist as D
     rank, world, device = D.init_from_env()
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
@@ -399,7 +415,8 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "star_kernel<NS_MOMENTUM> (K1: TMA stencil + |.| epilogue, STORE)"
                          if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "bytes_per_point": bpp,
+                         "traffic": (k1_traffic(args.workload) or {}).get("bytes"), "traffic_detail": k1_traffic(args.workload),
+                         "peak_source": peak_src, "bytes_per_point": bpp,
                          "kernel_ms": k1_ms, "kernel_gpoints_s": k1_pts / (k1_ms * 1e-3) / 1e9,
                          "points_per_launch": k1_pts, "share_of_step": k1_ms / ms,
                          "cover_kernel": {"what": "same K1 kernel, COVER epilogue (no residual written), validation half",
