@@ -317,8 +317,11 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
-    # stdout carries exactly one JSON line: NCCL's version banner / debug output goes to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: anything a library prints meanwhile (NCCL's version
+    # banner at communicator creation) is sent to stderr by pointing fd 1 there until the end
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     from cp_pre_b200 import _lib, dist as D
     rank, world, device = D.init_from_env()
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
@@ -392,6 +395,8 @@ def main():
                "path": "pinned host batch -> 32-sample double-buffered H2D overlapped with K1 -> K3/K5 -> qhat+coverage D2H"}
         del ee
 
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     if rank == 0:
         peak, peak_src = peaks()
         bpp = 4 * step.nf + 4
@@ -424,6 +429,8 @@ def main():
                                           "frac": cover_gbs / peak, "share_of_step": k1c_ms / ms}},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
         }))
+    sys.stdout.flush()
+    os.dup2(2, 1)
     if world > 1:
         torch.distributed.destroy_process_group()
 

@@ -620,6 +620,211 @@ ordered_keys_kernel(const float* __restrict__ x, int64_t n, int32_t* __restrict_
     if (i < n) out[i] = (int32_t)(ordered_key(x[i]) ^ 0x80000000u);
 }
 
+// ------------------------------------------------------------------------------------------
+// K3x: the multi-GPU marginal quantile with every exchange fused into the kernels (peer memory
+// over NVLink / NVSwitch, base pointers from CUDA symmetric allocations).  Three kernels, each
+// followed by a barrier on the host side (a one-word all-reduce); no data-carrying collective:
+//   peer_bcast_keys_kernel   key(a_r[c]) -> every peer's keys[me][c]
+//   window_exchange_kernel   lo/hi = min/max of the w keys of the cell (read locally); scan the
+//                            local column once; header (#above, #inside, NaN flag) + the
+//                            candidates inside [lo, hi] -> the owner's recv[me][1+W][slab]; only
+//                            as many candidate rows as the fullest cell of the warp are stored
+//   owner_select_kernel      owner of a cell slab: pack the w candidate lists of each cell, sort
+//                            one small network, pick the (kt - sum above)-th largest, store it
+//                            into every peer's q[c]  (the all-gather of qhat, fused)
+// ------------------------------------------------------------------------------------------
+struct PeerPtrs {
+    void* base[16];
+    int32_t n, me;
+};
+
+template <int V>
+__global__ void __launch_bounds__(kThreads)
+peer_bcast_keys_kernel(const float* __restrict__ a, int64_t cells, int64_t cells_pad, const PeerPtrs peers) {
+    const int64_t c = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * V;
+    if (c >= cells) return;
+    uint32_t k[V];
+    if constexpr (V == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(a + c));
+        k[0] = ordered_key(t.x); k[1] = ordered_key(t.y); k[2] = ordered_key(t.z); k[3] = ordered_key(t.w);
+    } else {
+        k[0] = ordered_key(__ldg(a + c));
+    }
+    for (int r = 0; r < peers.n; ++r) {
+        uint32_t* dst = reinterpret_cast<uint32_t*>(peers.base[r]) + (int64_t)peers.me * cells_pad + c;
+        if constexpr (V == 4) *reinterpret_cast<uint4*>(dst) = make_uint4(k[0], k[1], k[2], k[3]);
+        else *dst = k[0];
+    }
+}
+
+// header word of a (rank, cell) candidate list
+__device__ __forceinline__ uint32_t pack_header(uint32_t above, uint32_t inside, bool open) {
+    return (above & 0xffffffu) | (inside << 24) | (open ? 0x80000000u : 0u);
+}
+
+__global__ void __launch_bounds__(128)
+window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells,
+                       const uint32_t* keys, int64_t cells_pad, int32_t W, int64_t slab, uint32_t* overflow,
+                       int32_t* __restrict__ overflow_cells, int32_t overflow_cap, const PeerPtrs peers) {
+    extern __shared__ float slots[];                 // [W][128]
+    const int tid = threadIdx.x;
+    const int64_t c = (int64_t)blockIdx.x * 128 + tid;
+    const bool live = c < cells;
+    uint32_t klo = 0xffffffffu, khi = 0u;
+    if (live)
+        for (int r = 0; r < peers.n; ++r) {          // peer-written: read through L2, never the nc path
+            const uint32_t k = __ldcg(keys + (int64_t)r * cells_pad + c);
+            klo = min(klo, k);
+            khi = max(khi, k);
+        }
+    const uint32_t span = khi - klo;
+    const bool open = khi > 0xff800000u;             // some rank saw a NaN in this cell: the answer is NaN
+    uint32_t above = 0u, inside = 0u;
+    if (live && !open) {
+        const float* px = x + c;
+        auto take = [&](float v) {
+            const uint32_t key = ordered_key(v);
+            above += key > khi ? 1u : 0u;
+            if (key - klo <= span) {
+                if (inside < (uint32_t)W) slots[inside * 128 + tid] = v;
+                ++inside;
+            }
+        };
+        int32_t i = 0;
+        for (; i + 16 <= n; i += 16) {
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) { v[u] = __ldg(px); px += xs; }
+#pragma unroll
+            for (int u = 0; u < 16; ++u) take(v[u]);
+        }
+        for (; i < n; ++i) { take(__ldg(px)); px += xs; }
+    }
+    if (inside > (uint32_t)W) {                      // reported with the cell index: the caller redoes these exactly
+        const uint32_t at = atomicAdd(overflow, 1u);
+        if (at < (uint32_t)overflow_cap) overflow_cells[at] = (int32_t)c;
+        inside = (uint32_t)W;
+    }
+    const uint32_t rows = __reduce_max_sync(0xffffffffu, inside);
+    if (!live) return;
+    float* dst = reinterpret_cast<float*>(peers.base[c / slab]) + (int64_t)peers.me * (W + 1) * slab + c % slab;
+    dst[0] = __uint_as_float(pack_header(above, inside, open));
+    for (uint32_t s = 0; s < rows; ++s)
+        if (s < inside) dst[(int64_t)(s + 1) * slab] = slots[s * 128 + tid];
+}
+
+// Owner side.  recv = [w][1 + W][slab]: row 0 of block r holds rank r's headers, rows 1.. its
+// candidates (only the first `inside` of a column are meaningful; the rest is stale memory and is
+// never read).  One CTA handles TC cells with the register network of select_regsort_kernel:
+// the fill packs each cell's candidates to the front of its tile column (shared-memory atomics
+// hand out the positions), padding keys (0) sort first.
+template <int L, int R, int TC>
+__global__ void __launch_bounds__(TC * L)
+owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64_t cells, int32_t kt,
+                    int64_t cell_offset, uint32_t* overflow, int32_t* __restrict__ overflow_cells,
+                    int32_t overflow_cap, const PeerPtrs qpeers) {
+    constexpr int N = L * R;
+    constexpr int THREADS = TC * L;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int CW = 32 / L;
+    constexpr int LD = TC + 1;
+    static_assert(TC == 32 && CW * WARPS == TC, "bad tiling");
+    extern __shared__ uint32_t tile[];      // [N][LD] keys, then per column: count, above, flag; then w*TC list lengths
+    uint32_t* colcount = tile + N * LD;
+    uint32_t* above = colcount + TC;
+    uint32_t* flag = above + TC;
+    uint32_t* len = flag + TC;              // [w][TC]
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t c0 = (int64_t)blockIdx.x * TC;
+    for (int e = tid; e < N * LD; e += THREADS) tile[e] = 0u;
+    if (tid < TC) { colcount[tid] = 0u; above[tid] = 0u; flag[tid] = 0u; }
+    __syncthreads();
+    const int64_t block = (int64_t)(W + 1) * slab;
+    for (int e = tid; e < w * TC; e += THREADS) {
+        const int r = e / TC, col = e % TC;
+        uint32_t l = 0u;
+        if (c0 + col < cells) {
+            const uint32_t h = __float_as_uint(__ldcg(recv + (int64_t)r * block + c0 + col));
+            atomicAdd(&above[col], h & 0xffffffu);
+            if (h >> 31) flag[col] = 1u;
+            l = (h >> 24) & 0x7fu;
+        }
+        len[e] = l;
+    }
+    __syncthreads();
+    {
+        const int col = lane;
+        const bool live = c0 + col < cells;
+        for (int row = wid; row < w * W; row += WARPS) {
+            const int r = row / W, sl = row - r * W;
+            if (!live || (uint32_t)sl >= len[r * TC + col]) continue;
+            const uint32_t bits = __float_as_uint(__ldcg(recv + (int64_t)r * block + (int64_t)(1 + sl) * slab + c0 + col));
+            const uint32_t pos = atomicAdd(&colcount[col], 1u);
+            if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits);
+        }
+    }
+    __syncthreads();
+    const int j = lane % L, i = lane / L;
+    const int ct = wid + WARPS * i;
+    uint32_t k[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) k[r] = tile[(r * L + j) * LD + ct];
+    bitonic_sort_regs<L, R>(k, j);
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < R; ++r) tile[(r * L + j) * LD + ct] = k[r];
+    __syncthreads();
+    if (tid < TC && c0 + tid < cells) {
+        const int want = kt - (int)above[tid];
+        const int have = (int)colcount[tid];
+        bool nan = flag[tid] != 0u;
+        if (!nan && (want < 1 || want > have || have > N)) {   // bracket missed or a list was cut: redo exactly
+            const uint32_t at = atomicAdd(overflow, 1u);
+            if (at < (uint32_t)overflow_cap) overflow_cells[at] = (int32_t)(cell_offset + c0 + tid);
+            nan = true;
+        }
+        const int kq = nan ? 0 : N - want;
+        const uint32_t v = tile[((kq % R) * L + kq / R) * LD + tid];
+        const float q = nan ? __uint_as_float(0x7fc00000u) : __uint_as_float(key_to_float_bits(v));
+        for (int r = 0; r < qpeers.n; ++r)
+            reinterpret_cast<float*>(qpeers.base[r])[cell_offset + c0 + tid] = q;
+    }
+}
+
+template <int L, int R>
+int launch_owner(const float* recv, int32_t w, int32_t W, int64_t slab, int64_t cells, int32_t kt,
+                 int64_t cell_offset, uint32_t* overflow, int32_t* overflow_cells, int32_t cap,
+                 const PeerPtrs& qpeers, cudaStream_t st) {
+    constexpr int N = L * R, TC = 32;
+    const size_t smem = ((size_t)N * (TC + 1) + 3 * TC + (size_t)w * TC) * sizeof(uint32_t);
+    auto kern = owner_select_kernel<L, R, TC>;
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    const int64_t blocks = (cells + TC - 1) / TC;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    kern<<<(unsigned)blocks, TC * L, smem, st>>>(recv, w, W, slab, cells, kt, cell_offset, overflow, overflow_cells,
+                                                 cap, qpeers);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int fill_peers(PeerPtrs* P, void* const* h_ptrs, int32_t n_peers, int32_t my_rank) {
+    memset(P, 0, sizeof(*P));
+    CPPRE_REQUIRE(h_ptrs != nullptr && n_peers >= 1 && n_peers <= 16 && my_rank >= 0 && my_rank < n_peers,
+                  CPPRE_ERR_BAD_ARG, "bad peer list (n=%d me=%d)", n_peers, my_rank);
+    for (int r = 0; r < n_peers; ++r) {
+        CPPRE_REQUIRE(h_ptrs[r] != nullptr, CPPRE_ERR_BAD_ARG, "peer %d has no buffer", r);
+        P->base[r] = h_ptrs[r];
+    }
+    P->n = n_peers;
+    P->me = my_rank;
+    return CPPRE_OK;
+}
+
 // K3b: per-cell single-rank radix select straight from global memory (any n).  8 passes of
 // 4 bits; the 16 bucket counters are compared-and-added so they stay in registers.
 __global__ void __launch_bounds__(kThreads)
@@ -891,6 +1096,84 @@ int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows,
     CPPRE_REQUIRE(rc >= 0, CPPRE_ERR_UNSUPPORTED, "unsupported candidate select (rows=%lld network=%d)",
                   (long long)rows, network);
     return rc;
+}
+
+int cppre_peer_bcast_keys(const float* d_vals, int64_t cells, int64_t cells_pad, void* const* h_peer_keys,
+                          int32_t n_peers, int32_t my_rank, void* stream) {
+    PeerPtrs peers;
+    const int rc = fill_peers(&peers, h_peer_keys, n_peers, my_rank);
+    if (rc != CPPRE_OK) return rc;
+    CPPRE_REQUIRE(cells >= 0 && cells_pad >= cells && cells_pad % 4 == 0, CPPRE_ERR_BAD_ARG, "bad size");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_vals != nullptr, CPPRE_ERR_BAD_ARG, "null pointer");
+    bool v4 = cells % 4 == 0 && (reinterpret_cast<uintptr_t>(d_vals) & 15u) == 0;
+    for (int r = 0; r < n_peers; ++r) v4 = v4 && (reinterpret_cast<uintptr_t>(h_peer_keys[r]) & 15u) == 0;
+    const int64_t items = v4 ? cells / 4 : cells;
+    const int64_t blocks = (items + kThreads - 1) / kThreads;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    if (v4)
+        peer_bcast_keys_kernel<4><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_vals, cells, cells_pad, peers);
+    else
+        peer_bcast_keys_kernel<1><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_vals, cells, cells_pad, peers);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                          const uint32_t* d_keys, int64_t cells_pad, int32_t slots, int64_t slab,
+                          void* const* h_peer_recv, int32_t n_peers, int32_t my_rank, uint32_t* d_overflow,
+                          int32_t* d_overflow_cells, int32_t overflow_cap, void* stream) {
+    PeerPtrs peers;
+    const int rc = fill_peers(&peers, h_peer_recv, n_peers, my_rank);
+    if (rc != CPPRE_OK) return rc;
+    CPPRE_REQUIRE(n >= 0 && cells >= 0 && slots >= 1 && slots <= 96 && slab >= 1 && cells_pad >= cells,
+                  CPPRE_ERR_BAD_ARG, "bad size (n=%lld cells=%lld slots=%d slab=%lld)", (long long)n,
+                  (long long)cells, slots, (long long)slab);
+    CPPRE_REQUIRE((cells + slab - 1) / slab <= n_peers, CPPRE_ERR_BAD_ARG, "more cell slabs than peers");
+    CPPRE_REQUIRE(cells < (int64_t(1) << 31) && overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells),
+                  CPPRE_ERR_BAD_ARG, "bad overflow list");
+    CPPRE_REQUIRE(n < (int64_t(1) << 24), CPPRE_ERR_UNSUPPORTED, "n too large for the packed count");
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE((d_scores || n == 0) && d_keys && d_overflow, CPPRE_ERR_BAD_ARG, "null pointer");
+    const int64_t blocks = (cells + 127) / 128;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    const size_t smem = (size_t)slots * 128 * sizeof(float);
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem));
+        configured = smem;
+    }
+    window_exchange_kernel<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
+        d_scores, row_stride, (int32_t)n, cells, d_keys, cells_pad, slots, slab, d_overflow, d_overflow_cells,
+        overflow_cap, peers);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_owner_select(const float* d_recv, int32_t n_ranks, int32_t slots, int64_t slab, int64_t cells,
+                       int32_t kt, int32_t network, int64_t cell_offset, void* const* h_peer_q, int32_t n_peers,
+                       uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap, void* stream) {
+    PeerPtrs qp;
+    const int rc0 = fill_peers(&qp, h_peer_q, n_peers, 0);
+    if (rc0 != CPPRE_OK) return rc0;
+    CPPRE_REQUIRE(n_ranks >= 1 && n_ranks <= 16 && slots >= 1 && slots <= 96 && slab >= 1 && cells <= slab,
+                  CPPRE_ERR_BAD_ARG, "bad size");
+    CPPRE_REQUIRE(overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells), CPPRE_ERR_BAD_ARG, "bad overflow list");
+    if (cells <= 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_recv && d_overflow, CPPRE_ERR_BAD_ARG, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (network) {
+        case 32: return launch_owner<1, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        case 64: return launch_owner<2, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        case 128: return launch_owner<4, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        case 256: return launch_owner<8, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        case 512: return launch_owner<16, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        case 1024: return launch_owner<32, 32>(d_recv, n_ranks, slots, slab, cells, kt, cell_offset, d_overflow, d_overflow_cells, overflow_cap, qp, st);
+        default: break;
+    }
+    CPPRE_REQUIRE(false, CPPRE_ERR_UNSUPPORTED, "network must be a power of two in [32, 1024] (got %d)", network);
+    return CPPRE_ERR_UNSUPPORTED;
 }
 
 int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,

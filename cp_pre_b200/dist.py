@@ -149,25 +149,93 @@ def joint_quantile_hist(scores: torch.Tensor, rank_k: int, group=None,
 def _cuda_kernels():
     from . import ops
     return {"select": ops.select_ranks, "keys": ops.ordered_keys, "window": ops.window_compact,
-            "top": ops.select_from_top, "peer_exchange": True}
+            "top": ops.select_from_top, "peer_exchange": True, "bcast_keys": ops.peer_bcast_keys,
+            "window_x": ops.window_exchange, "owner": ops.owner_select}
 
 
 _SYMM = {}
 
 
-def _peer_recv_buffer(world: int, slots: int, slab: int, device, group):
-    """Every rank's candidate receive buffer [world, slots, slab], allocated once from CUDA
-    symmetric memory and mapped into every process of the group: (local tensor, peer base
-    pointers).  K3w stores into the peers' buffers directly (NVLink), no all-to-all call."""
+def _symm_buffer(tag: str, shape, dtype, device, group):
+    """A buffer of CUDA symmetric memory, allocated once per (group, shape) and mapped into every
+    process of the group: (local tensor, every rank's base pointer as seen from this process)."""
     import torch.distributed._symmetric_memory as symm
     name = (group or dist.group.WORLD).group_name
-    key = (name, world, slots, slab, device.index)
+    key = (tag, name, tuple(shape), dtype, device.index)
     if key not in _SYMM:
-        t = symm.empty((world, slots, slab), dtype=torch.float32, device=device)
+        t = symm.empty(tuple(shape), dtype=dtype, device=device)
         hdl = symm.rendezvous(t, name)
         _SYMM[key] = (t, hdl, [int(p) for p in hdl.buffer_ptrs])
     t, _, ptrs = _SYMM[key]
     return t, ptrs
+
+
+def _peer_recv_buffer(world: int, slots: int, slab: int, device, group):
+    """Every rank's candidate receive buffer [world, slots, slab] (K3w stores into the peers'
+    buffers directly over NVLink, no all-to-all call)."""
+    return _symm_buffer("recv", (world, slots, slab), torch.float32, device, group)
+
+
+def _barrier(flag: torch.Tensor, group):
+    """Orders the peer stores of the kernel just enqueued before the peers' next kernel: a
+    one-word all-reduce on the same stream (nothing else travels)."""
+    dist.all_reduce(flag, group=group)
+
+
+def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int):
+    """K3x: `_window_quantile` with every exchange inside the kernels (include/cppre.h).  Per
+    quantile: K3t local order statistic -> keys stored into every peer -> barrier -> window scan,
+    headers + candidates stored into the owners -> barrier -> owner select, qhat stored into
+    every peer -> all-gather of the overflow counters (the last barrier).  Same bracket argument
+    and the same exact redo of overflowing cells as `_window_quantile`."""
+    w = _world(group)
+    me = dist.get_rank(group)
+    n = scores.shape[0]
+    flat = scores.reshape(n, -1)
+    cells = flat.shape[1]
+    dev = scores.device
+    kt = w * n - int(rank_k)
+    J = -(-kt // w)
+    slab = (cells + w - 1) // w
+    cells_pad = (slab * w + 3) // 4 * 4
+    keys, key_ptrs = _symm_buffer("keys", (w, cells_pad), torch.int32, dev, group)
+    recv, recv_ptrs = _symm_buffer("recvx", (w, 1 + slots, slab), torch.float32, dev, group)
+    qbuf, q_ptrs = _symm_buffer("q", (cells_pad,), torch.float32, dev, group)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    over = torch.zeros(1, dtype=torch.int32, device=dev)
+    over_cells = torch.full((OVERFLOW_CAP,), -1, dtype=torch.int32, device=dev)
+
+    a = kern["select"](flat, [n - J])[0]
+    kern["bcast_keys"](a, cells_pad, key_ptrs, me)
+    _barrier(flag, group)
+    kern["window_x"](flat, keys, slots, slab, recv_ptrs, me, over, over_cells)
+    _barrier(flag, group)
+    live = max(0, min(slab, cells - me * slab))
+    kern["owner"](recv, live, kt, owner_network(w, slots), me * slab, q_ptrs, over, over_cells)
+    counts = [torch.empty_like(over) for _ in range(w)]
+    dist.all_gather(counts, over, group=group)                # also the barrier that orders the q stores
+    q = qbuf[:cells].clone()
+    counts = torch.stack(counts).cpu()
+    if int(counts.sum()) == 0:
+        return q
+    if int(counts.max()) > OVERFLOW_CAP:
+        return None
+    return _redo_cells(flat, q, over_cells, rank_k, group, kern["select"])
+
+
+def _redo_cells(flat, q, over_cells, rank_k, group, select_fn):
+    """Cells on some rank's overflow list, redone exactly from their gathered full columns."""
+    w = _world(group)
+    cells = flat.shape[1]
+    lists = [torch.empty_like(over_cells) for _ in range(w)]
+    dist.all_gather(lists, over_cells, group=group)
+    ids = torch.unique(torch.cat(lists))
+    ids = ids[(ids >= 0) & (ids < cells)].to(torch.int64)
+    cols = flat[:, ids].contiguous()
+    allcols = [torch.empty_like(cols) for _ in range(w)]
+    dist.all_gather(allcols, cols, group=group)
+    q[ids] = select_fn(torch.cat(allcols), [int(rank_k)])[0].to(q.dtype)
+    return q
 
 
 def _exchange_quantiles(scores: torch.Tensor, ranks: Sequence[int], group, select_fn) -> torch.Tensor:
@@ -242,16 +310,7 @@ def _window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int)
         return q
     if int(counts.max()) > OVERFLOW_CAP:
         return None                                          # too many: the caller transposes everything
-    # redo the few overflowing cells from their full columns (exact): union of the rank lists
-    lists = [torch.empty_like(over_cells) for _ in range(w)]
-    dist.all_gather(lists, over_cells, group=group)
-    ids = torch.unique(torch.cat(lists))
-    ids = ids[(ids >= 0) & (ids < cells)].to(torch.int64)
-    cols = flat[:, ids].contiguous()
-    allcols = [torch.empty_like(cols) for _ in range(w)]
-    dist.all_gather(allcols, cols, group=group)
-    q[ids] = kern["select"](torch.cat(allcols), [int(rank_k)])[0].to(q.dtype)
-    return q
+    return _redo_cells(flat, q, over_cells, rank_k, group, kern["select"])
 
 
 OVERFLOW_CAP = 8192
@@ -292,7 +351,8 @@ def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
         return q.reshape((len(ranks),) + cell_shape)
     out = []
     for k in ranks:
-        q = _window_quantile(scores, k, group, kernels, slots)
+        fused = ("owner" in kernels and scores.is_cuda and os.environ.get("CPPRE_FUSED_EXCHANGE", "1") != "0")
+        q = (_fused_window_quantile if fused else _window_quantile)(scores, k, group, kernels, slots)
         if q is None:
             if mode == "window":
                 raise RuntimeError(f"candidate window overflowed in more than {OVERFLOW_CAP} cells (slots={slots})")

@@ -326,6 +326,46 @@ def select_from_top(cand: torch.Tensor, cnt: torch.Tensor, kt: int, overflow: to
     return out
 
 
+def _ptr_array(ptrs: Sequence[int]):
+    return (C.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
+
+
+def peer_bcast_keys(vals: torch.Tensor, cells_pad: int, peer_keys: Sequence[int], my_rank: int):
+    """K3x-1: ordered uint32 key of vals[c] -> every peer's key buffer [world, cells_pad] at [my_rank, c]."""
+    lib = L.load()
+    v = vals.reshape(-1).contiguous()
+    with torch.cuda.device(v.device):
+        L.check(lib.cppre_peer_bcast_keys(_ptr(v), v.numel(), int(cells_pad), _ptr_array(peer_keys), len(peer_keys),
+                                          int(my_rank), _stream(v.device)))
+
+
+def window_exchange(scores: torch.Tensor, keys: torch.Tensor, slots: int, slab: int, peer_recv: Sequence[int],
+                    my_rank: int, overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
+    """K3x-2: scores [n, cells...]; keys = this rank's [world, cells_pad] key buffer (int32 storage of uint32
+    keys).  Headers + candidates go straight into the owners' receive buffers [world, 1+slots, slab]."""
+    lib = L.load()
+    fs, rs = _rows(scores)
+    n, cells = fs.shape
+    cap = 0 if overflow_cells is None else overflow_cells.numel()
+    with torch.cuda.device(scores.device):
+        L.check(lib.cppre_window_exchange(_ptr(fs), rs, n, cells, _ptr(keys), int(keys.shape[1]), int(slots), int(slab),
+                                          _ptr_array(peer_recv), len(peer_recv), int(my_rank), _ptr(overflow),
+                                          _ptr(overflow_cells), cap, _stream(scores.device)))
+
+
+def owner_select(recv: torch.Tensor, cells: int, kt: int, network: int, cell_offset: int, peer_q: Sequence[int],
+                 overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
+    """K3x-3: recv = this rank's [world, 1+slots, slab] receive buffer; the answers of its `cells` live
+    cells are stored into every peer's q buffer at [cell_offset + c]."""
+    lib = L.load()
+    w, rows, slab = recv.shape
+    cap = 0 if overflow_cells is None else overflow_cells.numel()
+    with torch.cuda.device(recv.device):
+        L.check(lib.cppre_owner_select(_ptr(recv), int(w), int(rows - 1), int(slab), int(cells), int(kt), int(network),
+                                       int(cell_offset), _ptr_array(peer_q), len(peer_q), _ptr(overflow),
+                                       _ptr(overflow_cells), cap, _stream(recv.device)))
+
+
 def radix_hist(x: torch.Tensor, prefix: int, mask: int, shift: int, hist: torch.Tensor):
     lib = L.load()
     flat = x.reshape(-1).contiguous()

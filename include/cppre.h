@@ -224,6 +224,38 @@ int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows,
                           uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap,
                           int64_t cell_offset, void* stream);
 
+/* K3x: the same protocol with EVERY exchange fused into the kernels (peer memory over NVLink /
+ * NVSwitch; each h_peer_* is a HOST array of n_peers device pointers, rank r's buffer mapped into
+ * this process, e.g. from a CUDA symmetric-memory allocation).  Between the three calls the
+ * caller only needs a barrier (any one-word collective); no data-carrying collective is left:
+ *   1. cppre_peer_bcast_keys: order-preserving uint32 key of this rank's local order statistic
+ *      d_vals[c] -> h_peer_keys[r][my_rank * cells_pad + c] for every r (cells_pad % 4 == 0).
+ *      Replaces cppre_ordered_keys + the MIN/MAX all-reduce: every rank then holds all n_peers
+ *      keys of every cell and takes min / max itself.
+ *   2. cppre_window_exchange: reads d_keys = this rank's [n_peers][cells_pad] key buffer, scans the
+ *      local scores once and stores, for the owner r = c / slab of cell c, into
+ *      h_peer_recv[r][my_rank][1 + slots][slab]: row 0 = header word
+ *      (#{x > hi} in bits 0..23, #candidates in bits 24..30, bit 31 = the cell holds a NaN on
+ *      some rank), rows 1.. = the candidates inside [lo, hi] in sample order.  Rows beyond a
+ *      column's candidate count are NOT written (stale memory the owner never reads).
+ *      Overflow list as in cppre_window_compact.
+ *   3. cppre_owner_select: the owner of slab `cell_offset / slab` reads its own receive buffer
+ *      d_recv [n_ranks][1 + slots][slab] (`cells` <= slab live cells), packs the candidate lists of
+ *      each cell, sorts `network` keys (power of two, 32..1024) and stores the
+ *      (kt - sum of #above)-th largest (1-based) into h_peer_q[r][cell_offset + c] for every r --
+ *      the all-gather of qhat, fused.  NaN where a header carries the NaN bit; cells that cannot
+ *      be answered (bracket missed, a list was cut, more than `network` candidates) are counted
+ *      in *d_overflow, listed in d_overflow_cells and written as NaN for the caller to redo. */
+int cppre_peer_bcast_keys(const float* d_vals, int64_t cells, int64_t cells_pad, void* const* h_peer_keys,
+                          int32_t n_peers, int32_t my_rank, void* stream);
+int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
+                          const uint32_t* d_keys, int64_t cells_pad, int32_t slots, int64_t slab,
+                          void* const* h_peer_recv, int32_t n_peers, int32_t my_rank, uint32_t* d_overflow,
+                          int32_t* d_overflow_cells, int32_t overflow_cap, void* stream);
+int cppre_owner_select(const float* d_recv, int32_t n_ranks, int32_t slots, int64_t slab, int64_t cells,
+                       int32_t kt, int32_t network, int64_t cell_offset, void* const* h_peer_q, int32_t n_peers,
+                       uint32_t* d_overflow, int32_t* d_overflow_cells, int32_t overflow_cap, void* stream);
+
 /* ---- K5: coverage --------------------------------------------------------------------- */
 /* inside[i] = #{ c : lo[i,c] <= y[i,c] <= hi[i,c] }, uint32 per sample, overwritten.
  * lo / hi: row stride 0 broadcasts one [cells] row over all samples.

@@ -334,3 +334,48 @@ def test_window_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alp
         np.testing.assert_array_equal(got, O.calibrate(full, N, alpha))
     else:                                                  # a bracket wider than 32 slots is reported, never silent
         assert alpha == 0.5
+
+
+@pytest.mark.parametrize("world,n_loc,alpha,cells", [(2, 256, 0.1, 1000), (8, 64, 0.1, 1003), (4, 100, 0.05, 517),
+                                                     (3, 50, 0.5, 1000), (8, 256, 0.1, 4096)])
+def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alpha, cells):
+    """K3x (keys broadcast -> window scan with in-band headers -> owner select with the qhat
+    broadcast), the ranks emulated one after the other on this GPU: plain device buffers stand in
+    for the peers' symmetric memory.  Bit-equal to np.quantile over the union; NaN cells are NaN;
+    cells that cannot be answered from the window are listed, never silently wrong."""
+    rng = np.random.default_rng(world * 1000 + n_loc)
+    full = np.abs(rng.standard_normal((world * n_loc, cells))).astype(np.float32)
+    full[rng.integers(0, world * n_loc, 4), 3] = 0.75          # ties
+    full[rng.integers(0, world * n_loc), 11] = np.nan          # one NaN -> that cell is NaN
+    full[:, 17] = 1.25                                         # a constant column: every sample sits in the bracket
+    N = world * n_loc
+    k = O.calibrate_rank(N, N, alpha)
+    kt, slots = N - k, 32
+    J = -(-kt // world)
+    slab = -(-cells // world)
+    cells_pad = (slab * world + 3) // 4 * 4
+    shards = [cuda(full[r * n_loc:(r + 1) * n_loc]) for r in range(world)]
+    keys = [torch.zeros((world, cells_pad), dtype=torch.int32, device="cuda") for _ in range(world)]
+    recv = [torch.full((world, 1 + slots, slab), float("nan"), device="cuda") for _ in range(world)]   # stale garbage
+    qbuf = [torch.full((cells_pad,), -7.0, device="cuda") for _ in range(world)]
+    ov = torch.zeros(1, dtype=torch.int32, device="cuda")
+    cells_ov = torch.full((256,), -1, dtype=torch.int32, device="cuda")
+    for me, s in enumerate(shards):
+        ops.peer_bcast_keys(ops.select_ranks(s, [n_loc - J])[0], cells_pad, [t.data_ptr() for t in keys], me)
+    for me, s in enumerate(shards):
+        ops.window_exchange(s, keys[me], slots, slab, [t.data_ptr() for t in recv], me, ov, cells_ov)
+    for me in range(world):
+        live = max(0, min(slab, cells - me * slab))
+        ops.owner_select(recv[me], live, kt, D.owner_network(world, slots), me * slab, [t.data_ptr() for t in qbuf],
+                         ov, cells_ov)
+    want = O.calibrate(full, N, alpha)
+    listed = set(int(c) for c in cells_ov.cpu().numpy() if c >= 0)
+    assert int(ov.item()) <= 256
+    assert 17 in listed or n_loc <= slots                      # the constant column overflows the window
+    for r in range(world):                                     # every rank received the same, complete qhat
+        got = qbuf[r][:cells].cpu().numpy()
+        keep = np.array([c not in listed for c in range(cells)])
+        np.testing.assert_array_equal(got[keep], want[keep])
+        assert np.isnan(got[11]) and np.isnan(want[11])
+    if alpha != 0.5:
+        assert listed <= {17}
