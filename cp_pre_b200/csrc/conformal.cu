@@ -682,13 +682,26 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
     uint32_t above = 0u, inside = 0u;
     if (live && !open) {
         const float* px = x + c;
+        // Branch-free per sample (10 instructions): key, `above` by predicate, and the candidate
+        // store as a predicated st.shared at a running shared-window address -- a data-dependent
+        // branch here costs a BSSY/BRA/BSYNC triple per sample and made the scan issue-bound.
+        uint32_t sa = (uint32_t)__cvta_generic_to_shared(slots) + 4u * (uint32_t)tid;
+        const uint32_t wmax = (uint32_t)W;
         auto take = [&](float v) {
             const uint32_t key = ordered_key(v);
-            above += key > khi ? 1u : 0u;
-            if (key - klo <= span) {
-                if (inside < (uint32_t)W) slots[inside * 128 + tid] = v;
-                ++inside;
-            }
+            const uint32_t t = key - klo;
+            asm volatile(
+                "{\n\t.reg .pred a, q, p;\n\t"
+                "setp.gt.u32 a, %3, %4;\n\t"             // above the bracket
+                "@a add.u32 %0, %0, 1;\n\t"
+                "setp.le.u32 q, %5, %6;\n\t"             // inside the bracket
+                "setp.lt.and.u32 p, %1, %7, q;\n\t"      // and a slot is left
+                "@p st.shared.f32 [%2], %8;\n\t"
+                "@p add.u32 %2, %2, 512;\n\t"
+                "@q add.u32 %1, %1, 1;\n\t}"
+                : "+r"(above), "+r"(inside), "+r"(sa)
+                : "r"(key), "r"(khi), "r"(t), "r"(span), "r"(wmax), "f"(v)
+                : "memory");
         };
         int32_t i = 0;
         for (; i + 16 <= n; i += 16) {
@@ -729,47 +742,49 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
     constexpr int CW = 32 / L;
     constexpr int LD = TC + 1;
     static_assert(TC == 32 && CW * WARPS == TC, "bad tiling");
-    extern __shared__ uint32_t tile[];      // [N][LD] keys, then per column: count, above, flag; then w*TC list lengths
+    extern __shared__ uint32_t tile[];      // [N][LD] keys, then per column: count, above, flag
     uint32_t* colcount = tile + N * LD;
     uint32_t* above = colcount + TC;
     uint32_t* flag = above + TC;
-    uint32_t* len = flag + TC;              // [w][TC]
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t c0 = (int64_t)blockIdx.x * TC;
-    for (int e = tid; e < N * LD; e += THREADS) tile[e] = 0u;
     if (tid < TC) { colcount[tid] = 0u; above[tid] = 0u; flag[tid] = 0u; }
     __syncthreads();
+    // Warp `wid` takes the lists of ranks wid, wid + WARPS, ...: lane = cell.  Header first, then
+    // as many candidate rows as the longest list among the 32 cells.  The tile is not cleared:
+    // the read-out below masks everything at or above the column's count to the padding key.
     const int64_t block = (int64_t)(W + 1) * slab;
-    for (int e = tid; e < w * TC; e += THREADS) {
-        const int r = e / TC, col = e % TC;
-        uint32_t l = 0u;
-        if (c0 + col < cells) {
-            const uint32_t h = __float_as_uint(__ldcg(recv + (int64_t)r * block + c0 + col));
-            atomicAdd(&above[col], h & 0xffffffu);
-            if (h >> 31) flag[col] = 1u;
-            l = (h >> 24) & 0x7fu;
-        }
-        len[e] = l;
-    }
-    __syncthreads();
     {
         const int col = lane;
         const bool live = c0 + col < cells;
-        for (int row = wid; row < w * W; row += WARPS) {
-            const int r = row / W, sl = row - r * W;
-            if (!live || (uint32_t)sl >= len[r * TC + col]) continue;
-            const uint32_t bits = __float_as_uint(__ldcg(recv + (int64_t)r * block + (int64_t)(1 + sl) * slab + c0 + col));
-            const uint32_t pos = atomicAdd(&colcount[col], 1u);
-            if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits);
+        for (int r = wid; r < w; r += WARPS) {
+            const float* src = recv + (int64_t)r * block + c0 + col;
+            uint32_t l = 0u;
+            if (live) {
+                const uint32_t h = __float_as_uint(__ldcg(src));
+                atomicAdd(&above[col], h & 0xffffffu);
+                if (h >> 31) flag[col] = 1u;
+                l = (h >> 24) & 0x7fu;
+            }
+            const uint32_t rows = __reduce_max_sync(0xffffffffu, l);
+            for (uint32_t sl = 0; sl < rows; ++sl) {
+                if (sl >= l) continue;
+                const uint32_t bits = __float_as_uint(__ldcg(src + (int64_t)(1 + sl) * slab));
+                const uint32_t pos = atomicAdd(&colcount[col], 1u);
+                if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits);
+            }
         }
     }
     __syncthreads();
     const int j = lane % L, i = lane / L;
     const int ct = wid + WARPS * i;
     uint32_t k[R];
+    {
+        const uint32_t have = colcount[ct];
 #pragma unroll
-    for (int r = 0; r < R; ++r) k[r] = tile[(r * L + j) * LD + ct];
+        for (int r = 0; r < R; ++r) k[r] = (uint32_t)(r * L + j) < have ? tile[(r * L + j) * LD + ct] : 0u;   // padding sorts first
+    }
     bitonic_sort_regs<L, R>(k, j);
     __syncthreads();
 #pragma unroll
@@ -797,7 +812,7 @@ int launch_owner(const float* recv, int32_t w, int32_t W, int64_t slab, int64_t 
                  int64_t cell_offset, uint32_t* overflow, int32_t* overflow_cells, int32_t cap,
                  const PeerPtrs& qpeers, cudaStream_t st) {
     constexpr int N = L * R, TC = 32;
-    const size_t smem = ((size_t)N * (TC + 1) + 3 * TC + (size_t)w * TC) * sizeof(uint32_t);
+    const size_t smem = ((size_t)N * (TC + 1) + 3 * TC) * sizeof(uint32_t);
     auto kern = owner_select_kernel<L, R, TC>;
     static size_t configured = 48 * 1024;
     if (smem > configured) {

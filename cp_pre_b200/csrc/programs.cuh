@@ -5,12 +5,47 @@
 // (I is the compile-time index of the point inside the thread's register block; the generic
 // kernel ignores it).  Field / slot / scalar orders are the ones documented in cppre.h.
 //
+// The algebra is written once over a value type T = decltype(c.D<..>()): `float` (one grid point,
+// generic kernel) or `f2` (two neighbouring grid points in one 64-bit register pair, TMA star
+// kernel).  On sm_100a the f2 operations are single FFMA2 / FMUL2 / FADD2 instructions
+// (__ffma2_rn & co., crt/sm_100_rt.h) whose scalar operands (coefficients, program scalars) are
+// broadcast from one uniform register and whose negations are operand modifiers -- half the
+// issue slots of the scalar form, same IEEE results per component.
+//
 // The formulas restate the reference's residual expressions; see the file:line on each.
 #pragma once
 
 #include "common.cuh"
 
 namespace cppre {
+
+
+// ---- value-type algebra -------------------------------------------------------------------
+struct f2 {
+    float2 v;
+};
+__device__ __forceinline__ f2 mk2(float x, float y) { return f2{make_float2(x, y)}; }
+__device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
+
+__device__ __forceinline__ float pmul(float a, float b) { return a * b; }
+__device__ __forceinline__ float padd(float a, float b) { return a + b; }
+__device__ __forceinline__ float psub(float a, float b) { return a - b; }
+__device__ __forceinline__ float pfma(float a, float b, float c) { return fmaf(a, b, c); }    // a*b + c
+__device__ __forceinline__ float pfnma(float a, float b, float c) { return fmaf(-a, b, c); }  // c - a*b
+__device__ __forceinline__ float pinv(float a) { return 1.0f / a; }   // IEEE division (no fast-math)
+
+__device__ __forceinline__ f2 pmul(f2 a, f2 b) { return f2{__fmul2_rn(a.v, b.v)}; }
+__device__ __forceinline__ f2 pmul(f2 a, float b) { return f2{__fmul2_rn(a.v, bc2(b))}; }
+__device__ __forceinline__ f2 pmul(float a, f2 b) { return f2{__fmul2_rn(b.v, bc2(a))}; }
+__device__ __forceinline__ f2 padd(f2 a, f2 b) { return f2{__fadd2_rn(a.v, b.v)}; }
+__device__ __forceinline__ f2 psub(f2 a, f2 b) { return f2{__fadd2_rn(a.v, make_float2(-b.v.x, -b.v.y))}; }
+__device__ __forceinline__ f2 psub(f2 a, float b) { return f2{__fadd2_rn(a.v, bc2(-b))}; }
+__device__ __forceinline__ f2 pfma(f2 a, f2 b, f2 c) { return f2{__ffma2_rn(a.v, b.v, c.v)}; }
+__device__ __forceinline__ f2 pfma(f2 a, float b, f2 c) { return f2{__ffma2_rn(a.v, bc2(b), c.v)}; }
+__device__ __forceinline__ f2 pfma(float a, f2 b, f2 c) { return f2{__ffma2_rn(b.v, bc2(a), c.v)}; }
+__device__ __forceinline__ f2 pfnma(f2 a, f2 b, f2 c) { return f2{__ffma2_rn(make_float2(-a.v.x, -a.v.y), b.v, c.v)}; }
+__device__ __forceinline__ f2 pfnma(f2 a, float b, f2 c) { return f2{__ffma2_rn(a.v, bc2(-b), c.v)}; }
+__device__ __forceinline__ f2 pinv(f2 a) { return mk2(1.0f / a.v.x, 1.0f / a.v.y); }
 
 template <int KIND>
 struct Prog;
@@ -20,7 +55,7 @@ template <>
 struct Prog<CPPRE_PROG_LINEAR> {
     static constexpr int NF = 1, NSLOT = 1;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float*) {
+    __device__ __forceinline__ static auto eval(const C& c, const float*) {
         return c.template D<0, 0, I>();
     }
 };
@@ -31,11 +66,11 @@ template <>
 struct Prog<CPPRE_PROG_BURGERS> {
     static constexpr int NF = 1, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float* s) {
-        const float u = c.template V<0, I>();
-        float r = s[0] * c.template D<0, 0, I>();
-        r += (s[1] * u) * c.template D<1, 0, I>();
-        r -= s[2] * c.template D<2, 0, I>();
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
+        const auto u = c.template V<0, I>();
+        auto r = pmul(c.template D<0, 0, I>(), s[0]);
+        r = pfma(pmul(u, s[1]), c.template D<1, 0, I>(), r);
+        r = pfnma(c.template D<2, 0, I>(), s[2], r);
         return r;
     }
 };
@@ -46,8 +81,8 @@ template <>
 struct Prog<CPPRE_PROG_NS_CONTINUITY> {
     static constexpr int NF = 2, NSLOT = 2;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float* s) {
-        return c.template D<0, 0, I>() + s[0] * c.template D<1, 1, I>();
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
+        return pfma(c.template D<1, 1, I>(), s[0], c.template D<0, 0, I>());
     }
 };
 
@@ -57,20 +92,20 @@ template <>
 struct Prog<CPPRE_PROG_NS_MOMENTUM> {
     static constexpr int NF = 3, NSLOT = 4;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float* s) {
-        const float u = c.template V<0, I>(), v = c.template V<1, I>();
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
+        const auto u = c.template V<0, I>(), v = c.template V<1, I>();
         const float a = s[0], b = s[1], cc = s[2], d = s[3];
-        float rx = c.template D<0, 0, I>() * a;
-        rx += (u * c.template D<1, 0, I>()) * b;
-        rx += (v * c.template D<2, 0, I>()) * cc;
-        rx -= c.template D<3, 0, I>() * d;
-        rx += c.template D<1, 2, I>() * b;
-        float ry = c.template D<0, 1, I>() * a;
-        ry += (u * c.template D<1, 1, I>()) * cc;
-        ry += (v * c.template D<2, 1, I>()) * b;
-        ry -= c.template D<3, 1, I>() * d;
-        ry += c.template D<2, 2, I>() * cc;
-        return rx + ry;
+        auto rx = pmul(c.template D<0, 0, I>(), a);
+        rx = pfma(pmul(u, c.template D<1, 0, I>()), b, rx);
+        rx = pfma(pmul(v, c.template D<2, 0, I>()), cc, rx);
+        rx = pfnma(c.template D<3, 0, I>(), d, rx);
+        rx = pfma(c.template D<1, 2, I>(), b, rx);
+        auto ry = pmul(c.template D<0, 1, I>(), a);
+        ry = pfma(pmul(u, c.template D<1, 1, I>()), cc, ry);
+        ry = pfma(pmul(v, c.template D<2, 1, I>()), b, ry);
+        ry = pfnma(c.template D<3, 1, I>(), d, ry);
+        ry = pfma(c.template D<2, 2, I>(), cc, ry);
+        return padd(rx, ry);
     }
 };
 
@@ -80,13 +115,13 @@ template <>
 struct Prog<CPPRE_PROG_MHD_CONTINUITY> {
     static constexpr int NF = 3, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float*) {
-        const float rho = c.template V<0, I>(), u = c.template V<1, I>(), v = c.template V<2, I>();
-        float r = c.template D<0, 0, I>();
-        r += u * c.template D<1, 0, I>();
-        r += rho * c.template D<1, 1, I>();
-        r += v * c.template D<2, 0, I>();
-        r += rho * c.template D<2, 2, I>();
+    __device__ __forceinline__ static auto eval(const C& c, const float*) {
+        const auto rho = c.template V<0, I>(), u = c.template V<1, I>(), v = c.template V<2, I>();
+        auto r = c.template D<0, 0, I>();
+        r = pfma(u, c.template D<1, 0, I>(), r);
+        r = pfma(rho, c.template D<1, 1, I>(), r);
+        r = pfma(v, c.template D<2, 0, I>(), r);
+        r = pfma(rho, c.template D<2, 2, I>(), r);
         return r;
     }
 };
@@ -96,28 +131,28 @@ template <>
 struct Prog<CPPRE_PROG_MHD_MOMENTUM> {
     static constexpr int NF = 6, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float*) {
-        const float rho = c.template V<0, I>(), u = c.template V<1, I>(), v = c.template V<2, I>();
-        const float Bx = c.template V<4, I>(), By = c.template V<5, I>();
-        const float ir = 1.0f / rho;  // IEEE division (no fast-math): rho is a divisor in the reference
-        const float bxr = Bx * ir, byr = By * ir;
-        const float dxBx = c.template D<1, 4, I>(), dyBy = c.template D<2, 5, I>();
-        const float dyBx = c.template D<2, 4, I>(), dxBy = c.template D<1, 5, I>();
-        float rx = c.template D<0, 1, I>();
-        rx += u * c.template D<1, 1, I>();
-        rx += ir * c.template D<1, 3, I>();
-        rx -= 2.0f * bxr * dxBx;
-        rx += v * c.template D<2, 1, I>();
-        rx -= byr * dyBx;
-        rx -= bxr * dyBy;
-        float ry = c.template D<0, 2, I>();
-        ry += u * c.template D<1, 2, I>();
-        ry += ir * c.template D<2, 3, I>();
-        ry -= 2.0f * byr * dyBy;
-        ry += v * c.template D<2, 2, I>();
-        ry -= byr * dxBx;
-        ry -= bxr * dxBy;
-        return rx + ry;
+    __device__ __forceinline__ static auto eval(const C& c, const float*) {
+        const auto rho = c.template V<0, I>(), u = c.template V<1, I>(), v = c.template V<2, I>();
+        const auto Bx = c.template V<4, I>(), By = c.template V<5, I>();
+        const auto ir = pinv(rho);    // rho is a divisor in the reference
+        const auto bxr = pmul(Bx, ir), byr = pmul(By, ir);
+        const auto dxBx = c.template D<1, 4, I>(), dyBy = c.template D<2, 5, I>();
+        const auto dyBx = c.template D<2, 4, I>(), dxBy = c.template D<1, 5, I>();
+        auto rx = c.template D<0, 1, I>();
+        rx = pfma(u, c.template D<1, 1, I>(), rx);
+        rx = pfma(ir, c.template D<1, 3, I>(), rx);
+        rx = pfnma(pmul(bxr, 2.0f), dxBx, rx);
+        rx = pfma(v, c.template D<2, 1, I>(), rx);
+        rx = pfnma(byr, dyBx, rx);
+        rx = pfnma(bxr, dyBy, rx);
+        auto ry = c.template D<0, 2, I>();
+        ry = pfma(u, c.template D<1, 2, I>(), ry);
+        ry = pfma(ir, c.template D<2, 3, I>(), ry);
+        ry = pfnma(pmul(byr, 2.0f), dyBy, ry);
+        ry = pfma(v, c.template D<2, 2, I>(), ry);
+        ry = pfnma(byr, dxBx, ry);
+        ry = pfnma(bxr, dxBy, ry);
+        return padd(rx, ry);
     }
 };
 
@@ -126,19 +161,20 @@ template <>
 struct Prog<CPPRE_PROG_MHD_ENERGY> {
     static constexpr int NF = 6, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float* s) {
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
         const float g = s[0];
-        const float u = c.template V<1, I>(), v = c.template V<2, I>(), p = c.template V<3, I>();
-        const float Bx = c.template V<4, I>(), By = c.template V<5, I>();
-        const float bx2 = Bx * Bx, by2 = By * By;
-        const float gp = g * (p - 0.5f * (bx2 + by2));
-        float r = c.template D<0, 0, I>();
-        r += u * c.template D<1, 3, I>();
-        r += v * c.template D<2, 3, I>();
-        r += ((g - 2.0f) * (u * Bx + v * By)) * (c.template D<1, 4, I>() + c.template D<2, 5, I>());
-        r += (gp + by2) * c.template D<1, 1, I>();
-        r += (gp + bx2) * c.template D<2, 2, I>();
-        r -= (Bx * By) * (c.template D<2, 1, I>() + c.template D<1, 2, I>());
+        const auto u = c.template V<1, I>(), v = c.template V<2, I>(), p = c.template V<3, I>();
+        const auto Bx = c.template V<4, I>(), By = c.template V<5, I>();
+        const auto bx2 = pmul(Bx, Bx), by2 = pmul(By, By);
+        const auto gp = pmul(pfnma(padd(bx2, by2), 0.5f, p), g);       // g * (p - 0.5*(bx2+by2))
+        auto r = c.template D<0, 0, I>();
+        r = pfma(u, c.template D<1, 3, I>(), r);
+        r = pfma(v, c.template D<2, 3, I>(), r);
+        const auto ub = pmul(pfma(v, By, pmul(u, Bx)), g - 2.0f);      // (g-2) * (u*Bx + v*By)
+        r = pfma(ub, padd(c.template D<1, 4, I>(), c.template D<2, 5, I>()), r);
+        r = pfma(padd(gp, by2), c.template D<1, 1, I>(), r);
+        r = pfma(padd(gp, bx2), c.template D<2, 2, I>(), r);
+        r = pfnma(pmul(Bx, By), padd(c.template D<2, 1, I>(), c.template D<1, 2, I>()), r);
         return r;
     }
 };
@@ -148,20 +184,20 @@ template <>
 struct Prog<CPPRE_PROG_MHD_INDUCTION> {
     static constexpr int NF = 4, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float*) {
-        const float u = c.template V<0, I>(), v = c.template V<1, I>();
-        const float Bx = c.template V<2, I>(), By = c.template V<3, I>();
-        float rx = c.template D<0, 2, I>();
-        rx -= By * c.template D<2, 0, I>();
-        rx += Bx * c.template D<2, 1, I>();
-        rx -= v * c.template D<2, 2, I>();
-        rx += u * c.template D<2, 3, I>();
-        float ry = c.template D<0, 3, I>();
-        ry += By * c.template D<1, 0, I>();
-        ry -= Bx * c.template D<1, 1, I>();
-        ry -= v * c.template D<1, 2, I>();
-        ry += u * c.template D<1, 3, I>();
-        return rx + ry;
+    __device__ __forceinline__ static auto eval(const C& c, const float*) {
+        const auto u = c.template V<0, I>(), v = c.template V<1, I>();
+        const auto Bx = c.template V<2, I>(), By = c.template V<3, I>();
+        auto rx = c.template D<0, 2, I>();
+        rx = pfnma(By, c.template D<2, 0, I>(), rx);
+        rx = pfma(Bx, c.template D<2, 1, I>(), rx);
+        rx = pfnma(v, c.template D<2, 2, I>(), rx);
+        rx = pfma(u, c.template D<2, 3, I>(), rx);
+        auto ry = c.template D<0, 3, I>();
+        ry = pfma(By, c.template D<1, 0, I>(), ry);
+        ry = pfnma(Bx, c.template D<1, 1, I>(), ry);
+        ry = pfnma(v, c.template D<1, 2, I>(), ry);
+        ry = pfma(u, c.template D<1, 3, I>(), ry);
+        return padd(rx, ry);
     }
 };
 
@@ -170,8 +206,8 @@ template <>
 struct Prog<CPPRE_PROG_MHD_GAUSS> {
     static constexpr int NF = 2, NSLOT = 3;
     template <int I, class C>
-    __device__ __forceinline__ static float eval(const C& c, const float*) {
-        return c.template D<1, 0, I>() + c.template D<2, 1, I>();
+    __device__ __forceinline__ static auto eval(const C& c, const float*) {
+        return padd(c.template D<1, 0, I>(), c.template D<2, 1, I>());
     }
 };
 

@@ -117,27 +117,33 @@ struct StarCtx {
     float (&ym)[NF][RX];
     float (&yp)[NF][RX];
 
-    template <int SLOT, int FD, int I>
-    __device__ __forceinline__ float D() const {
-        constexpr int j = I / 4, i = I % 4;
+    // Two neighbouring columns (2h, 2h+1) of row j per evaluation: IP = 2*j + h.  Every arm is
+    // one FFMA2 whose coefficient is a broadcast uniform-register operand; pairs that are not a
+    // register pair of the 128-bit shared-memory loads (the y+-1 arms) cost one extra MOV.
+    template <int SLOT, int FD, int IP>
+    __device__ __forceinline__ f2 D() const {
+        constexpr int j = IP / 2, h = IP % 2, i0 = 2 * h, i1 = 2 * h + 1;
         constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
         constexpr int jm = j > 0 ? j - 1 : 0, jp = j < RX - 1 ? j + 1 : RX - 1;
-        constexpr int im = i > 0 ? i - 1 : 0, ip = i < 3 ? i + 1 : 3;
         const float* c = k.c[SLOT];
         // accumulation in row-major tap order (t-, x-, y-, centre, y+, x+, t+), like the oracle
-        float acc = 0.0f;
-        if constexpr ((m >> ARM_TM) & 1) acc = fmaf(c[ARM_TM], prev[FD][j][i], acc);
-        if constexpr ((m >> ARM_XM) & 1) acc = fmaf(c[ARM_XM], (j > 0 ? cur[FD][jm][i] : xm[FD][i]), acc);
-        if constexpr ((m >> ARM_YM) & 1) acc = fmaf(c[ARM_YM], (i > 0 ? cur[FD][j][im] : ym[FD][j]), acc);
-        if constexpr ((m >> ARM_C) & 1) acc = fmaf(c[ARM_C], cur[FD][j][i], acc);
-        if constexpr ((m >> ARM_YP) & 1) acc = fmaf(c[ARM_YP], (i < 3 ? cur[FD][j][ip] : yp[FD][j]), acc);
-        if constexpr ((m >> ARM_XP) & 1) acc = fmaf(c[ARM_XP], (j < RX - 1 ? cur[FD][jp][i] : xp[FD][i]), acc);
-        if constexpr ((m >> ARM_TP) & 1) acc = fmaf(c[ARM_TP], next[FD][j][i], acc);
+        f2 acc = mk2(0.0f, 0.0f);
+        if constexpr ((m >> ARM_TM) & 1) acc = pfma(mk2(prev[FD][j][i0], prev[FD][j][i1]), c[ARM_TM], acc);
+        if constexpr ((m >> ARM_XM) & 1)
+            acc = pfma(j > 0 ? mk2(cur[FD][jm][i0], cur[FD][jm][i1]) : mk2(xm[FD][i0], xm[FD][i1]), c[ARM_XM], acc);
+        if constexpr ((m >> ARM_YM) & 1)
+            acc = pfma(mk2(h == 0 ? ym[FD][j] : cur[FD][j][1], cur[FD][j][i0]), c[ARM_YM], acc);
+        if constexpr ((m >> ARM_C) & 1) acc = pfma(mk2(cur[FD][j][i0], cur[FD][j][i1]), c[ARM_C], acc);
+        if constexpr ((m >> ARM_YP) & 1)
+            acc = pfma(mk2(cur[FD][j][i1], h == 1 ? yp[FD][j] : cur[FD][j][2]), c[ARM_YP], acc);
+        if constexpr ((m >> ARM_XP) & 1)
+            acc = pfma(j < RX - 1 ? mk2(cur[FD][jp][i0], cur[FD][jp][i1]) : mk2(xp[FD][i0], xp[FD][i1]), c[ARM_XP], acc);
+        if constexpr ((m >> ARM_TP) & 1) acc = pfma(mk2(next[FD][j][i0], next[FD][j][i1]), c[ARM_TP], acc);
         return acc;
     }
-    template <int FD, int I>
-    __device__ __forceinline__ float V() const {
-        return cur[FD][I / 4][I % 4];
+    template <int FD, int IP>
+    __device__ __forceinline__ f2 V() const {
+        return mk2(cur[FD][IP / 2][2 * (IP % 2)], cur[FD][IP / 2][2 * (IP % 2) + 1]);
     }
 };
 
@@ -360,11 +366,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                     if (!refiller) bar_arrive(stage + 1, kThreads);
                 if constexpr (j + 1 < RX) fetch_operands(std::integral_constant<int, j + 1>{});
                 if (live & (1u << j)) {
-                    float r[4];
-                    r[0] = Prog<KIND>::template eval<4 * j + 0>(ctx, p.scalars);
-                    r[1] = Prog<KIND>::template eval<4 * j + 1>(ctx, p.scalars);
-                    r[2] = Prog<KIND>::template eval<4 * j + 2>(ctx, p.scalars);
-                    r[3] = Prog<KIND>::template eval<4 * j + 3>(ctx, p.scalars);
+                    const f2 r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
+                    const f2 r23 = Prog<KIND>::template eval<2 * j + 1>(ctx, p.scalars);
+                    float r[4] = {r01.v.x, r01.v.y, r23.v.x, r23.v.y};
                     const float rr[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
                     const float ww[4] = {wq[j].x, wq[j].y, wq[j].z, wq[j].w};
                     if constexpr (COVER) {

@@ -154,6 +154,7 @@ def _cuda_kernels():
 
 
 _SYMM = {}
+_TUNE = {}     # self-tuning of the owner's network size, keyed by problem shape
 
 
 def _symm_buffer(tag: str, shape, dtype, device, group):
@@ -211,11 +212,15 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     kern["window_x"](flat, keys, slots, slab, recv_ptrs, me, over, over_cells)
     _barrier(flag, group)
     live = max(0, min(slab, cells - me * slab))
-    kern["owner"](recv, live, kt, owner_network(w, slots), me * slab, q_ptrs, over, over_cells)
+    tune = ("net", w, n, cells, slots)
+    network = min(1024, owner_network(w, slots) << _TUNE.get(tune, 0))
+    kern["owner"](recv, live, kt, network, me * slab, q_ptrs, over, over_cells)
     counts = [torch.empty_like(over) for _ in range(w)]
     dist.all_gather(counts, over, group=group)                # also the barrier that orders the q stores
     q = qbuf[:cells].clone()
     counts = torch.stack(counts).cpu()
+    if int(counts.sum()) > OVERFLOW_CAP // 8 and network < 1024:
+        _TUNE[tune] = _TUNE.get(tune, 0) + 1     # same counts on every rank: every rank widens alike
     if int(counts.sum()) == 0:
         return q
     if int(counts.max()) > OVERFLOW_CAP:
@@ -318,9 +323,10 @@ OVERFLOW_CAP = 8192
 
 def owner_network(world: int, slots: int) -> int:
     """Keys the owner of a cell slab sorts per cell: a power of two above the number of real
-    candidates the union of `world` brackets holds (about 14 per rank at alpha = 0.1, n = 256;
-    the rare cell above it is redone exactly), never more than the candidate rows."""
-    need = max(32, 32 * world)
+    candidates the union of `world` brackets holds (about 2.5 per rank at world = 2 and 6 per rank
+    at world = 8 for alpha = 0.1, n = 256; the rare cell above it is redone exactly), never more
+    than the candidate rows.  `_fused_window_quantile` doubles it when too many cells overflow."""
+    need = max(32, 16 * world)
     net = 32
     while net < need and net < world * slots:
         net *= 2
