@@ -662,7 +662,7 @@ __device__ __forceinline__ uint32_t pack_header(uint32_t above, uint32_t inside,
     return (above & 0xffffffu) | (inside << 24) | (open ? 0x80000000u : 0u);
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 8)
 window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells,
                        const uint32_t* keys, int64_t cells_pad, int32_t W, int64_t slab, uint32_t* overflow,
                        int32_t* __restrict__ overflow_cells, int32_t overflow_cap, const PeerPtrs peers) {
@@ -703,15 +703,29 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
                 : "r"(key), "r"(khi), "r"(t), "r"(span), "r"(wmax), "f"(v)
                 : "memory");
         };
-        int32_t i = 0;
-        for (; i + 16 <= n; i += 16) {
-            float v[16];
+        // two batches of 16 loads in flight per lane: the next batch is requested before the
+        // current one is consumed (the asm statements above are ordering barriers for the
+        // compiler, so the overlap has to be written out)
+        float va[16], vb[16];
+        auto load16 = [&](float (&v)[16]) {
 #pragma unroll
             for (int u = 0; u < 16; ++u) { v[u] = __ldg(px); px += xs; }
+        };
+        auto take16 = [&](const float (&v)[16]) {
 #pragma unroll
             for (int u = 0; u < 16; ++u) take(v[u]);
+        };
+        const int32_t nb = n / 16;
+        if (nb > 0) load16(va);
+        int32_t b = 0;
+        for (; b + 2 <= nb; b += 2) {
+            load16(vb);
+            take16(va);
+            if (b + 2 < nb) load16(va);
+            take16(vb);
         }
-        for (; i < n; ++i) { take(__ldg(px)); px += xs; }
+        if (b < nb) take16(va);
+        for (int32_t i = nb * 16; i < n; ++i) { take(__ldg(px)); px += xs; }
     }
     if (inside > (uint32_t)W) {                      // reported with the cell index: the caller redoes these exactly
         const uint32_t at = atomicAdd(overflow, 1u);

@@ -324,9 +324,11 @@ OVERFLOW_CAP = 8192
 def owner_network(world: int, slots: int) -> int:
     """Keys the owner of a cell slab sorts per cell: a power of two above the number of real
     candidates the union of `world` brackets holds (about 2.5 per rank at world = 2 and 6 per rank
-    at world = 8 for alpha = 0.1, n = 256; the rare cell above it is redone exactly), never more
-    than the candidate rows.  `_fused_window_quantile` doubles it when too many cells overflow."""
-    need = max(32, 16 * world)
+    at world = 8 on average for alpha = 0.1, n = 256, but a cell whose ranks disagree by 2-3
+    sigma holds several times that, and at 3.3 M cells per step those cells exist; the rare cell
+    above the network is redone exactly), never more than the candidate rows.
+    `_fused_window_quantile` doubles it when too many cells overflow."""
+    need = max(32, 32 * world)
     net = 32
     while net < need and net < world * slots:
         net *= 2
