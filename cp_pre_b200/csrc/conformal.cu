@@ -736,8 +736,10 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
     if (!live) return;
     float* dst = reinterpret_cast<float*>(peers.base[c / slab]) + (int64_t)peers.me * (W + 1) * slab + c % slab;
     dst[0] = __uint_as_float(pack_header(above, inside, open));
-    for (uint32_t s = 0; s < rows; ++s)
-        if (s < inside) dst[(int64_t)(s + 1) * slab] = slots[s * 128 + tid];
+    // every lane stores every row up to the warp's longest list (its own rows beyond `inside` are
+    // don't-care words the owner never reads): a full warp row is four whole 32-byte sectors,
+    // which is what NVLink moves efficiently -- lane-predicated stores cost 2x here at 8 GPUs
+    for (uint32_t s = 0; s < rows; ++s) dst[(int64_t)(s + 1) * slab] = slots[s * 128 + tid];
 }
 
 // Owner side.  recv = [w][1 + W][slab]: row 0 of block r holds rank r's headers, rows 1.. its

@@ -154,6 +154,7 @@ def _cuda_kernels():
 
 
 _SYMM = {}
+LAST_STATS = {}   # diagnostics of the last fused quantile (overflowing cells, network size)
 _TUNE = {}     # self-tuning of the owner's network size, keyed by problem shape
 
 
@@ -219,8 +220,12 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     dist.all_gather(counts, over, group=group)                # also the barrier that orders the q stores
     q = qbuf[:cells].clone()
     counts = torch.stack(counts).cpu()
-    if int(counts.sum()) > OVERFLOW_CAP // 8 and network < 1024:
-        _TUNE[tune] = _TUNE.get(tune, 0) + 1     # same counts on every rank: every rank widens alike
+    LAST_STATS.update(overflow_cells=int(counts.sum()), network=network, slots=slots)
+    if int(counts.max()) > OVERFLOW_CAP // 2 and network < 1024:
+        # close to the point where the whole tensor would be transposed instead: sort more keys per
+        # cell from now on (a few thousand redone cells are cheaper than a network twice the size);
+        # the counts are the same on every rank, so every rank widens alike
+        _TUNE[tune] = _TUNE.get(tune, 0) + 1
     if int(counts.sum()) == 0:
         return q
     if int(counts.max()) > OVERFLOW_CAP:

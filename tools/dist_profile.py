@@ -35,7 +35,7 @@ def main():
     rank, world, dev = D.init_from_env()
     n, cells = 256, 50 * 256 * 256
     g = torch.Generator(device=dev).manual_seed(rank)
-    scores = torch.rand((n, cells), device=dev, generator=g)
+    scores = torch.randn((n, cells), device=dev, generator=g).abs_()
     T = Timed()
     kern = {k: T.wrap(k, f) for k, f in D._cuda_kernels().items()}
     for name in ("all_reduce", "all_to_all_single", "all_gather"):
@@ -56,6 +56,7 @@ def main():
     out["calls_per_quantile"] = {k: len(v) // reps for k, v in T.t.items()}
     out["total_ms"] = round(sum(tot[skip:]) / (reps - skip), 3)
     out["world"] = world
+    out["stats"] = dict(D.LAST_STATS)
     if rank == 0:
         print(json.dumps(out))
     dist.destroy_process_group()
