@@ -162,6 +162,7 @@ class Step:
         self.points = self.bs * self.nt * self.nx * self.ny
         self.interior_cells = (self.nt - 2) * (self.nx - 2) * (self.ny - 2)
         self.k1_events, self.k1c_events = [], []
+        self.defer = world > 1     # overflow counters of the fused quantile are settled after the timed loop
 
     def _input(self, v):
         return v if self.workload == "ns" else v[:, 0]
@@ -182,7 +183,7 @@ class Step:
     def quantile(self):
         from cp_pre_b200 import dist as D
         if self.world > 1:
-            return D.marginal_quantiles(self.scores, [self.rank_k])[0]
+            return D.marginal_quantiles(self.scores, [self.rank_k], defer=self.defer)[0]
         return self.ops.select_ranks(self.scores, [self.rank_k])[0]
 
     def cover_val(self, v, qhat, timed=False):
@@ -334,18 +335,37 @@ def main():
         torch.cuda.synchronize()
 
     torch.cuda.profiler.start()      # ncu --profile-from-start off: the launch list starts here (no-op otherwise)
-    for _ in range(W):
-        qhat, inside = step.run()
-    barrier()
-    l0 = _lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(device.index or 0) as clk:
+
+    def timed_loop():
+        step.k1_events.clear()
+        step.k1c_events.clear()
+        for _ in range(W):
+            out = step.run()
         barrier()
-        e0.record()
-        for _ in range(K):
-            qhat, inside = step.run(timed=True)
-        e1.record()
-        barrier()
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(device.index or 0) as clk:
+            barrier()
+            e0.record()
+            for _ in range(K):
+                out = step.run(timed=True)
+            e1.record()
+            barrier()
+        return out, l0, e0, e1, clk
+
+    (qhat, inside), l0, e0, e1, clk = timed_loop()
+    quantile_check = "n/a (single GPU: direct select)"
+    if world > 1:
+        # deferred mode: every step's quantile was consumed without a host round trip; settle all
+        # overflow counters now.  Any cell that could not be answered from its window voids the
+        # timing: repeat the loop in the checked mode (host sync + exact redo inside every step).
+        bad = torch.tensor([D.pending_overflow()], dtype=torch.int64, device=device)
+        torch.distributed.all_reduce(bad)
+        quantile_check = "deferred: 0 overflowing cells in every warm-up and timed step"
+        if int(bad.item()) > 0:
+            step.defer = False
+            (qhat, inside), l0, e0, e1, clk = timed_loop()
+            quantile_check = f"checked per step ({int(bad.item())} overflowing cells seen in deferred mode)"
     torch.cuda.profiler.stop()
     launches = _lib.launch_count() - l0
     ms = e0.elapsed_time(e1) / K
@@ -376,6 +396,7 @@ def main():
     # end-to-end through the public API with host inputs
     e2e = None
     if not args.no_e2e:
+        step.defer = False            # e2e is PCIe-bound: keep the per-step overflow check + exact redo
         ee = E2E(step)
         for _ in range(2):
             ee.run()
@@ -416,7 +437,7 @@ def main():
                        "per_gpu_batch": step.bs, "global_batch": step.bs * world, "sharding": "batch axis",
                        "l2": f"inputs ({step.vars.numel() * 4 / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
                        "empirical_coverage": coverage, "target_coverage": 1 - ALPHA,
-                       "qhat_spot_check_4096_cells_equal": verified},
+                       "qhat_spot_check_4096_cells_equal": verified, "quantile_overflow_check": quantile_check},
             "roofline": {"bound": "hbm", "kernel": "star_kernel<NS_MOMENTUM> (K1: TMA stencil + |.| epilogue, STORE)"
                          if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <initializer_list>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -758,7 +759,7 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
     constexpr int CW = 32 / L;
     constexpr int LD = TC + 1;
     static_assert(TC == 32 && CW * WARPS == TC, "bad tiling");
-    extern __shared__ uint32_t tile[];      // [N][LD] keys, then per column: count, above, flag
+    extern __shared__ uint32_t tile[];      // [N][LD] keys, then per column: count, above, flag; then the tile's longest list
     uint32_t* colcount = tile + N * LD;
     uint32_t* above = colcount + TC;
     uint32_t* flag = above + TC;
@@ -793,20 +794,40 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
         }
     }
     __syncthreads();
+    // The network is sized by the fullest cell of THIS tile: N, N/2 or N/4 keys (the first RS
+    // registers of every lane hold positions < RS*L, and the fill packs candidates from position
+    // 0), so the capacity N only costs when a tile needs it.
+    if (wid == 0) {
+        const uint32_t m = __reduce_max_sync(0xffffffffu, colcount[lane]);
+        if (lane == 0) flag[TC] = m;
+    }
+    __syncthreads();
+    const uint32_t maxhave = flag[TC];
     const int j = lane % L, i = lane / L;
     const int ct = wid + WARPS * i;
-    uint32_t k[R];
-    {
-        const uint32_t have = colcount[ct];
+    const uint32_t mine = colcount[ct];
+    int RS = R;
+    auto sort_sub = [&](auto RSC) {
+        constexpr int rs = decltype(RSC)::value;
+        uint32_t k[rs];
 #pragma unroll
-        for (int r = 0; r < R; ++r) k[r] = (uint32_t)(r * L + j) < have ? tile[(r * L + j) * LD + ct] : 0u;   // padding sorts first
+        for (int r = 0; r < rs; ++r) k[r] = (uint32_t)(r * L + j) < mine ? tile[(r * L + j) * LD + ct] : 0u;   // padding sorts first
+        bitonic_sort_regs<L, rs>(k, j);
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < rs; ++r) tile[(r * L + j) * LD + ct] = k[r];
+        RS = rs;
+    };
+    if constexpr (R >= 8) {
+        if (maxhave * 4u <= (uint32_t)N) sort_sub(std::integral_constant<int, R / 4>{});
+        else if (maxhave * 2u <= (uint32_t)N) sort_sub(std::integral_constant<int, R / 2>{});
+        else sort_sub(std::integral_constant<int, R>{});
+    } else {
+        sort_sub(std::integral_constant<int, R>{});
     }
-    bitonic_sort_regs<L, R>(k, j);
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < R; ++r) tile[(r * L + j) * LD + ct] = k[r];
     __syncthreads();
     if (tid < TC && c0 + tid < cells) {
+        const int NS = RS * L;
         const int want = kt - (int)above[tid];
         const int have = (int)colcount[tid];
         bool nan = flag[tid] != 0u;
@@ -815,8 +836,8 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
             if (at < (uint32_t)overflow_cap) overflow_cells[at] = (int32_t)(cell_offset + c0 + tid);
             nan = true;
         }
-        const int kq = nan ? 0 : N - want;
-        const uint32_t v = tile[((kq % R) * L + kq / R) * LD + tid];
+        const int kq = nan ? 0 : NS - want;
+        const uint32_t v = tile[((kq % RS) * L + kq / RS) * LD + tid];
         const float q = nan ? __uint_as_float(0x7fc00000u) : __uint_as_float(key_to_float_bits(v));
         for (int r = 0; r < qpeers.n; ++r)
             reinterpret_cast<float*>(qpeers.base[r])[cell_offset + c0 + tid] = q;
@@ -828,7 +849,7 @@ int launch_owner(const float* recv, int32_t w, int32_t W, int64_t slab, int64_t 
                  int64_t cell_offset, uint32_t* overflow, int32_t* overflow_cells, int32_t cap,
                  const PeerPtrs& qpeers, cudaStream_t st) {
     constexpr int N = L * R, TC = 32;
-    const size_t smem = ((size_t)N * (TC + 1) + 3 * TC) * sizeof(uint32_t);
+    const size_t smem = ((size_t)N * (TC + 1) + 3 * TC + 1) * sizeof(uint32_t);
     auto kern = owner_select_kernel<L, R, TC>;
     static size_t configured = 48 * 1024;
     if (smem > configured) {

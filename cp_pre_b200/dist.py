@@ -154,6 +154,7 @@ def _cuda_kernels():
 
 
 _SYMM = {}
+PENDING = []      # overflow counters of deferred fused quantiles (device tensors)
 LAST_STATS = {}   # diagnostics of the last fused quantile (overflowing cells, network size)
 _TUNE = {}     # self-tuning of the owner's network size, keyed by problem shape
 
@@ -184,7 +185,16 @@ def _barrier(flag: torch.Tensor, group):
     dist.all_reduce(flag, group=group)
 
 
-def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int):
+def pending_overflow() -> int:
+    """Settles every deferred fused quantile since the last call: one host sync, returns how many
+    cells could not be answered from their candidate windows (0 = every deferred result stands)."""
+    total = 0
+    while PENDING:
+        total += int(PENDING.pop().sum().item())
+    return total
+
+
+def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int, defer: bool = False):
     """K3x: `_window_quantile` with every exchange inside the kernels (include/cppre.h).  Per
     quantile: K3t local order statistic -> keys stored into every peer -> barrier -> window scan,
     headers + candidates stored into the owners -> barrier -> owner select, qhat stored into
@@ -219,6 +229,12 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     counts = [torch.empty_like(over) for _ in range(w)]
     dist.all_gather(counts, over, group=group)                # also the barrier that orders the q stores
     q = qbuf[:cells].clone()
+    if defer:
+        # no host round trip here: the caller consumes q right away and settles the overflow
+        # counters of all deferred calls later with `pending_overflow()`; a non-zero total means
+        # those results must be recomputed with defer=False (which redoes the cells exactly)
+        PENDING.append(torch.stack(counts))
+        return q
     counts = torch.stack(counts).cpu()
     LAST_STATS.update(overflow_cells=int(counts.sum()), network=network, slots=slots)
     if int(counts.max()) > OVERFLOW_CAP // 2 and network < 1024:
@@ -328,12 +344,13 @@ OVERFLOW_CAP = 8192
 
 def owner_network(world: int, slots: int) -> int:
     """Keys the owner of a cell slab sorts per cell: a power of two above the number of real
-    candidates the union of `world` brackets holds (about 2.5 per rank at world = 2 and 6 per rank
-    at world = 8 on average for alpha = 0.1, n = 256, but a cell whose ranks disagree by 2-3
-    sigma holds several times that, and at 3.3 M cells per step those cells exist; the rare cell
-    above the network is redone exactly), never more than the candidate rows.
-    `_fused_window_quantile` doubles it when too many cells overflow."""
-    need = max(32, 32 * world)
+    candidates the union of `world` brackets holds.  Measured on |N(0,1)| scores, alpha = 0.1,
+    n = 256 per rank, 3.3 M cells (tools/k3x_diag.py): world 2 -> 12 per cell on average, 62 at
+    most; world 8 -> 110 on average, 224 at the 99.9th percentile, 323 at most.  The fused owner
+    kernel sorts N, N/2 or N/4 keys depending on the fullest cell of each 32-cell tile, so the
+    capacity is sized for the maximum (64 per rank) and costs only where it is needed; a cell
+    above it is redone exactly.  Never more than the candidate rows."""
+    need = max(32, 64 * world)
     net = 32
     while net < need and net < world * slots:
         net *= 2
@@ -342,7 +359,7 @@ def owner_network(world: int, slots: int) -> int:
 
 def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
                        select_fn: Optional[Callable] = None, kernels: Optional[dict] = None,
-                       slots: int = 40, mode: str = "auto") -> torch.Tensor:
+                       slots: int = 56, mode: str = "auto", defer: bool = False) -> torch.Tensor:
     """scores: rank-local [n_local, cells...] (same n_local on every rank).  Returns
     [len(ranks), cells...] order statistics over the global n_local*world samples, on every rank.
 
@@ -350,7 +367,12 @@ def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
     NVLink instead of n_local); cells that overflow the window are redone exactly from their
     full columns, and past OVERFLOW_CAP such cells the whole tensor is transposed instead
     (decided collectively, so every process takes the same path); "window" raises instead of
-    transposing; "exchange" always transposes the whole tensor."""
+    transposing; "exchange" always transposes the whole tensor.
+
+    defer=True (fused CUDA path only) skips the host round trip that checks the overflow
+    counters, so the next kernel can be enqueued while this one runs; the caller MUST then call
+    `pending_overflow()` before trusting the results and recompute with defer=False when it
+    returns non-zero."""
     w = _world(group)
     if kernels is None and select_fn is None:
         kernels = _cuda_kernels()
@@ -365,7 +387,10 @@ def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
     out = []
     for k in ranks:
         fused = ("owner" in kernels and scores.is_cuda and os.environ.get("CPPRE_FUSED_EXCHANGE", "1") != "0")
-        q = (_fused_window_quantile if fused else _window_quantile)(scores, k, group, kernels, slots)
+        if fused:
+            q = _fused_window_quantile(scores, k, group, kernels, slots, defer)
+        else:
+            q = _window_quantile(scores, k, group, kernels, slots)
         if q is None:
             if mode == "window":
                 raise RuntimeError(f"candidate window overflowed in more than {OVERFLOW_CAP} cells (slots={slots})")
