@@ -663,13 +663,18 @@ __device__ __forceinline__ uint32_t pack_header(uint32_t above, uint32_t inside,
     return (above & 0xffffffu) | (inside << 24) | (open ? 0x80000000u : 0u);
 }
 
-__global__ void __launch_bounds__(128, 8)
+// T = lanes (cells) per CTA.  128 lanes x 60 candidate slots = 30.7 KB of shared memory per CTA; the
+// carve-out is held at 164 KB (5 CTAs = 20 warps x 32 loads in flight) so that 64 KB of L1 remain for
+// the lines in flight: with the carve-out at its maximum the same kernel measured 0.77 instead of
+// 0.57 ms, and 64-lane CTAs (256-byte instead of 512-byte row pieces) were as slow.
+template <int T>
+__global__ void __launch_bounds__(T, 1024 / T)
 window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64_t cells,
                        const uint32_t* keys, int64_t cells_pad, int32_t W, int64_t slab, uint32_t* overflow,
                        int32_t* __restrict__ overflow_cells, int32_t overflow_cap, const PeerPtrs peers) {
-    extern __shared__ float slots[];                 // [W][128]
+    extern __shared__ float slots[];                 // [W][T]
     const int tid = threadIdx.x;
-    const int64_t c = (int64_t)blockIdx.x * 128 + tid;
+    const int64_t c = (int64_t)blockIdx.x * T + tid;
     const bool live = c < cells;
     uint32_t klo = 0xffffffffu, khi = 0u;
     if (live)
@@ -698,10 +703,10 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
                 "setp.le.u32 q, %5, %6;\n\t"             // inside the bracket
                 "setp.lt.and.u32 p, %1, %7, q;\n\t"      // and a slot is left
                 "@p st.shared.f32 [%2], %8;\n\t"
-                "@p add.u32 %2, %2, 512;\n\t"
+                "@p add.u32 %2, %2, %9;\n\t"
                 "@q add.u32 %1, %1, 1;\n\t}"
                 : "+r"(above), "+r"(inside), "+r"(sa)
-                : "r"(key), "r"(khi), "r"(t), "r"(span), "r"(wmax), "f"(v)
+                : "r"(key), "r"(khi), "r"(t), "r"(span), "r"(wmax), "f"(v), "n"(4 * T)
                 : "memory");
         };
         // two batches of 16 loads in flight per lane: the next batch is requested before the
@@ -740,7 +745,7 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
     // every lane stores every row up to the warp's longest list (its own rows beyond `inside` are
     // don't-care words the owner never reads): a full warp row is four whole 32-byte sectors,
     // which is what NVLink moves efficiently -- lane-predicated stores cost 2x here at 8 GPUs
-    for (uint32_t s = 0; s < rows; ++s) dst[(int64_t)(s + 1) * slab] = slots[s * 128 + tid];
+    for (uint32_t s = 0; s < rows; ++s) dst[(int64_t)(s + 1) * slab] = slots[s * T + tid];
 }
 
 // Owner side.  recv = [w][1 + W][slab]: row 0 of block r holds rank r's headers, rows 1.. its
@@ -1187,16 +1192,19 @@ int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, 
     CPPRE_REQUIRE(n < (int64_t(1) << 24), CPPRE_ERR_UNSUPPORTED, "n too large for the packed count");
     if (cells == 0) return CPPRE_OK;
     CPPRE_REQUIRE((d_scores || n == 0) && d_keys && d_overflow, CPPRE_ERR_BAD_ARG, "null pointer");
-    const int64_t blocks = (cells + 127) / 128;
+    constexpr int T = 128;
+    const int64_t blocks = (cells + T - 1) / T;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
-    const size_t smem = (size_t)slots * 128 * sizeof(float);
-    static size_t configured = 48 * 1024;
+    const size_t smem = (size_t)slots * T * sizeof(float);
+    static size_t configured = 0;
     if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem));
+        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel<T>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                              72));
         configured = smem;
     }
-    window_exchange_kernel<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
+    window_exchange_kernel<T><<<(unsigned)blocks, T, smem, (cudaStream_t)stream>>>(
         d_scores, row_stride, (int32_t)n, cells, d_keys, cells_pad, slots, slab, d_overflow, d_overflow_cells,
         overflow_cap, peers);
     CPPRE_CHECK_LAUNCH();

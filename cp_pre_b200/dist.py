@@ -359,7 +359,7 @@ def owner_network(world: int, slots: int) -> int:
 
 def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
                        select_fn: Optional[Callable] = None, kernels: Optional[dict] = None,
-                       slots: int = 56, mode: str = "auto", defer: bool = False) -> torch.Tensor:
+                       slots: int = 60, mode: str = "auto", defer: bool = False) -> torch.Tensor:
     """scores: rank-local [n_local, cells...] (same n_local on every rank).  Returns
     [len(ranks), cells...] order statistics over the global n_local*world samples, on every rank.
 

@@ -25,7 +25,7 @@ def timed(fn, reps=5):
 
 def main():
     world = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-    slots = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+    slots = int(sys.argv[2]) if len(sys.argv) > 2 else 60
     n, cells = 256, 50 * 256 * 256
     g = torch.Generator(device="cuda").manual_seed(0)
     s = torch.randn((n, cells), device="cuda", generator=g).abs_()     # every emulated rank scans this shard
