@@ -75,8 +75,9 @@ SIGNATURES = {
     "cppre_window_compact": (C.c_int, [_P, _I64, _I64, _I64, _P, _P, C.c_int32, _I64, _P, _P, _P, _P, C.c_int32,
                                        C.POINTER(C.c_void_p), C.c_int32, C.c_int32, _P]),
     "cppre_select_from_top": (C.c_int, [_P, _I64, _I64, _I64, _P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, _I64, _P]),
+    "cppre_peer_copy": (C.c_int, [_P, _I64, _I64, C.POINTER(C.c_void_p), C.c_int32, _P]),
     "cppre_peer_bcast_keys": (C.c_int, [_P, _I64, _I64, C.POINTER(C.c_void_p), C.c_int32, C.c_int32, _P]),
-    "cppre_window_exchange": (C.c_int, [_P, _I64, _I64, _I64, _P, _I64, C.c_int32, _I64, C.POINTER(C.c_void_p),
+    "cppre_window_exchange": (C.c_int, [_P, _I64, _I64, _I64, _P, _I64, C.c_int32, C.c_int32, _I64, C.POINTER(C.c_void_p),
                                         C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     "cppre_owner_select": (C.c_int, [_P, C.c_int32, C.c_int32, _I64, _I64, C.c_int32, C.c_int32, _I64,
                                      C.POINTER(C.c_void_p), C.c_int32, _P, _P, C.c_int32, _P]),

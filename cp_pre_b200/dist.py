@@ -150,7 +150,7 @@ def _cuda_kernels():
     from . import ops
     return {"select": ops.select_ranks, "keys": ops.ordered_keys, "window": ops.window_compact,
             "top": ops.select_from_top, "peer_exchange": True, "bcast_keys": ops.peer_bcast_keys,
-            "window_x": ops.window_exchange, "owner": ops.owner_select}
+            "window_x": ops.window_exchange, "owner": ops.owner_select, "peer_copy": ops.peer_copy}
 
 
 _SYMM = {}
@@ -177,6 +177,14 @@ def _peer_recv_buffer(world: int, slots: int, slab: int, device, group):
     """Every rank's candidate receive buffer [world, slots, slab] (K3w stores into the peers'
     buffers directly over NVLink, no all-to-all call)."""
     return _symm_buffer("recv", (world, slots, slab), torch.float32, device, group)
+
+
+def _keys_by_allreduce(world: int) -> bool:
+    """Bracket exchange: NCCL MAX all-reduce (True) or peer-store broadcast of the keys (False).
+    CPPRE_KEYS_ALLREDUCE=0/1 overrides; default: all-reduce from 4 ranks up, where the broadcast's
+    world x 13 MB per rank starts to dominate."""
+    env = os.environ.get("CPPRE_KEYS_ALLREDUCE")
+    return (env != "0") if env is not None else world >= 4
 
 
 def _barrier(flag: torch.Tensor, group):
@@ -210,7 +218,6 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     J = -(-kt // w)
     slab = (cells + w - 1) // w
     cells_pad = (slab * w + 3) // 4 * 4
-    keys, key_ptrs = _symm_buffer("keys", (w, cells_pad), torch.int32, dev, group)
     recv, recv_ptrs = _symm_buffer("recvx", (w, 1 + slots, slab), torch.float32, dev, group)
     qbuf, q_ptrs = _symm_buffer("q", (cells_pad,), torch.float32, dev, group)
     flag = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -218,14 +225,27 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     over_cells = torch.full((OVERFLOW_CAP,), -1, dtype=torch.int32, device=dev)
 
     a = kern["select"](flat, [n - J])[0]
-    kern["bcast_keys"](a, cells_pad, key_ptrs, me)
-    _barrier(flag, group)
-    kern["window_x"](flat, keys, slots, slab, recv_ptrs, me, over, over_cells)
+    if _keys_by_allreduce(w):
+        # bracket by one MAX all-reduce of [~key, key] (2 x 13 MB through the switch, reduced in it
+        # where NVLS is up) instead of world x 13 MB of peer stores + a barrier
+        ak = kern["keys"](a).reshape(-1)
+        both = torch.empty((2, cells_pad), dtype=torch.int32, device=dev)
+        both[0, :cells] = ~ak
+        both[1, :cells] = ak
+        dist.all_reduce(both, op=dist.ReduceOp.MAX, group=group)
+        kern["window_x"](flat, both, slots, slab, recv_ptrs, me, over, over_cells, 1)
+    else:
+        keys, key_ptrs = _symm_buffer("keys", (w, cells_pad), torch.int32, dev, group)
+        kern["bcast_keys"](a, cells_pad, key_ptrs, me)
+        _barrier(flag, group)
+        kern["window_x"](flat, keys, slots, slab, recv_ptrs, me, over, over_cells)
     _barrier(flag, group)
     live = max(0, min(slab, cells - me * slab))
     tune = ("net", w, n, cells, slots)
     network = min(1024, owner_network(w, slots) << _TUNE.get(tune, 0))
-    kern["owner"](recv, live, kt, network, me * slab, q_ptrs, over, over_cells)
+    kern["owner"](recv, live, kt, network, me * slab, [q_ptrs[me]], over, over_cells)     # my slab, written locally
+    if live > 0:                                                                          # ... then pushed to the peers
+        kern["peer_copy"](qbuf[me * slab:me * slab + live], me * slab, [p for r, p in enumerate(q_ptrs) if r != me])
     counts = [torch.empty_like(over) for _ in range(w)]
     dist.all_gather(counts, over, group=group)                # also the barrier that orders the q stores
     q = qbuf[:cells].clone()

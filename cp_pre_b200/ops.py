@@ -330,6 +330,17 @@ def _ptr_array(ptrs: Sequence[int]):
     return (C.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
 
 
+def peer_copy(src: torch.Tensor, dst_offset_words: int, peer_dst: Sequence[int]):
+    """src (contiguous, 4-byte elements) -> every listed peer buffer at word offset dst_offset_words."""
+    if not peer_dst or src.numel() == 0:
+        return
+    lib = L.load()
+    assert src.is_contiguous() and src.element_size() == 4
+    with torch.cuda.device(src.device):
+        L.check(lib.cppre_peer_copy(_ptr(src), src.numel(), int(dst_offset_words), _ptr_array(peer_dst), len(peer_dst),
+                                    _stream(src.device)))
+
+
 def peer_bcast_keys(vals: torch.Tensor, cells_pad: int, peer_keys: Sequence[int], my_rank: int):
     """K3x-1: ordered uint32 key of vals[c] -> every peer's key buffer [world, cells_pad] at [my_rank, c]."""
     lib = L.load()
@@ -340,15 +351,17 @@ def peer_bcast_keys(vals: torch.Tensor, cells_pad: int, peer_keys: Sequence[int]
 
 
 def window_exchange(scores: torch.Tensor, keys: torch.Tensor, slots: int, slab: int, peer_recv: Sequence[int],
-                    my_rank: int, overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
+                    my_rank: int, overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None,
+                    key_mode: int = 0):
     """K3x-2: scores [n, cells...]; keys = this rank's [world, cells_pad] key buffer (int32 storage of uint32
-    keys).  Headers + candidates go straight into the owners' receive buffers [world, 1+slots, slab]."""
+    keys; key_mode 0) or the MAX-all-reduced [2, cells_pad] pair [~min, max] of signed keys (key_mode 1).
+    Headers + candidates go straight into the owners' receive buffers [world, 1+slots, slab]."""
     lib = L.load()
     fs, rs = _rows(scores)
     n, cells = fs.shape
     cap = 0 if overflow_cells is None else overflow_cells.numel()
     with torch.cuda.device(scores.device):
-        L.check(lib.cppre_window_exchange(_ptr(fs), rs, n, cells, _ptr(keys), int(keys.shape[1]), int(slots), int(slab),
+        L.check(lib.cppre_window_exchange(_ptr(fs), rs, n, cells, _ptr(keys), int(keys.shape[1]), int(key_mode), int(slots), int(slab),
                                           _ptr_array(peer_recv), len(peer_recv), int(my_rank), _ptr(overflow),
                                           _ptr(overflow_cells), cap, _stream(scores.device)))
 

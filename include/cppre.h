@@ -232,7 +232,10 @@ int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows,
  *      d_vals[c] -> h_peer_keys[r][my_rank * cells_pad + c] for every r (cells_pad % 4 == 0).
  *      Replaces cppre_ordered_keys + the MIN/MAX all-reduce: every rank then holds all n_peers
  *      keys of every cell and takes min / max itself.
- *   2. cppre_window_exchange: reads d_keys = this rank's [n_peers][cells_pad] key buffer, scans the
+ *   2. cppre_window_exchange: reads d_keys = this rank's [n_peers][cells_pad] key buffer (key_mode 0)
+ *      or, key_mode 1, a [2][cells_pad] buffer holding [~min, max] of the signed keys of
+ *      cppre_ordered_keys after a MAX all-reduce (26 MB through the switch instead of world x 13 MB
+ *      of peer stores: the cheaper bracket exchange from 4 GPUs up), scans the
  *      local scores once and stores, for the owner r = c / slab of cell c, into
  *      h_peer_recv[r][my_rank][1 + slots][slab]: row 0 = header word
  *      (#{x > hi} in bits 0..23, #candidates in bits 24..30, bit 31 = the cell holds a NaN on
@@ -246,10 +249,15 @@ int cppre_select_from_top(const float* d_cand, int64_t row_stride, int64_t rows,
  *      the all-gather of qhat, fused.  NaN where a header carries the NaN bit; cells that cannot
  *      be answered (bracket missed, a list was cut, more than `network` candidates) are counted
  *      in *d_overflow, listed in d_overflow_cells and written as NaN for the caller to redo. */
+/* n_words 32-bit words from d_src -> h_peer_dst[r] + dst_offset_words for every listed peer (wide stores
+ * over NVLink): used to push the owner's slab of qhat to the other ranks after cppre_owner_select wrote
+ * it locally (h_peer_q = {own buffer}); one pass of 128-bit stores instead of per-CTA peer stores. */
+int cppre_peer_copy(const void* d_src, int64_t n_words, int64_t dst_offset_words, void* const* h_peer_dst,
+                    int32_t n_peers, void* stream);
 int cppre_peer_bcast_keys(const float* d_vals, int64_t cells, int64_t cells_pad, void* const* h_peer_keys,
                           int32_t n_peers, int32_t my_rank, void* stream);
 int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, int64_t cells,
-                          const uint32_t* d_keys, int64_t cells_pad, int32_t slots, int64_t slab,
+                          const uint32_t* d_keys, int64_t cells_pad, int32_t key_mode, int32_t slots, int64_t slab,
                           void* const* h_peer_recv, int32_t n_peers, int32_t my_rank, uint32_t* d_overflow,
                           int32_t* d_overflow_cells, int32_t overflow_cap, void* stream);
 int cppre_owner_select(const float* d_recv, int32_t n_ranks, int32_t slots, int64_t slab, int64_t cells,

@@ -338,7 +338,8 @@ def test_window_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alp
 
 @pytest.mark.parametrize("world,n_loc,alpha,cells", [(2, 256, 0.1, 1000), (8, 64, 0.1, 1003), (4, 100, 0.05, 517),
                                                      (3, 50, 0.5, 1000), (8, 256, 0.1, 4096)])
-def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alpha, cells):
+@pytest.mark.parametrize("key_mode", [0, 1])
+def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_loc, alpha, cells, key_mode):
     """K3x (keys broadcast -> window scan with in-band headers -> owner select with the qhat
     broadcast), the ranks emulated one after the other on this GPU: plain device buffers stand in
     for the peers' symmetric memory.  Bit-equal to np.quantile over the union; NaN cells are NaN;
@@ -360,14 +361,23 @@ def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_
     qbuf = [torch.full((cells_pad,), -7.0, device="cuda") for _ in range(world)]
     ov = torch.zeros(1, dtype=torch.int32, device="cuda")
     cells_ov = torch.full((256,), -1, dtype=torch.int32, device="cuda")
+    stats = [ops.select_ranks(s, [n_loc - J])[0] for s in shards]
+    if key_mode == 0:                                          # keys stored into every peer
+        for me in range(world):
+            ops.peer_bcast_keys(stats[me], cells_pad, [t.data_ptr() for t in keys], me)
+    else:                                                      # [~min, max] of signed keys, as a MAX all-reduce leaves it
+        ak = torch.stack([ops.ordered_keys(a) for a in stats])
+        both = torch.zeros((2, cells_pad), dtype=torch.int32, device="cuda")
+        both[0, :cells], both[1, :cells] = (~ak).max(0).values, ak.max(0).values
+        keys = [both] * world
     for me, s in enumerate(shards):
-        ops.peer_bcast_keys(ops.select_ranks(s, [n_loc - J])[0], cells_pad, [t.data_ptr() for t in keys], me)
-    for me, s in enumerate(shards):
-        ops.window_exchange(s, keys[me], slots, slab, [t.data_ptr() for t in recv], me, ov, cells_ov)
-    for me in range(world):
+        ops.window_exchange(s, keys[me], slots, slab, [t.data_ptr() for t in recv], me, ov, cells_ov, key_mode)
+    for me in range(world):                                    # owner writes its slab locally, then pushes it
         live = max(0, min(slab, cells - me * slab))
-        ops.owner_select(recv[me], live, kt, D.owner_network(world, slots), me * slab, [t.data_ptr() for t in qbuf],
+        ops.owner_select(recv[me], live, kt, D.owner_network(world, slots), me * slab, [qbuf[me].data_ptr()],
                          ov, cells_ov)
+        ops.peer_copy(qbuf[me][me * slab:me * slab + live], me * slab,
+                      [t.data_ptr() for r, t in enumerate(qbuf) if r != me])
     want = O.calibrate(full, N, alpha)
     listed = set(int(c) for c in cells_ov.cpu().numpy() if c >= 0)
     assert int(ov.item()) <= 256

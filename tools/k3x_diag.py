@@ -44,7 +44,7 @@ def main():
     out["total_max"] = float(tot.max())
     out["cells_total_gt_network"] = int((tot > network).sum())
     for me in range(world):
-        ops.owner_select(recv[me], slab, kt, network, me * slab, [t.data_ptr() for t in qbuf], ov, ovc)
+        ops.owner_select(recv[me], slab, kt, network, me * slab, [qbuf[me].data_ptr()], ov, ovc)
     out["overflow_after_owner"] = int(ov.item())
     print(json.dumps(out))
 

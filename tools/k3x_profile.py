@@ -57,7 +57,8 @@ def main():
     hdr = recv[0][:, 0].view(torch.int32)
     out["mean_inside"] = float(((hdr >> 24) & 0x7f).float().mean())
     out["owner"] = timed(lambda: ops.owner_select(recv[0], slab, kt, D.owner_network(world, slots), 0,
-                                                  [t.data_ptr() for t in qbuf], ov, ovc))
+                                                  [qbuf[0].data_ptr()], ov, ovc))
+    out["peer_copy"] = timed(lambda: ops.peer_copy(qbuf[0][:slab], 0, [t.data_ptr() for t in qbuf[1:]]))
     out["overflow"] = int(ov.item())
     print(json.dumps(out))
 
