@@ -814,11 +814,19 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
                 l = (h >> 24) & 0x7fu;
             }
             const uint32_t rows = __reduce_max_sync(0xffffffffu, l);
-            for (uint32_t sl = 0; sl < rows; ++sl) {
-                if (sl >= l) continue;
-                const uint32_t bits = __float_as_uint(__ldcg(src + (int64_t)(1 + sl) * slab));
-                const uint32_t pos = atomicAdd(&colcount[col], 1u);
-                if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits);
+            // eight row loads in flight per lane before any is consumed: one load per trip made the
+            // fill a chain of L2 round trips (the whole kernel was latency-bound, 26 % issue-active)
+            for (uint32_t sl0 = 0; sl0 < rows; sl0 += 8) {
+                uint32_t bits[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    bits[u] = sl0 + u < l ? __float_as_uint(__ldcg(src + (int64_t)(1 + sl0 + u) * slab)) : 0u;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (sl0 + u < l) {
+                        const uint32_t pos = atomicAdd(&colcount[col], 1u);
+                        if (pos < (uint32_t)N) tile[pos * LD + col] = float_to_key(bits[u]);
+                    }
             }
         }
     }
