@@ -330,3 +330,62 @@ def test_autograd_through_operator_matches_torch_conv3d():
     ref = (F.conv3d(u2.unsqueeze(1), k[None, None], padding=1).squeeze(1) ** 2).sum()
     ref.backward()
     assert_close_rel(u.grad.cpu().numpy(), u2.grad.cpu().numpy(), 1e-5, "grad")
+
+
+def test_burgers_joint_cp_at_full_config_size():
+    """BASELINE config 2 at its full size ([4096,100,1024], 1-D Burgers + Joint CP) through
+    size-independent properties: the fused SCORE and COVER epilogues reproduce, bit for bit, what
+    the stored residual gives (same arithmetic, nothing but [BS] numbers written); the joint
+    quantile is the order statistic np.quantile(method='higher') picks; and a slab of the residual
+    agrees with the CPU oracle [ref: Joint/Burgers_Residuals_CP.py:182-187,212-260]."""
+    from Neural_PDE.UQ.inductive_cp import calibrate
+    m1, c = _mods()["1d"], synth.BURGERS
+    pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                          c["dx"], c["dt"], c["nu"])
+    bs, nt, nx = 4096, 100, 1024
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = torch.linspace(0, 1, nx, device="cuda")
+    u = torch.sin(2 * np.pi * (x[None, None, :] + torch.rand(bs, 1, 1, device="cuda", generator=g))) \
+        * torch.exp(-torch.linspace(0, 1, nt, device="cuda"))[None, :, None] \
+        + 0.01 * torch.randn(bs, nt, nx, device="cuda", generator=g)
+    res = pb.residual(u, boundary=True)
+    assert L.last_path() == "tma" and res.shape == u.shape
+    want = O.residual_burgers(u[:4].cpu().numpy(), c["dx"], c["dt"], c["nu"])
+    assert_close_rel(res[:4, 1:-1, 1:-1].cpu().numpy(), want[:, 1:-1, 1:-1], TOL, "oracle slab")
+    n_cal = bs // 2
+    inner = res[:, 1:-1, 1:-1]
+    mod = inner[:n_cal].std(dim=0, unbiased=False)                     # modulation over the calibration half
+    inv = torch.zeros(nt, nx, device="cuda")
+    inv[1:-1, 1:-1] = 1.0 / mod
+    scores = pb.joint_scores(u, inv)                                   # one pass, [BS] floats written
+    assert torch.equal(scores, (inner.abs() * inv[1:-1, 1:-1]).amax(dim=(1, 2)))
+    qhat = calibrate(scores[:n_cal].cpu().numpy(), n_cal, 0.1)
+    assert qhat == np.sort(scores[:n_cal].cpu().numpy())[O.calibrate_rank(n_cal, n_cal, 0.1)]
+    half = torch.zeros(nt, nx, device="cuda")
+    half[1:-1, 1:-1] = mod
+    inside = pb.coverage_counts(u[n_cal:], float(qhat), half)          # -qhat*mod <= R <= qhat*mod, sets never built
+    band = half[1:-1, 1:-1] * float(qhat)
+    assert torch.equal(inside.to(torch.int64), (inner[n_cal:].abs() <= band).sum(dim=(1, 2)))
+    joint_cov = float((inside == pb.interior_cells(u.shape)).float().mean())
+    assert 0.85 <= joint_cov <= 0.95, joint_cov                        # exchangeable halves: ~1 - alpha
+
+
+def test_mhd_programs_on_a_config5_per_gpu_slab():
+    """BASELINE config 5 (2-D MHD, Nt=100, 256x256, 6 fields; 256 samples per GPU at 8 GPUs) on a
+    32-sample slab of the per-GPU shape: every MHD program runs on the TMA kernel, its fused joint
+    score equals the max of its stored residual bit for bit, and one sample agrees with the oracle."""
+    o, c = _programs_2d(), synth.MHD
+    bs, nt, n = 32, 100, 256
+    g = torch.Generator(device="cuda").manual_seed(5)
+    w = 0.1 * torch.randn(bs, 6, nt, n, n, device="cuda", generator=g)
+    w[:, 0] += 1.0                                                      # rho, a divisor: strictly positive
+    w[:, 3] += 1.0
+    f1 = [w[:1, j].cpu().numpy() for j in range(6)]
+    for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+        p = programs.mhd(eq, o["D_t"], o["D_x"], o["D_y"], c["gamma"])
+        r = p.residual(w, boundary=True)
+        assert L.last_path() == "tma", eq
+        s = p.joint_scores(w)
+        assert torch.equal(s, r[:, 1:-1, 1:-1, 1:-1].abs().amax(dim=(1, 2, 3))), eq
+        want = O.residual_mhd(eq, *f1, gamma=c["gamma"], ops=O.ops_2d())
+        assert_close_rel(r[:1].cpu().numpy(), want, TOL, eq)
