@@ -48,6 +48,7 @@ constexpr int kMaxStages = 8;
 template <int NF>
 struct alignas(64) StarParams {
     CUtensorMap map[NF];
+    CUtensorMap wmap;     // per-cell epilogue weight [N2][N1][N0] (used when it is staged by TMA, see WTMA)
     StarCoef coef;
     float scalars[CPPRE_MAX_SCALARS];
     EpiDev e;
@@ -95,6 +96,13 @@ __device__ __forceinline__ void bar_arrive(uint32_t id, uint32_t threads) {
 }
 __device__ __forceinline__ void bar_sync(uint32_t id, uint32_t threads) {
     asm volatile("barrier.cta.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
 }
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
                                             int c0, int c1, int c2, int c3) {
@@ -173,7 +181,13 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int SR = TX + 2 * HALO;             // smem rows per tile
     constexpr uint32_t BOX_BYTES = (uint32_t)(SR * kTWP * sizeof(float));
     constexpr uint32_t BUF_BYTES = (BOX_BYTES + 127u) & ~127u;   // one (stage, field) tile
-    constexpr uint32_t STAGE_BYTES = NF * BUF_BYTES;
+    // WTMA: with a compiled-in weight-only operand set on 3-D problems in a reducing mode (the
+    // marginal COVER / joint SCORE launches), the per-cell weight tile of plane t rides the same
+    // TMA ring as the fields: the epilogue reads it with one 128-bit ld.shared instead of an
+    // ld.global whose L2 round trip was 25 % of the COVER kernel's stall samples.
+    constexpr bool WTMA = OPER == 2 && !BATCH_ROWS && !STORE;
+    constexpr uint32_t WBUF_BYTES = WTMA ? (uint32_t)(TX * kTW * sizeof(float)) : 0u;
+    constexpr uint32_t STAGE_BYTES = NF * BUF_BYTES + WBUF_BYTES;
     constexpr uint32_t ROW_BYTES = kTWP * sizeof(float);
     (void)SCORE;
 
@@ -207,7 +221,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     const int NPL = p.N2;
     auto issue = [&](int plane, int stage) {
         const uint32_t bar = bars + 8u * stage;
-        mbar_expect_tx(bar, BOX_BYTES * NF);
+        mbar_expect_tx(bar, BOX_BYTES * NF + WBUF_BYTES);
+        if constexpr (WTMA)
+            tma_load_3d(base + (uint32_t)stage * STAGE_BYTES + NF * BUF_BYTES, &p.wmap, bar, col0, row0, plane);
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
             const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * BUF_BYTES;
@@ -233,6 +249,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
 
     // shared address of this thread's first centre cell in ring slot 0
     const uint32_t cell0 = base + (uint32_t)(((HALO + tr * RX) * kTWP + 4 + 4 * tc) * sizeof(float));
+    // this thread's weight row 0 relative to its centre cell, within one ring slot
+    const uint32_t woff = (NF * BUF_BYTES + (uint32_t)((tr * RX * kTW + 4 * tc) * sizeof(float))) - (cell0 - base);
+    (void)woff;
     auto load_centres = [&](float (&dst)[NF][RX][4], uint32_t a) {
 #pragma unroll
         for (int f = 0; f < NF; ++f)
@@ -310,7 +329,8 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
             wq[j] = make_float4(1.f, 1.f, 1.f, 1.f);
             if (live & (1u << j)) {
                 if (has_ref) rq[j] = __ldg(reinterpret_cast<const float4*>(refp + j * ref_row));
-                if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * w_row));
+                if constexpr (WTMA) wq[j] = lds128(cur_a + woff + j * (uint32_t)(kTW * sizeof(float)));
+                else if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * w_row));
             }
         };
         fetch_operands(std::integral_constant<int, 0>{});
@@ -584,6 +604,18 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
         CPPRE_REQUIRE(rc == CUDA_SUCCESS, CPPRE_ERR_UNSUPPORTED,
                       "cuTensorMapEncodeTiled rejected field %d (CUresult %d)", f, (int)rc);
     }
+    constexpr bool WTMA = CPPRE_TMA_OPER == 2 && !BR && CPPRE_TMA_MODE != CPPRE_EPI_STORE;
+    if (WTMA) {     // weight [N2][N1][N0], contiguous fp32: box 128 x TX x 1, no halo
+        const cuuint64_t dims[3] = {(cuuint64_t)g.N0, (cuuint64_t)g.N1, (cuuint64_t)g.N2};
+        const cuuint64_t strides[2] = {(cuuint64_t)g.N0 * sizeof(float), (cuuint64_t)g.N0 * g.N1 * sizeof(float)};
+        const cuuint32_t box[3] = {(cuuint32_t)kTW, (cuuint32_t)TX, 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        CUresult rc = encode(&sp.wmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(P.epi.weight), dims,
+                             strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        CPPRE_REQUIRE(rc == CUDA_SUCCESS, CPPRE_ERR_UNSUPPORTED,
+                      "cuTensorMapEncodeTiled rejected the weight tensor (CUresult %d)", (int)rc);
+    }
     sp.coef = H.coef;
     memcpy(sp.scalars, P.scalars, sizeof(sp.scalars));
     sp.e = P.epi;
@@ -602,8 +634,8 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
         env_stages = s ? atoi(s) : 0;
     }
     int stages = env_stages > 0 ? env_stages : 4;
-    const size_t per_stage = (size_t)NF * sp.buf_bytes;
-    while (stages > 2 && stages * per_stage + 256 > 110 * 1024) --stages;
+    const size_t per_stage = (size_t)NF * sp.buf_bytes + (WTMA ? (size_t)TX * kTW * sizeof(float) : 0);
+    while (stages > 2 && stages * per_stage + 256 > 112 * 1024) --stages;      // 2 x (112 KB + 1 KB) <= 228 KB per SM
     if (stages > kMaxStages) stages = kMaxStages;
     if (stages < 2) stages = 2;
     sp.stages = stages;
