@@ -18,6 +18,10 @@ halo and no data-path collective.  Only calibration coupl
             bracket holds more candidates than the window falls back to transposing the whole
             score tensor.
 
+  Nx-slab   a single field too large for one GPU is split along x instead: one ghost row per
+            side travels (``exchange_x_halo``), everything else -- PRE, per-cell calibration --
+            is rank-local (``slab_residual``).
+
 The kernels are injected (``hist_fn`` / ``select_fn`` / ``moments_fn``) so the orchestration can
 be tested on CPU with the oracle's NumPy implementations; the defaults are the CUDA kernels and
 there is no CPU fallback in the product path.
@@ -417,6 +421,54 @@ def marginal_quantiles(scores: torch.Tensor, ranks: Sequence[int], group=None,
             q = _exchange_quantiles(scores, [k], group, select_fn)[0]
         out.append(q)
     return torch.stack(out).reshape((len(ranks),) + cell_shape)
+
+
+# ---------------------------------------------------------------------------------------
+# Nx-slab partition: one field too large for one GPU
+# ---------------------------------------------------------------------------------------
+def exchange_x_halo(padded: torch.Tensor, axis: int = -2, group=None) -> torch.Tensor:
+    """``padded`` is this rank's slab of a field split along ``axis`` (the x axis of
+    [..., Nt, Nx, Ny] data), allocated WITH one ghost row on each side: [..., nx_loc + 2, Ny].
+    Fills the ghost rows in place from the neighbouring ranks (rank-1 owns the rows below,
+    rank+1 the rows above); the two global edges keep whatever they hold -- zeros reproduce the
+    reference's zero "same" padding (F.conv3d padding=k//2, Utils/ConvOps_2d.py:135-150).
+    One send + one receive per neighbour (NCCL point-to-point over NVLink, gloo on CPU); the
+    star stencils of the hot path reach one row, so one ghost row is all that ever travels."""
+    w = _world(group)
+    if w == 1:
+        return padded
+    me = dist.get_rank(group)
+    n = padded.shape[axis]
+    lo_ghost, lo_edge = padded.select(axis, 0), padded.select(axis, 1)
+    hi_edge, hi_ghost = padded.select(axis, n - 2), padded.select(axis, n - 1)
+    ops_, bufs = [], []
+    to_global = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
+    if me > 0:
+        send, recv = lo_edge.contiguous(), torch.empty_like(lo_ghost, memory_format=torch.contiguous_format)
+        ops_ += [dist.P2POp(dist.isend, send, to_global(me - 1), group), dist.P2POp(dist.irecv, recv, to_global(me - 1), group)]
+        bufs.append((lo_ghost, recv))
+    if me < w - 1:
+        send, recv = hi_edge.contiguous(), torch.empty_like(hi_ghost, memory_format=torch.contiguous_format)
+        ops_ += [dist.P2POp(dist.isend, send, to_global(me + 1), group), dist.P2POp(dist.irecv, recv, to_global(me + 1), group)]
+        bufs.append((hi_ghost, recv))
+    for req in dist.batch_isend_irecv(ops_):
+        req.wait()
+    for ghost, recv in bufs:
+        ghost.copy_(recv)
+    return padded
+
+
+def slab_residual(program, padded_vars: torch.Tensor, axis: int = -2, group=None, residual_fn: Optional[Callable] = None):
+    """PRE of an x-slab: exchange the ghost rows, evaluate the residual program on the padded
+    slab (one K1 launch, boundary rows included) and drop the two ghost rows of the result.
+    Every kept cell sees exactly the neighbourhood it has in the undivided field, so the
+    concatenation of the ranks' results equals the single-GPU residual bit for bit.  Per-cell
+    (marginal) calibration of a slab needs no exchange at all: a rank owns all samples of its
+    cells.  ``residual_fn(padded_vars)`` replaces the CUDA program in the CPU tests."""
+    exchange_x_halo(padded_vars, axis, group)
+    full = residual_fn(padded_vars) if residual_fn is not None else program.residual(padded_vars, boundary=True)
+    n = full.shape[axis]
+    return full.narrow(axis if axis >= 0 else full.dim() + axis, 1, n - 2)
 
 
 def allreduce_counts(*values: int, device=None, group=None):

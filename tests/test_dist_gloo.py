@@ -131,6 +131,16 @@ def _worker(rank, world, port, out):
     q = D.marginal_quantiles(mine_big, [N // 2], kernels=NP_KERNELS, mode="auto", slots=1)
     res["fallback_equal"] = bool(np.array_equal(q.numpy(), ref[[N // 2]], equal_nan=True))
     D.OVERFLOW_CAP = cap
+    # Nx-slab partition of one field: ghost rows exchanged, the oracle's wave residual
+    # on the padded slab, ghost rows dropped -> the concatenation equals the residual of the whole field
+    field = rng.standard_normal((3, 6, 8 * world + 3, 12)).astype(np.float32)       # x extent not divisible
+    xlo, xhi = D.shard_range(field.shape[2], rank, world)
+    padded = torch.zeros((3, 6, xhi - xlo + 2, 12))
+    padded[:, :, 1:-1] = torch.from_numpy(field[:, :, xlo:xhi])
+    kw = O.build_kernel("2d", "t", 2) - np.float32(0.25) * O.build_kernel("2d", ("x", "y"), 2)   # wave operator
+    wave = lambda t: torch.from_numpy(O.correlate(t.numpy(), kw))
+    mine_res = D.slab_residual(None, padded, residual_fn=wave)
+    res["slab_equal"] = bool(np.array_equal(mine_res.numpy(), O.correlate(field, kw)[:, :, xlo:xhi]))
     res["counts"] = D.allreduce_counts(rank + 1, 10)
     out[rank] = res
     dist.barrier()
@@ -149,6 +159,7 @@ def test_sharded_calibration_orchestration(world):
             assert r["std_err"] < 1e-6
             assert r["marginal_equal"] and r["marginal_odd_equal"]
             assert r["window_equal"] and r["auto_equal"] and r["overflow_raises"] and r["fallback_equal"]
+            assert r["slab_equal"]
             assert r["counts"] == [world * (world + 1) // 2, 10 * world]
 
 

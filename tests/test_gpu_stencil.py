@@ -389,3 +389,23 @@ def test_mhd_programs_on_a_config5_per_gpu_slab():
         assert torch.equal(s, r[:, 1:-1, 1:-1, 1:-1].abs().amax(dim=(1, 2, 3))), eq
         want = O.residual_mhd(eq, *f1, gamma=c["gamma"], ops=O.ops_2d())
         assert_close_rel(r[:1].cpu().numpy(), want, TOL, eq)
+
+
+def test_x_slab_partition_equals_the_undivided_field():
+    """Nx-slab partition (one field too large for one GPU), two slabs emulated on
+    this GPU: ghost rows filled by hand the way dist.exchange_x_halo fills them, the NS momentum
+    program on each padded slab, ghost rows dropped -> bit-identical to the undivided launch."""
+    o, n = _programs_2d(), synth.NS
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    v = cuda(synth.fields(61, 3, (4, 9, 40, 128)))                     # [BS, F, Nt, Nx, Ny]
+    want = prog.residual(v, boundary=True)
+    parts = []
+    for lo, hi in ((0, 24), (24, 40)):
+        padded = torch.zeros((4, 3, 9, hi - lo + 2, 128), device="cuda")
+        padded[..., 1:-1, :] = v[..., lo:hi, :]
+        if lo > 0:
+            padded[..., 0, :] = v[..., lo - 1, :]
+        if hi < 40:
+            padded[..., -1, :] = v[..., hi, :]
+        parts.append(prog.residual(padded, boundary=True)[..., 1:-1, :])
+    assert torch.equal(torch.cat(parts, dim=-2), want)
