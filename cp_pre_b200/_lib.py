@@ -26,7 +26,7 @@ PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS
 
 EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1
-FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2 = 1, 2, 4, 8
+FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16 = 1, 2, 4, 8, 16
 PATH_AUTO, PATH_GENERIC, PATH_TMA = 0, 1, 2
 
 BC_DIRICHLET, BC_NEUMANN, BC_PERIODIC, BC_SYMMETRIC, BC_NONE = range(5)

@@ -96,6 +96,7 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
     CPPRE_REQUIRE(epi->mode == CPPRE_EPI_STORE || epi->mode == CPPRE_EPI_SCORE || epi->mode == CPPRE_EPI_COVER,
                   CPPRE_ERR_BAD_ARG, "unknown epilogue mode %d", epi->mode);
     P.epi.mode = epi->mode;
+    P.in_bf16 = (epi->flags & CPPRE_FLAG_IN_BF16) ? 1 : 0;
     P.epi.flags = epi->flags;
     P.epi.reduce = epi->reduce;
     P.epi.ref = epi->d_ref;
@@ -172,6 +173,9 @@ int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
         // nothing has been launched in that case, so AUTO takes the generic kernel instead
         if (rc != CPPRE_ERR_UNSUPPORTED || path == CPPRE_PATH_TMA) return rc;
     }
+    CPPRE_REQUIRE(!P.in_bf16, CPPRE_ERR_UNSUPPORTED,
+                  "bf16 fields are served by the TMA star kernel only (star stencils, 'same' padding, N0 %% 8 == 0, "
+                  "16-byte aligned rows and strides)");
     set_path("generic");
     return launch_generic(P, st);
 }

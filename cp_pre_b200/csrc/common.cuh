@@ -103,6 +103,7 @@ struct Prepared {
     EpiDev epi;
     float scalars[CPPRE_MAX_SCALARS];
     int kind, n_fields, n_slots;
+    int in_bf16;   // CPPRE_FLAG_IN_BF16: fields[].p point to bfloat16 elements
 };
 int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_field_t* fields,
             const cppre_epilogue_t* epi, Prepared* out);
@@ -118,13 +119,29 @@ int launch_generic(const Prepared& P, cudaStream_t stream);
 CPPRE_TMA_TU(store_dyn) CPPRE_TMA_TU(store_plain)
 CPPRE_TMA_TU(score_dyn) CPPRE_TMA_TU(score_plain) CPPRE_TMA_TU(score_w)
 CPPRE_TMA_TU(cover_dyn) CPPRE_TMA_TU(cover_w)
+CPPRE_TMA_TU(store_dyn_bf16) CPPRE_TMA_TU(store_plain_bf16)
+CPPRE_TMA_TU(score_dyn_bf16) CPPRE_TMA_TU(score_w_bf16)
+CPPRE_TMA_TU(cover_dyn_bf16) CPPRE_TMA_TU(cover_w_bf16)
 #undef CPPRE_TMA_TU
 inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
+    if (P.in_bf16)
+        return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store_dyn_bf16(prog, P)
+             : P.epi.mode == CPPRE_EPI_SCORE ? tma_eligible_score_dyn_bf16(prog, P) : tma_eligible_cover_dyn_bf16(prog, P);
     return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store_dyn(prog, P)
          : P.epi.mode == CPPRE_EPI_SCORE ? tma_eligible_score_dyn(prog, P) : tma_eligible_cover_dyn(prog, P);
 }
 inline int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
     const int oper = (P.epi.ref ? 1 : 0) | (P.epi.weight ? 2 : 0);
+    if (P.in_bf16) {
+        switch (P.epi.mode) {
+            case CPPRE_EPI_STORE:
+                return oper == 0 ? launch_tma_store_plain_bf16(prog, P, stream) : launch_tma_store_dyn_bf16(prog, P, stream);
+            case CPPRE_EPI_SCORE:
+                return oper == 2 ? launch_tma_score_w_bf16(prog, P, stream) : launch_tma_score_dyn_bf16(prog, P, stream);
+            default:
+                return oper == 2 ? launch_tma_cover_w_bf16(prog, P, stream) : launch_tma_cover_dyn_bf16(prog, P, stream);
+        }
+    }
     switch (P.epi.mode) {
         case CPPRE_EPI_STORE:
             return oper == 0 ? launch_tma_store_plain(prog, P, stream) : launch_tma_store_dyn(prog, P, stream);

@@ -42,8 +42,19 @@ constexpr int kTPR = 32;            // threads per tile row (one warp)
 constexpr int kWarps = 8;           // thread rows per CTA
 constexpr int kThreads = kTPR * kWarps;
 constexpr int kTW = 4 * kTPR;       // tile width in cells (128)
-constexpr int kTWP = kTW + 8;       // smem row: 4 halo/pad cells each side keeps the interior 16-byte aligned
 constexpr int kMaxStages = 8;
+// Field element type of this translation unit: fp32, or bf16 (CPPRE_TMA_BF16: the bf16-input
+// mode -- tiles are staged as bf16, halving the field bytes read from HBM, and widened to fp32
+// on the way into registers; all arithmetic and every output stay fp32).
+#ifndef CPPRE_TMA_BF16
+#define CPPRE_TMA_BF16 0
+#endif
+constexpr bool kBF16 = CPPRE_TMA_BF16 != 0;
+constexpr uint32_t kES = kBF16 ? 2u : 4u;      // bytes per staged field element
+// smem row: 16 bytes of halo/pad each side (4 fp32 / 8 bf16 cells).  The TMA box must START on a
+// 16-byte boundary of the global row (col0 - kHP), and the interior stays 16-byte aligned.
+constexpr int kHP = 16 / (int)kES;
+constexpr int kTWP = kTW + 2 * kHP;
 
 template <int NF>
 struct alignas(64) StarParams {
@@ -166,6 +177,26 @@ __device__ __forceinline__ float lds32(uint32_t a) {
     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
     return v;
 }
+// four / one staged field cells -> fp32 registers (bf16: one 64-bit load, widening by shift / mask)
+__device__ __forceinline__ float4 lds_cells4(uint32_t a) {
+    if constexpr (kBF16) {
+        uint32_t w0, w1;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(a));
+        return make_float4(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u),
+                           __uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
+    } else {
+        return lds128(a);
+    }
+}
+__device__ __forceinline__ float lds_cell(uint32_t a) {
+    if constexpr (kBF16) {
+        uint16_t h;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(a));
+        return __uint_as_float((uint32_t)h << 16);
+    } else {
+        return lds32(a);
+    }
+}
 
 // OPER: which optional epilogue operands exist, known at compile time (bit 0 = ref, bit 1 =
 // weight) or -1 = decided at run time (any combination; a few predicated instructions more).
@@ -179,7 +210,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr int TX = kWarps * RX;               // rows per tile
     constexpr int HALO = BATCH_ROWS ? 0 : 1;      // row halo only when rows are a stencil axis
     constexpr int SR = TX + 2 * HALO;             // smem rows per tile
-    constexpr uint32_t BOX_BYTES = (uint32_t)(SR * kTWP * sizeof(float));
+    constexpr uint32_t BOX_BYTES = (uint32_t)(SR * kTWP) * kES;
     constexpr uint32_t BUF_BYTES = (BOX_BYTES + 127u) & ~127u;   // one (stage, field) tile
     // WTMA: with a compiled-in weight-only operand set on 3-D problems in a reducing mode (the
     // marginal COVER / joint SCORE launches), the per-cell weight tile of plane t rides the same
@@ -188,7 +219,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr bool WTMA = OPER == 2 && !BATCH_ROWS && !STORE;
     constexpr uint32_t WBUF_BYTES = WTMA ? (uint32_t)(TX * kTW * sizeof(float)) : 0u;
     constexpr uint32_t STAGE_BYTES = NF * BUF_BYTES + WBUF_BYTES;
-    constexpr uint32_t ROW_BYTES = kTWP * sizeof(float);
+    constexpr uint32_t ROW_BYTES = kTWP * kES;
     (void)SCORE;
 
     // Shared memory is addressed by 32-bit shared-window addresses only (ld.shared / TMA /
@@ -228,9 +259,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         for (int f = 0; f < NF; ++f) {
             const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * BUF_BYTES;
             if constexpr (BATCH_ROWS)   // map dims (N0, N2, B, 1): tile rows are samples
-                tma_load_4d(dst, &p.map[f], bar, col0 - 4, plane, row0, 0);
+                tma_load_4d(dst, &p.map[f], bar, col0 - kHP, plane, row0, 0);
             else                        // map dims (N0, N1, N2, B)
-                tma_load_4d(dst, &p.map[f], bar, col0 - 4, row0 - HALO, plane, outer);
+                tma_load_4d(dst, &p.map[f], bar, col0 - kHP, row0 - HALO, plane, outer);
         }
     };
     if (tid == 0) {
@@ -248,7 +279,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
             for (int i = 0; i < 4; ++i) prev[f][j][i] = 0.0f;
 
     // shared address of this thread's first centre cell in ring slot 0
-    const uint32_t cell0 = base + (uint32_t)(((HALO + tr * RX) * kTWP + 4 + 4 * tc) * sizeof(float));
+    const uint32_t cell0 = base + (uint32_t)((HALO + tr * RX) * kTWP + kHP + 4 * tc) * kES;
     // this thread's weight row 0 relative to its centre cell, within one ring slot
     const uint32_t woff = (NF * BUF_BYTES + (uint32_t)((tr * RX * kTW + 4 * tc) * sizeof(float))) - (cell0 - base);
     (void)woff;
@@ -257,7 +288,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         for (int f = 0; f < NF; ++f)
 #pragma unroll
             for (int j = 0; j < RX; ++j) {
-                const float4 v = lds128(a + f * BUF_BYTES + j * ROW_BYTES);
+                const float4 v = lds_cells4(a + f * BUF_BYTES + j * ROW_BYTES);
                 dst[f][j][0] = v.x; dst[f][j][1] = v.y; dst[f][j][2] = v.z; dst[f][j][3] = v.w;
             }
     };
@@ -354,19 +385,19 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 const uint32_t a = cur_a + f * BUF_BYTES;
                 if constexpr (!BATCH_ROWS) {
                     if constexpr (j == 0) {
-                        const float4 lo = lds128(a - ROW_BYTES);
+                        const float4 lo = lds_cells4(a - ROW_BYTES);
                         xm[f][0] = lo.x; xm[f][1] = lo.y; xm[f][2] = lo.z; xm[f][3] = lo.w;
                     }
                     if constexpr (j == RX - 1) {
-                        const float4 hi = lds128(a + RX * ROW_BYTES);
+                        const float4 hi = lds_cells4(a + RX * ROW_BYTES);
                         xp[f][0] = hi.x; xp[f][1] = hi.y; xp[f][2] = hi.z; xp[f][3] = hi.w;
                     }
                 } else if constexpr (j == 0) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) { xm[f][i] = 0.0f; xp[f][i] = 0.0f; }
                 }
-                ym[f][j] = lds32(a + j * ROW_BYTES - 4u);
-                yp[f][j] = lds32(a + j * ROW_BYTES + 16u);
+                ym[f][j] = lds_cell(a + j * ROW_BYTES - kES);
+                yp[f][j] = lds_cell(a + j * ROW_BYTES + 4u * kES);
             }
         };
         const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
@@ -543,11 +574,12 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) ==
 bool layout_ok(const Prepared& P, bool batch_rows) {
     const Geometry& g = P.g;
     if (g.N0 % 4 != 0 || g.N0 < 4) return false;
+    const int64_t q = 16 / kES;                    // global strides must be multiples of 16 bytes
     for (int f = 0; f < P.n_fields; ++f) {
         const FieldView& v = P.fields[f];
         if (!aligned16(v.p) || v.s0 != 1) return false;
-        if ((g.N1 > 1 && (v.s1 % 4 != 0 || v.s1 <= 0)) || (g.N2 > 1 && (v.s2 % 4 != 0 || v.s2 <= 0)) ||
-            (g.B > 1 && (v.sb % 4 != 0 || v.sb <= 0)))
+        if ((g.N1 > 1 && (v.s1 % q != 0 || v.s1 <= 0)) || (g.N2 > 1 && (v.s2 % q != 0 || v.s2 <= 0)) ||
+            (g.B > 1 && (v.sb % q != 0 || v.sb <= 0)))
             return false;
     }
     const EpiDev& e = P.epi;
@@ -584,7 +616,7 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
         // and the byte strides stay ascending for contiguous data.  A stride on an extent-1
         // axis is never used for addressing but must still be a positive multiple of 16 bytes.
         auto fix = [&](int64_t s, uint64_t extent) -> cuuint64_t {
-            return (cuuint64_t)((extent > 1 && s > 0) ? s : g.N0) * sizeof(float);
+            return (cuuint64_t)((extent > 1 && s > 0) ? s : (kBF16 ? (g.N0 + 7) / 8 * 8 : g.N0)) * kES;
         };
         cuuint64_t dims[4], strides[3];
         cuuint32_t box[4];
@@ -598,7 +630,8 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
             box[0] = kTWP; box[1] = SR; box[2] = 1; box[3] = 1;
         }
         const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
-        CUresult rc = encode(&sp.map[f], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(v.p), dims,
+        CUresult rc = encode(&sp.map[f], kBF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                             const_cast<float*>(v.p), dims,
                              strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         CPPRE_REQUIRE(rc == CUDA_SUCCESS, CPPRE_ERR_UNSUPPORTED,
@@ -625,7 +658,7 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     sp.R = R;
     sp.col_tiles = (g.N0 + kTW - 1) / kTW;
     sp.row_tiles = (R + TX - 1) / TX;
-    sp.buf_bytes = ((uint32_t)(SR * kTWP * sizeof(float)) + 127u) & ~127u;
+    sp.buf_bytes = ((uint32_t)(SR * kTWP) * kES + 127u) & ~127u;
 
     // ring depth: as deep as fits while leaving room for >= 2 CTAs per SM
     static int env_stages = -1;

@@ -106,8 +106,9 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     f0 = fields[0]
     if any(f.shape != f0.shape for f in fields):
         raise ValueError("all fields of a residual program must share one shape")
-    if any(f.dtype != torch.float32 for f in fields):
-        raise RuntimeError("expected scalar type Float (fields must be float32)")
+    bf16 = f0.dtype == torch.bfloat16          # bf16-input mode (include/cppre.h, CPPRE_FLAG_IN_BF16)
+    if any(f.dtype != f0.dtype for f in fields) or f0.dtype not in (torch.float32, torch.bfloat16):
+        raise RuntimeError("expected scalar type Float (fields must all be float32, or all bfloat16)")
     kernels = [np.ascontiguousarray(k, dtype=np.float32) for k in kernels]
     pads = [tuple(int(v) for v in p) for p in pads]
 
@@ -158,7 +159,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         for d in range(4):
             fl[i].stride[d] = f.stride(d)
     epi = L.Epilogue()
-    epi.mode, epi.flags, epi.reduce, epi.band_q = mode, flags, reduce, float(band_q)
+    epi.mode, epi.flags, epi.reduce, epi.band_q = mode, flags | (L.FLAG_IN_BF16 if bf16 else 0), reduce, float(band_q)
     dev = f0.device
     keep = []
     if ref is not None:

@@ -44,7 +44,10 @@ class ResidualProgram:
         return ks, pads
 
     def _fields(self, vars_):
-        v = ops.to_cuda(vars_)
+        # bf16-input mode: a bfloat16 CUDA tensor is passed through as it is (the TMA kernel stages
+        # bf16 tiles and computes in fp32); everything else is brought to float32 like the reference
+        bf16 = isinstance(vars_, torch.Tensor) and vars_.dtype == torch.bfloat16
+        v = ops.to_cuda(vars_, torch.bfloat16 if bf16 else torch.float32)
         if self.field_index is None:        # single-field programs take the field itself
             fs = [v]
         else:

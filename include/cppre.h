@@ -115,7 +115,14 @@ enum {
     CPPRE_FLAG_ABS = 1,
     CPPRE_FLAG_INTERIOR_0 = 2, /* axis N0 */
     CPPRE_FLAG_INTERIOR_1 = 4, /* axis N1 */
-    CPPRE_FLAG_INTERIOR_2 = 8  /* axis N2 */
+    CPPRE_FLAG_INTERIOR_2 = 8, /* axis N2 */
+    /* bf16-input mode: every cppre_field_t::d_data points to bfloat16 elements (strides in
+     * elements), staged as bf16 and widened to fp32 in the kernel; arithmetic, reference, weight
+     * and every output stay fp32.  Halves the field bytes read (NS momentum STORE: 16 -> 10 B per
+     * grid point).  Served by the TMA star kernel only: rows must be 16-byte aligned with
+     * N0 % 8 == 0 and strides % 8 == 0, otherwise CPPRE_ERR_UNSUPPORTED.  Parity is stated
+     * against the fp32 oracle evaluated on the bf16-rounded input. */
+    CPPRE_FLAG_IN_BF16 = 16
 };
 /* Which kernel executes the program.  AUTO picks the TMA star kernel when the request
  * qualifies (3-point star taps, 16-byte aligned rows) and the generic kernel otherwise. */

@@ -409,3 +409,45 @@ def test_x_slab_partition_equals_the_undivided_field():
             padded[..., -1, :] = v[..., hi, :]
         parts.append(prog.residual(padded, boundary=True)[..., 1:-1, :])
     assert torch.equal(torch.cat(parts, dim=-2), want)
+
+
+def test_bf16_input_mode_equals_fp32_kernel_on_the_widened_input():
+    """bf16-input mode (CPPRE_FLAG_IN_BF16; north_star: 'bf16-input mode stated separately'): the
+    fields are staged as bf16 tiles and widened in the kernel, all arithmetic stays fp32.  Stated
+    parity: (1) bit-identical to the fp32 kernel run on the widened input, for every epilogue;
+    (2) within 1e-5 of the fp32 oracle evaluated on the bf16-rounded input."""
+    o, n, c = _programs_2d(), synth.NS, synth.MHD
+    shape = (6, 9, 20, 136)                                            # two column tiles, the second 8 wide
+    rng = np.random.default_rng(4)
+    w = rng.uniform(0.5, 2.0, shape[1:]).astype(np.float32)
+    cases = {
+        "ns_mom": (programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"]),
+                   cuda(synth.fields(71, 3, shape)),
+                   lambda f: O.residual_ns_momentum(f[:, 0], f[:, 1], f[:, 2], n["dx"], n["dy"], n["dt"], n["nu"], O.ops_2d())),
+        "wave": (programs.linear(_wave_op()), cuda(synth.fields(72, 1, shape))[:, 0],
+                 lambda f: O.correlate(f, _wave_op().kernel.numpy())),
+        "mhd_mom": (programs.mhd("momentum", o["D_t"], o["D_x"], o["D_y"], c["gamma"]),
+                    cuda(synth.fields(73, 6, shape, positive=(0, 3))),
+                    lambda f: O.residual_mhd("momentum", *(f[:, j] for j in range(6)), gamma=c["gamma"], ops=O.ops_2d())),
+    }
+    for name, (prog, v, oracle) in cases.items():
+        vb = v.bfloat16()
+        wide = vb.float()
+        r = prog.residual(vb, boundary=True)
+        assert L.last_path() == "tma" and r.dtype == torch.float32, name
+        assert torch.equal(r, prog.residual(wide, boundary=True)), name
+        assert_close_rel(r.cpu().numpy(), oracle(wide.cpu().numpy()), TOL, name + " vs oracle on rounded input")
+        assert torch.equal(prog.joint_scores(vb, cuda(w)), prog.joint_scores(wide, cuda(w))), name
+        assert torch.equal(prog.coverage_counts(vb, 0.7, cuda(w)), prog.coverage_counts(wide, 0.7, cuda(w))), name
+        ref = 0.5 * r
+        assert torch.equal(prog.abs_scores(vb, ref=ref, boundary=True), prog.abs_scores(wide, ref=ref, boundary=True)), name
+    # 1-D + time (batch-rows tiles)
+    m1, cb = _mods()["1d"], synth.BURGERS
+    pb = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2), cb["dx"], cb["dt"], cb["nu"])
+    ub = cuda(synth.fields(74, 1, (37, 12, 264))[:, 0]).bfloat16()
+    assert torch.equal(pb.residual(ub, boundary=True), pb.residual(ub.float(), boundary=True))
+    assert L.last_path() == "tma"
+    # rows that are not 16-byte multiples in bf16 cannot be staged by TMA: refused, never silently widened
+    bad = cuda(synth.fields(75, 1, (2, 5, 8, 132)))[:, 0].bfloat16()
+    with pytest.raises(NotImplementedError):
+        programs.linear(_wave_op()).residual(bad, boundary=True)
