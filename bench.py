@@ -19,7 +19,8 @@ HBM, CUDA-event timed, max over ranks.  `e2e` = the same step through the public
 CUDA-event duration (STORE launch over the calibration half) vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` times the
 reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host
 threads) on a bounded sample.  With --gpus N (torchrun) the batch axis is sharded: every rank owns
-BS samples (weak scaling); the only exchange is the marginal quantile's score all-to-all.
+BS samples (weak scaling); the only exchange is the marginal quantile's candidate-window exchange
+(K3x: peer stores over NVLink from inside the kernels, cp_pre_b200/dist.py).
 """
 from __future__ import annotations
 

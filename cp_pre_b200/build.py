@@ -6,7 +6,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def build(jobs: int = 8, verbose: bool = False) -> str:
+def build(jobs: int = 0, verbose: bool = False) -> str:
+    jobs = jobs or max(4, min(16, os.cpu_count() or 8))
     cmd = ["make", "-C", os.path.join(HERE, "csrc"), f"-j{jobs}"]
     res = subprocess.run(cmd, capture_output=not verbose, text=True)
     if res.returncode != 0:
