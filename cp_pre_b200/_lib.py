@@ -16,13 +16,14 @@ MAX_FIELDS, MAX_SLOTS, MAX_SCALARS, MAX_TAPS = 6, 6, 12, 512
 OK, ERR_BAD_ARG, ERR_UNSUPPORTED, ERR_CUDA = 0, 1, 2, 3
 
 (PROG_LINEAR, PROG_BURGERS, PROG_NS_CONTINUITY, PROG_NS_MOMENTUM, PROG_MHD_CONTINUITY,
- PROG_MHD_MOMENTUM, PROG_MHD_ENERGY, PROG_MHD_INDUCTION, PROG_MHD_GAUSS) = range(9)
+ PROG_MHD_MOMENTUM, PROG_MHD_ENERGY, PROG_MHD_INDUCTION, PROG_MHD_GAUSS, PROG_JOREK_CONTINUITY,
+ PROG_JOREK_TEMPERATURE) = range(11)
 PROGRAM_FIELDS = {PROG_LINEAR: 1, PROG_BURGERS: 1, PROG_NS_CONTINUITY: 2, PROG_NS_MOMENTUM: 3,
                   PROG_MHD_CONTINUITY: 3, PROG_MHD_MOMENTUM: 6, PROG_MHD_ENERGY: 6,
-                  PROG_MHD_INDUCTION: 4, PROG_MHD_GAUSS: 2}
+                  PROG_MHD_INDUCTION: 4, PROG_MHD_GAUSS: 2, PROG_JOREK_CONTINUITY: 4, PROG_JOREK_TEMPERATURE: 4}
 PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS_MOMENTUM: 4,
                  PROG_MHD_CONTINUITY: 3, PROG_MHD_MOMENTUM: 3, PROG_MHD_ENERGY: 3,
-                 PROG_MHD_INDUCTION: 3, PROG_MHD_GAUSS: 3}
+                 PROG_MHD_INDUCTION: 3, PROG_MHD_GAUSS: 3, PROG_JOREK_CONTINUITY: 5, PROG_JOREK_TEMPERATURE: 5}
 
 EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1

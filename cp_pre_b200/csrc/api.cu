@@ -17,8 +17,8 @@ void set_error(const char* fmt, ...) {
 }
 void set_path(const char* name) { t_path = name; }
 
-static const int kFields[CPPRE_PROG_COUNT] = {1, 1, 2, 3, 3, 6, 6, 4, 2};
-static const int kSlots[CPPRE_PROG_COUNT] = {1, 3, 2, 4, 3, 3, 3, 3, 3};
+static const int kFields[CPPRE_PROG_COUNT] = {1, 1, 2, 3, 3, 6, 6, 4, 2, 4, 4};
+static const int kSlots[CPPRE_PROG_COUNT] = {1, 3, 2, 4, 3, 3, 3, 3, 3, 5, 5};
 int program_fields(int kind) { return kFields[kind]; }
 int program_slots(int kind) { return kSlots[kind]; }
 

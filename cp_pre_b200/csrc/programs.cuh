@@ -211,4 +211,46 @@ struct Prog<CPPRE_PROG_MHD_GAUSS> {
     }
 };
 
+// JOREK reduced MHD: fields {rho, phi, T, R}; slots {D_t, D_R, D_Z, D_RR, D_ZZ}
+//                                                    [ref: Marginal/JOREK_residuals_CP.py:211-242]
+// continuity; scalars {D}:
+//   D_t(rho) - R*(D_R(rho)*D_Z(phi) - D_R(phi)*D_Z(rho)) - 2*rho*D_Z(phi) - D*(D_RR(rho) + (1/R)*D_R(rho) + D_ZZ(rho))
+template <>
+struct Prog<CPPRE_PROG_JOREK_CONTINUITY> {
+    static constexpr int NF = 4, NSLOT = 5;
+    template <int I, class C>
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
+        const auto rho = c.template V<0, I>(), R = c.template V<3, I>();
+        const auto dRrho = c.template D<1, 0, I>(), dZrho = c.template D<2, 0, I>();
+        const auto dRphi = c.template D<1, 1, I>(), dZphi = c.template D<2, 1, I>();
+        auto r = c.template D<0, 0, I>();
+        r = pfnma(R, pfnma(dRphi, dZrho, pmul(dRrho, dZphi)), r);
+        r = pfnma(pmul(rho, 2.0f), dZphi, r);
+        const auto lap = padd(padd(c.template D<3, 0, I>(), pmul(pinv(R), dRrho)), c.template D<4, 0, I>());
+        return pfnma(lap, s[0], r);
+    }
+};
+
+// temperature; scalars {K, gamma}:
+//   T*D_t(rho) + rho*D_t(T) - rho*R*(D_R(T)*D_Z(phi) - D_R(phi)*D_Z(T)) + T*R*(D_R(rho)*D_Z(phi) - D_R(phi)*D_Z(rho))
+//   + 2*gamma*rho*T*D_Z(phi) + K*(D_RR(T) + (1/R)*D_R(T) + D_ZZ(T))
+template <>
+struct Prog<CPPRE_PROG_JOREK_TEMPERATURE> {
+    static constexpr int NF = 4, NSLOT = 5;
+    template <int I, class C>
+    __device__ __forceinline__ static auto eval(const C& c, const float* s) {
+        const auto rho = c.template V<0, I>(), T = c.template V<2, I>(), R = c.template V<3, I>();
+        const auto dRrho = c.template D<1, 0, I>(), dZrho = c.template D<2, 0, I>();
+        const auto dRphi = c.template D<1, 1, I>(), dZphi = c.template D<2, 1, I>();
+        const auto dRT = c.template D<1, 2, I>(), dZT = c.template D<2, 2, I>();
+        auto r = pmul(T, c.template D<0, 0, I>());
+        r = pfma(rho, c.template D<0, 2, I>(), r);
+        r = pfnma(pmul(rho, R), pfnma(dRphi, dZT, pmul(dRT, dZphi)), r);
+        r = pfma(pmul(T, R), pfnma(dRphi, dZrho, pmul(dRrho, dZphi)), r);
+        r = pfma(pmul(pmul(rho, 2.0f * s[1]), T), dZphi, r);
+        const auto lap = padd(padd(c.template D<3, 2, I>(), pmul(pinv(R), dRT)), c.template D<4, 2, I>());
+        return pfma(lap, s[0], r);
+    }
+};
+
 }  // namespace cppre

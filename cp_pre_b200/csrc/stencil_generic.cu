@@ -137,6 +137,8 @@ int launch_generic(const Prepared& P, cudaStream_t st) {
         CPPRE_CASE(CPPRE_PROG_MHD_ENERGY)
         CPPRE_CASE(CPPRE_PROG_MHD_INDUCTION)
         CPPRE_CASE(CPPRE_PROG_MHD_GAUSS)
+        CPPRE_CASE(CPPRE_PROG_JOREK_CONTINUITY)
+        CPPRE_CASE(CPPRE_PROG_JOREK_TEMPERATURE)
 #undef CPPRE_CASE
     }
     set_error("unknown program kind %d", P.kind);

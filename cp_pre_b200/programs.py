@@ -54,6 +54,14 @@ class ResidualProgram:
             fs = [v[:, j] for j in self.field_index]
         if self.nd == 2:
             fs = [f.unsqueeze(2) for f in fs]
+        if getattr(self, "coef_field", None) is not None:
+            # a 1-D coefficient grid that the reference broadcasts along the LAST axis (JOREK's R):
+            # appended as a stride-0 view, never materialised
+            cf = ops.to_cuda(self.coef_field, v.dtype).reshape(-1)
+            if fs[0].dim() == 4 and cf.numel() != fs[0].shape[-1]:
+                raise RuntimeError(f"The size of tensor a ({fs[0].shape[-1]}) must match the size of tensor b "
+                                   f"({cf.numel()}) at non-singleton dimension {fs[0].dim() - 1}")
+            fs.append(cf.view(1, 1, 1, -1).expand(fs[0].shape))
         if fs[0].dim() != 4:
             raise RuntimeError(f"{self.name}: expected {'[BS,F,Nt,Nx,Ny]' if self.field_index else '[BS,Nt,...]'} input")
         return fs
@@ -174,6 +182,17 @@ def mhd(equation, D_t, D_x, D_y, gamma=5 / 3):
     """Ideal-MHD residuals on vars = [rho,u,v,p,Bx,By]  [ref: Joint/MHD_Residuals_CP.py:225-278]"""
     kind, idx = _MHD[equation]
     return ResidualProgram(kind, [D_t, D_x, D_y], [_f(gamma)], idx, 3, "mhd_" + equation)
+
+
+def jorek(equation, D_t, D_R, D_Z, D_RR, D_ZZ, R, coef, gamma=5 / 3):
+    """JOREK reduced-MHD residuals on vars = [rho, phi, T]; ``R`` the 1-D major-radius grid (broadcast
+    along the last axis, as the script's ``R * (...)`` does), ``coef`` the diffusivity D
+    (equation="continuity") or conductivity K ("temperature")  [ref: Marginal/JOREK_residuals_CP.py:211-242]."""
+    kind = {"continuity": L.PROG_JOREK_CONTINUITY, "temperature": L.PROG_JOREK_TEMPERATURE}[equation]
+    scalars = [_f(coef)] if equation == "continuity" else [_f(coef), _f(gamma)]
+    prog = ResidualProgram(kind, [D_t, D_R, D_Z, D_RR, D_ZZ], scalars, [0, 1, 2], 3, "jorek_" + equation)
+    prog.coef_field = R
+    return prog
 
 
 # ---------------------------------------------------------------------------------------

@@ -68,7 +68,14 @@ enum {
     CPPRE_PROG_MHD_ENERGY = 6,
     CPPRE_PROG_MHD_INDUCTION = 7,
     CPPRE_PROG_MHD_GAUSS = 8,
-    CPPRE_PROG_COUNT = 9
+    /* JOREK reduced MHD with a radius-dependent coefficient: fields {rho, phi, T, R}, where R is the
+     * major-radius grid as a FIELD (pass the stride-0 broadcast view of the 1-D grid along N0, the
+     * axis the reference's `R * (...)` broadcasts over); slots {D_t, D_R, D_Z, D_RR, D_ZZ};
+     * scalars {D} (continuity) / {K, gamma} (temperature)   Marginal/JOREK_residuals_CP.py:211-242.
+     * Served by the generic kernel (a stride-0 field cannot be a TMA tensor map). */
+    CPPRE_PROG_JOREK_CONTINUITY = 9,
+    CPPRE_PROG_JOREK_TEMPERATURE = 10,
+    CPPRE_PROG_COUNT = 11
 };
 
 /* One input field: a strided fp32 view of logical shape [B, N2, N1, N0].

@@ -402,6 +402,38 @@ def residual_mhd(equation, rho, u, v, p, Bx, By, gamma=5.0 / 3.0, ops=None):
     raise ValueError(equation)
 
 
+def ops_jorek(scale2=5.0 / 3.0):
+    """The operator set of the JOREK script [ref: Marginal/JOREK_residuals_CP.py:188-208]: first-order
+    operators with scale 1 (alpha = beta = 1 after :192); D_RR / D_ZZ are built with ``scale=gamma``
+    AFTER gamma was re-bound to tensor(5/3) at :201, so they carry that factor."""
+    return dict(D_t=build_kernel("2d", "t", 1), D_R=build_kernel("2d", "x", 1), D_Z=build_kernel("2d", "y", 1),
+                D_RR=build_kernel("2d", "x", 2, scale2), D_ZZ=build_kernel("2d", "y", 2, scale2))
+
+
+def residual_jorek(equation, rho, phi, T, R, coef, gamma=5.0 / 3.0, ops=None):
+    """Reduced-MHD continuity / temperature residuals [ref: Marginal/JOREK_residuals_CP.py:211-242].
+    ``R`` is the 1-D major-radius grid: as a 1-D tensor it broadcasts along the LAST axis of the
+    [BS,Nt,Nx,Ny] fields (the script passes x_grid, so this needs Nx == Ny there).  ``coef`` is the
+    diffusivity D (continuity) or conductivity K (temperature)."""
+    o = ops or ops_jorek()
+    rho, phi, T, R = (np.asarray(a, dtype=F32) for a in (rho, phi, T, R))
+    Dt = lambda f: correlate(f, o["D_t"])
+    DR = lambda f: correlate(f, o["D_R"])
+    DZ = lambda f: correlate(f, o["D_Z"])
+    DRR = lambda f: correlate(f, o["D_RR"])
+    DZZ = lambda f: correlate(f, o["D_ZZ"])
+    one, two = F32(1), F32(2)
+    c, g = F32(coef), F32(gamma)
+    if equation == "continuity":
+        return Dt(rho) - R * (DR(rho) * DZ(phi) - DR(phi) * DZ(rho)) - two * rho * DZ(phi) \
+            - c * (DRR(rho) + (one / R) * DR(rho) + DZZ(rho))
+    if equation == "temperature":
+        return T * Dt(rho) + rho * Dt(T) - rho * R * (DR(T) * DZ(phi) - DR(phi) * DZ(T)) \
+            + T * R * (DR(rho) * DZ(phi) - DR(phi) * DZ(rho)) + two * g * rho * T * DZ(phi) \
+            + c * (DRR(T) + (one / R) * DR(T) + DZZ(T))
+    raise ValueError(equation)
+
+
 def interior(res, nd):
     """[ref: Joint/Wave_Residuals_CP.py:184] strip one cell on each of the last nd axes."""
     return res[(Ellipsis,) + (slice(1, -1),) * nd]

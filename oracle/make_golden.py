@@ -373,6 +373,37 @@ def gen_residuals(ref):
     return len(out)
 
 
+def gen_jorek(ref):
+    """JOREK reduced-MHD residuals [ref: Marginal/JOREK_residuals_CP.py:184-242], transcribed and
+    evaluated with the reference's own operators.  As in the script: alpha = beta = 1, but the
+    second-order operators are built AFTER `gamma` was re-bound to tensor(5/3), so their kernels
+    carry that factor; R = x_grid is a 1-D tensor and broadcasts along the LAST axis."""
+    from oracle import synth
+    out = {}
+    C2 = ref.ConvOps_2d.ConvOperator
+    vj = synth.fields(15, 3, (2, 6, 12, 16), positive=(0, 2))
+    R = torch.linspace(1.5, 2.5, 16, dtype=torch.float32)
+    D = torch.tensor(3.4, dtype=torch.float32)
+    K = torch.tensor(2.25 * 1e-7, dtype=torch.float32)
+    gamma = torch.tensor(5 / 3, dtype=torch.float32)
+    D_t = C2(domain='t', order=1, scale=1)
+    D_R = C2(domain='x', order=1, scale=1)
+    D_Z = C2(domain='y', order=1, scale=1)
+    D_RR = C2(domain='x', order=2, scale=gamma)
+    D_ZZ = C2(domain='y', order=2, scale=gamma)
+    vars_ = T(vj)
+    rho, phi, Tt = vars_[:, 0], vars_[:, 1], vars_[:, 2]
+    out["vars"], out["R"] = vj, N(R)
+    out["k|D_RR"], out["k|D_ZZ"] = N(D_RR.kernel), N(D_ZZ.kernel)
+    out["continuity"] = N(D_t(rho) - R*(D_R(rho)*D_Z(phi) - D_R(phi)*D_Z(rho)) - 2*rho*D_Z(phi)
+                          - D*(D_RR(rho) + (1/R)*D_R(rho) + D_ZZ(rho)))
+    out["temperature"] = N(Tt*D_t(rho) + rho*D_t(Tt) - rho*R*(D_R(Tt)*D_Z(phi) - D_R(phi)*D_Z(Tt))
+                           + Tt*R*(D_R(rho)*D_Z(phi) - D_R(phi)*D_Z(rho)) + 2*gamma*rho*Tt*D_Z(phi)
+                           + K * (D_RR(Tt) + (1/R)*D_R(Tt) + D_ZZ(Tt)))
+    np.savez_compressed(os.path.join(OUT, "jorek.npz"), **out)
+    return len(out)
+
+
 def gen_cp(ref):
     """Conformal helpers: the module is absent from the reference; pins are its in-tree
     inline twins, evaluated verbatim with NumPy on seeded residual-like arrays."""
@@ -406,7 +437,10 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     ref = ref_shim.load()
-    for fn in (gen_kernels, gen_conv, gen_spectral, gen_bc, gen_vector, gen_residuals, gen_cp):
+    only = sys.argv[1:]            # e.g. `python -m oracle.make_golden gen_jorek` regenerates one file
+    for fn in (gen_kernels, gen_conv, gen_spectral, gen_bc, gen_vector, gen_residuals, gen_jorek, gen_cp):
+        if only and fn.__name__ not in only:
+            continue
         n = fn(ref)
         print(f"{fn.__name__}: {n} arrays")
 

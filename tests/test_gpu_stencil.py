@@ -451,3 +451,26 @@ def test_bf16_input_mode_equals_fp32_kernel_on_the_widened_input():
     bad = cuda(synth.fields(75, 1, (2, 5, 8, 132)))[:, 0].bfloat16()
     with pytest.raises(NotImplementedError):
         programs.linear(_wave_op()).residual(bad, boundary=True)
+
+
+def test_jorek_coefficient_field_programs_match_reference_golden():
+    """the JOREK reduced-MHD residuals (R-dependent coefficients, second-order D_RR / D_ZZ
+    scaled by the re-bound gamma) against tests/golden/jorek.npz, which the unmodified reference's
+    operators produced; the fused score / coverage epilogues work on them like on every program."""
+    g = load_golden("jorek")
+    C = _mods()["2d"].ConvOperator
+    gam = torch.tensor(5 / 3, dtype=torch.float32)
+    D = [C(domain="t", order=1, scale=1), C(domain="x", order=1, scale=1), C(domain="y", order=1, scale=1),
+         C(domain="x", order=2, scale=gam), C(domain="y", order=2, scale=gam)]
+    np.testing.assert_array_equal(D[3].kernel.cpu().numpy(), g["k|D_RR"])
+    v = cuda(g["vars"])
+    for eq, coef in (("continuity", torch.tensor(3.4)), ("temperature", torch.tensor(2.25 * 1e-7))):
+        p = programs.jorek(eq, *D, torch.from_numpy(g["R"]), coef, gam)
+        r = p.residual(v, boundary=True)
+        assert L.last_path() == "generic"                              # stride-0 coefficient field
+        assert_close_rel(r.cpu().numpy(), g[eq], TOL, eq)
+        assert_close_rel(p.residual(v).cpu().numpy(), g[eq][:, 1:-1, 1:-1, 1:-1], TOL, eq + " interior")
+        s = p.joint_scores(v)
+        assert torch.equal(s, r[:, 1:-1, 1:-1, 1:-1].abs().amax(dim=(1, 2, 3))), eq
+    with pytest.raises(RuntimeError):                                  # R must match the last axis, like torch broadcasting
+        programs.jorek("continuity", *D, torch.ones(5), 3.4).residual(v)

@@ -286,3 +286,16 @@ def test_torch_port_matches_reference():
     assert_close_rel(TP.burgers(torch.from_numpy(g["burgers|u"]), c["dx"], c["dt"], c["nu"], True).numpy(),
                      g["burgers|res"], 1e-6)
     assert_close_rel(TP.mhd_momentum(torch.from_numpy(g["mhd|vars"]), boundary=True).numpy(), g["mhd|momentum"], 1e-6)
+
+
+def test_jorek_residuals_against_reference_golden():
+    """tests/golden/jorek.npz = the JOREK reduced-MHD residuals composed from the UNMODIFIED reference's
+    operators exactly as Marginal/JOREK_residuals_CP.py:203-242 does (oracle/make_golden.py gen_jorek)."""
+    g = load_golden("jorek")
+    o = O.ops_jorek()
+    np.testing.assert_array_equal(o["D_RR"], g["k|D_RR"])          # scale = the re-bound gamma = 5/3
+    np.testing.assert_array_equal(o["D_ZZ"], g["k|D_ZZ"])
+    v = g["vars"]
+    for eq, coef in (("continuity", 3.4), ("temperature", 2.25 * 1e-7)):
+        got = O.residual_jorek(eq, v[:, 0], v[:, 1], v[:, 2], g["R"], coef, ops=o)
+        assert_close_rel(got, g[eq], 1e-5, eq)
