@@ -7,15 +7,18 @@
 //     axis N2 (time for contiguous [BS,Nt,Nx,Ny] data);
 //   * one elected thread stages plane t+k of every field into a ring of shared-memory tiles
 //     with cp.async.bulk.tensor (TMA), completion signalled on an mbarrier.  Tiles carry a
-//     +-1 row and +-4 column halo; out-of-range coordinates are zero-filled by the TMA unit,
-//     which IS the reference's zero "same" padding (F.conv3d padding=k//2) -- no boundary
+//     +-1 row and +-16 byte (4 fp32 / 8 bf16 cells) column halo; out-of-range coordinates are
+//     zero-filled by the TMA unit, which IS the reference's zero "same" padding (F.conv3d padding=k//2) -- no boundary
 //     branches in the kernel;
 //   * the t-1 / t / t+1 centre values live in registers (a 3-deep register pipeline), so a
 //     plane is read from shared memory once for its centre values (128-bit LDS) plus the x+-1
 //     rows (128-bit LDS) and two scalar y+-1 edge values per row;
 //   * derivative coefficients sit in the kernel parameter (constant) bank and are used as
-//     FFMA constant operands; which arms of each slot exist is a template parameter, so zero
-//     taps cost nothing.
+//     broadcast uniform-register operands of FFMA2 (two neighbouring cells per instruction,
+//     programs.cuh); which arms of each slot exist is a template parameter, so zero taps cost
+//     nothing;
+//   * with a weight-only operand set the per-cell weight tile rides the same ring (WTMA);
+//   * CPPRE_TMA_BF16: the field tiles are staged as bf16 and widened on the way into registers.
 // Epilogue (fused, same kernel): minus reference residual, |.|, per-cell weight
 // (1/modulation), then either a 128-bit coalesced store or a per-sample max/sum kept in
 // registers, reduced with redux.sync / shuffles and one atomic per warp -- the Joint score
@@ -611,8 +614,8 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     const int R = BR ? g.B : g.N1;
     for (int f = 0; f < NF; ++f) {
         const FieldView& v = P.fields[f];
-        // Tensor-map dims, innermost first.  3-D problems: (N0, N1, N2, B), box 136 x (TX+2) x 1 x 1.
-        // Batch-rows (1-D+time) problems: (N0, N2, B, 1), box 136 x 1 x TX x 1 -- same smem image,
+        // Tensor-map dims, innermost first.  3-D problems: (N0, N1, N2, B), box kTWP x (TX+2) x 1 x 1
+        // (kTWP = 136 fp32 / 144 bf16 cells).  Batch-rows (1-D+time): (N0, N2, B, 1), box kTWP x 1 x TX x 1 -- same smem image,
         // and the byte strides stay ascending for contiguous data.  A stride on an extent-1
         // axis is never used for addressing but must still be a positive multiple of 16 bytes.
         auto fix = [&](int64_t s, uint64_t extent) -> cuuint64_t {
