@@ -528,7 +528,7 @@ int launch_topk(const float* x, int64_t xs, int64_t n, int64_t cells, const Rank
     return CPPRE_OK;
 }
 
-// Every requested rank within K of one end of the column, K <= 32 and the column longer than
+// Every requested rank within K of one end of the column, K <= 64 and the column longer than
 // the window (otherwise the full sort is as cheap): returns -1 when that does not hold.
 int dispatch_topk(const float* x, int64_t xs, int64_t n, int64_t cells, const RankList& rl, float* out,
                   cudaStream_t st) {
@@ -540,12 +540,15 @@ int dispatch_topk(const float* x, int64_t xs, int64_t n, int64_t cells, const Ra
     const int64_t need_top = n - lo, need_bot = (int64_t)hi + 1;   // window sizes that cover all ranks
     const bool top = need_top <= need_bot;
     const int64_t need = top ? need_top : need_bot;
-    if (need > 32 || n <= 64) return -1;
+    if (need > 64 || n <= 64 || (need > 32 && n <= 256)) return -1;
     if (need <= 8)
         return top ? launch_topk<8, false>(x, xs, n, cells, rl, out, st) : launch_topk<8, true>(x, xs, n, cells, rl, out, st);
     if (need <= 16)
         return top ? launch_topk<16, false>(x, xs, n, cells, rl, out, st) : launch_topk<16, true>(x, xs, n, cells, rl, out, st);
-    return top ? launch_topk<32, false>(x, xs, n, cells, rl, out, st) : launch_topk<32, true>(x, xs, n, cells, rl, out, st);
+    if (need <= 32)
+        return top ? launch_topk<32, false>(x, xs, n, cells, rl, out, st) : launch_topk<32, true>(x, xs, n, cells, rl, out, st);
+    // 33..64 from one end of a long column (e.g. alpha = 0.1 on n = 512): still 3x cheaper than the full sort
+    return top ? launch_topk<64, false>(x, xs, n, cells, rl, out, st) : launch_topk<64, true>(x, xs, n, cells, rl, out, st);
 }
 
 // K3w: window compaction, the second pass of the multi-GPU marginal quantile.  Every rank knows

@@ -96,7 +96,7 @@ def test_select_ranks_every_rank_signed_values_nan_and_strided_rows(n):
 
 @pytest.mark.parametrize("n", [65, 100, 256, 300, 1000, 3000])
 def test_select_ranks_near_one_end_streaming_topk_windows(n):
-    """Ranks within 8 / 16 / 32 of either end take the streaming top-K kernel (K3t): every window
+    """Ranks within 8 / 16 / 32 / 64 of either end take the streaming top-K kernel (K3t): every window
     size, both ends, n not a multiple of the window, +-inf, ties, NaNs of either sign, strided rows."""
     rng = np.random.default_rng(7 * n)
     cells = 150
@@ -112,7 +112,9 @@ def test_select_ranks_near_one_end_streaming_topk_windows(n):
     ref = np.sort(wide[:, 2:2 + cells], axis=0)
     nan_cols = np.isnan(ref).any(axis=0)
     assert nan_cols.sum() == 3
-    for w in (1, 8, 9, 16, 17, 32):
+    for w in (1, 8, 9, 16, 17, 32, 33, 52, 64):
+        if w > n:
+            continue
         for rr in (list(range(n - w, n)), list(range(w)), [n - w], [w - 1], [n - 1, n - w]):
             got = ops.select_ranks(t, rr).cpu().numpy()
             want = ref[rr]
