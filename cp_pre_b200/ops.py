@@ -120,6 +120,16 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     if canonicalise and f0.numel() > 0 and all(_axis_order(f) == _axis_order(f0) for f in fields):
         perm = _axis_order(f0)
     if perm != [0, 1, 2]:
+        # Memory order pays only when its innermost axis can fill the 128-column TMA tiles.  The
+        # t-innermost views FNO surrogates emit (Nt = 50..100 innermost) cannot: measured on B200
+        # (tools/perm_layout.py, NS momentum) 13-19 Gpoints/s in place against 67 Gpoints/s for one
+        # transposing copy + the contiguous kernel (416 Gpoints/s), so those are copied once.
+        n0_mem, n0_log = int(f0.shape[1 + perm[2]]), int(f0.shape[3])
+        if (n0_mem % 4 != 0 or n0_mem < 128) and n0_log % 4 == 0 and n0_log >= n0_mem:
+            fields = [f.contiguous() for f in fields]
+            f0 = fields[0]
+            perm = [0, 1, 2]
+    if perm != [0, 1, 2]:
         tperm = [0] + [1 + d for d in perm]
         fields = [f.permute(tperm) for f in fields]
         kernels = [np.ascontiguousarray(np.transpose(k, perm)) for k in kernels]
