@@ -85,6 +85,7 @@ SIGNATURES = {
     "cppre_radix_hist": (C.c_int, [_P, _I64, C.c_uint32, C.c_uint32, C.c_int32, _P, _P]),
     "cppre_inside_count": (C.c_int, [_P, _I64, _P, _I64, _P, _I64, _I64, _I64, _P, _P]),
     "cppre_inside_count_band": (C.c_int, [_P, _I64, _P, _I64, _P, C.c_float, _I64, _I64, _P, _P]),
+    "cppre_transpose_inner": (C.c_int, [_P, _I64, _I64, _I64, _I64, _P, _P]),
     "cppre_bc_padded_shape": (C.c_int, [C.POINTER(BC), _I64, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
     "cppre_bc_index_map": (C.c_int, [C.POINTER(BC), _I64, _I64, C.POINTER(C.c_int32), C.POINTER(C.c_float),
                                      C.POINTER(C.c_int32), C.POINTER(C.c_float)]),

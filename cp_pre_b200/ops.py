@@ -87,6 +87,22 @@ def _axis_order(t: torch.Tensor):
     return perm
 
 
+def _to_logical_order(f: torch.Tensor, perm) -> torch.Tensor:
+    """A contiguous [B,N2,N1,N0] copy of a permuted view.  The FNO layout -- memory order
+    (B, N1, N0, N2), every sample one contiguous block -- goes through the library's tiled
+    transpose (cppre_transpose_inner); anything else through torch's copy."""
+    B, N2, N1, N0 = (int(v) for v in f.shape)
+    M = N1 * N0
+    if (perm == [1, 2, 0] and f.dtype == torch.float32 and N2 <= 256 and B < 65536 and f.stride(1) == 1
+            and f.stride(3) == N2 and f.stride(2) == N0 * N2 and (B == 1 or f.stride(0) >= M * N2)):
+        out = torch.empty((B, N2, N1, N0), dtype=torch.float32, device=f.device)
+        with torch.cuda.device(f.device):
+            L.check(L.load().cppre_transpose_inner(_ptr(f), int(f.stride(0)) if B > 1 else M * N2, B, M, N2, _ptr(out),
+                                                   _stream(f.device)))
+        return out
+    return f.contiguous()
+
+
 def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.ndarray],
                 pads: Sequence[Sequence[int]], scalars: Sequence[float] = (), *,
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
@@ -126,7 +142,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         # transposing copy + the contiguous kernel (416 Gpoints/s), so those are copied once.
         n0_mem, n0_log = int(f0.shape[1 + perm[2]]), int(f0.shape[3])
         if (n0_mem % 4 != 0 or n0_mem < 128) and n0_log % 4 == 0 and n0_log >= n0_mem:
-            fields = [f.contiguous() for f in fields]
+            fields = [_to_logical_order(f, perm) for f in fields]
             f0 = fields[0]
             perm = [0, 1, 2]
     if perm != [0, 1, 2]:

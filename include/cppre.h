@@ -295,6 +295,14 @@ int cppre_inside_count_band(const float* d_y, int64_t y_row_stride, const float*
                             int64_t centre_row_stride, const float* d_half, float q, int64_t n,
                             int64_t cells, uint32_t* d_inside, void* stream);
 
+/* ---- layout ingestion ------------------------------------------------------------------ */
+/* d_dst[b][n][m] = d_src[b * src_batch_stride + m * N + n]: per sample a [M][N] -> [N][M] transpose
+ * (N <= 256).  Brings the t-innermost tensors FNO surrogates emit ([BS,F,Nx,Ny,Nt], passed on as
+ * pred.permute(0,1,4,2,3), Joint/Wave_Residuals_CP.py:216) to the [Nt][Nx*Ny] order K1 tiles; it
+ * replaces the implicit .contiguous() copy F.conv3d makes of such a view (Utils/ConvOps_2d.py:149). */
+int cppre_transpose_inner(const float* d_src, int64_t src_batch_stride, int64_t batch, int64_t M, int64_t N,
+                          float* d_dst, void* stream);
+
 /* ---- boundary conditions -------------------------------------------------------------- */
 /* Per-side boundary codes, order {left, right, top, bottom}; left/right act on the last axis. */
 enum {

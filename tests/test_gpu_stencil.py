@@ -474,3 +474,20 @@ def test_jorek_coefficient_field_programs_match_reference_golden():
         assert torch.equal(s, r[:, 1:-1, 1:-1, 1:-1].abs().amax(dim=(1, 2, 3))), eq
     with pytest.raises(RuntimeError):                                  # R must match the last axis, like torch broadcasting
         programs.jorek("continuity", *D, torch.ones(5), 3.4).residual(v)
+
+
+def test_fno_layout_views_are_transposed_by_the_library_and_match_the_contiguous_run():
+    """The t-innermost tensors FNO surrogates emit, passed on as pred.permute(0,1,4,2,3):
+    cppre_transpose_inner brings each field to [Nt][Nx*Ny] order (bit-equal to torch's copy, ragged tile
+    edges included) and the residual equals the run on a contiguous copy bit for bit."""
+    o, n = _programs_2d(), synth.NS
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    g = torch.Generator(device="cuda").manual_seed(9)
+    for nx, ny, nt in ((12, 20, 50), (16, 128, 7), (40, 132, 33)):
+        raw = torch.randn((3, 3, nx, ny, nt), device="cuda", generator=g)      # [BS,F,Nx,Ny,Nt]
+        view = raw.permute(0, 1, 4, 2, 3)                                      # [BS,F,Nt,Nx,Ny]
+        for j in range(3):
+            assert torch.equal(ops._to_logical_order(view[:, j], [1, 2, 0]), view[:, j].contiguous())
+        want = prog.residual(view.contiguous(), boundary=True)
+        got = prog.residual(view, boundary=True)
+        assert got.shape == want.shape and torch.equal(got, want), (nx, ny, nt)
