@@ -260,3 +260,12 @@ def test_vector_ops_strict_reference_flag_raises_like_reference():
     a, b = torch.randn(2, 3, 4, 5), torch.randn(2, 3, 4, 5)
     assert torch.equal(V.cross((a, b), (b, b)), a * b + b * b)
     assert V.vectorize(a, b).shape == (2, 2, 3, 4, 5)
+
+
+def test_integration_guide_covers_every_exported_entry_point():
+    """INTEGRATION.md shows (or explains) the reference-side binding of every symbol include/cppre.h declares."""
+    header = open(os.path.join(ROOT, "include", "cppre.h")).read()
+    guide = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    names = set(re.findall(r"\b(cppre_[a-z0-9_]+)\s*\(", header))
+    assert len(names) >= 30
+    assert not [n for n in sorted(names) if n not in guide]

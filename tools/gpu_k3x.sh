@@ -1,5 +1,6 @@
 #!/bin/bash
-TAG=${1:-v8}; O=gpurun_out; mkdir -p $O
+# K3x pass on ONE GPU: parity tests, short bench, the fused-exchange kernels with the ranks emulated (tools/k3x_profile.py), ncu of window / owner.
+TAG=${1:-k3x}; O=gpurun_out; mkdir -p $O
 timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $O/${TAG}_pytest_gpu.log
 tail -4 $O/${TAG}_pytest_gpu.log
 timeout 600 python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench exit $?"
