@@ -44,6 +44,8 @@ WORKLOADS = {
     "ns": (512, 3, 50, 256, 256, "configs[3]: 2D Navier-Stokes momentum PRE + marginal per-cell CP, BS=512 Nt=50 256x256"),
     "wave": (1024, 1, 80, 128, 128, "configs[2]: 2D wave PRE + marginal per-cell CP, BS=1024 Nt=80 128x128"),
 }
+# secondary line (own JSON, single GPU): BASELINE configs[1], 1-D Burgers nonlinear-residual PRE + Joint CP
+JOINT_WORKLOADS = {"burgers": (4096, 100, 1024, "configs[1]: 1D Burgers nonlinear-residual PRE + Joint CP, BS=4096 Nt=100 Nx=1024")}
 
 
 # ----------------------------------------------------------------------------------------
@@ -305,6 +307,77 @@ def run_reference(args):
     }))
 
 
+def run_joint(args):
+    """--workload burgers: BASELINE configs[1] on ONE GPU, data-free Joint CP [ref: Joint/Burgers_Residuals_CP.py:
+    182-260]: K1 STORE (residual of the calibration half) -> K2 (per-cell std = modulation, per-sample max of
+    |res|/modulation) -> joint quantile -> K1 COVER on the validation half with the band qhat*modulation (sets never
+    built).  qhat crosses to the host once per step (the band factor is a by-value argument of the ABI)."""
+    import cp_pre_b200
+    from cp_pre_b200 import _lib, ops, programs
+    from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+    from oracle import synth
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
+    cp_pre_b200.install()
+    import ConvOps_1d as C1
+    bs, nt, nx, desc = JOINT_WORKLOADS[args.workload]
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    c = synth.BURGERS
+    prog = programs.burgers(C1.ConvOperator("t", 1), C1.ConvOperator("x", 1), C1.ConvOperator("x", 2), c["dx"], c["dt"], c["nu"])
+    g = torch.Generator(device=dev).manual_seed(1235)
+    x = torch.linspace(0, 1, nx, device=dev)
+    u = torch.sin(2 * np.pi * (x[None, None, :] + torch.rand(bs, 1, 1, device=dev, generator=g))) \
+        * torch.exp(-torch.linspace(0, 1, nt, device=dev))[None, :, None] + 0.01 * torch.randn(bs, nt, nx, device=dev, generator=g)
+    n_cal = bs // 2
+    k = calibrate_rank(n_cal, n_cal, ALPHA)
+    cells_in = prog.interior_cells(u.shape)
+    k1 = []
+
+    def step(timed=False):
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        mod, inv, scores = programs.joint_calibration(prog, u[:n_cal])
+        if timed:
+            e1.record()
+            k1.append((e0, e1))
+        qhat = float(ops.select_ranks(scores.reshape(-1, 1), [k])[0].item())
+        inside = prog.coverage_counts(u[n_cal:], qhat, mod)
+        return qhat, (inside == cells_in).float().mean()
+
+    W, K = max(args.warmup, 3), args.steps
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(0) as clk:
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(K):
+            qhat, cov = step(timed=True)
+        b.record()
+        torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / K
+    cal_ms = float(np.mean([p.elapsed_time(q) for p, q in k1]))
+    P = bs * nt * nx
+    peak, peak_src = peaks()
+    cal_bytes = (4 + 4 + 4 + 4) * (P // 2)          # K1 STORE read + write, K2 moments read, K2 score read
+    print(json.dumps({
+        "metric": "PRE+joint-CP throughput", "value": P / (ms * 1e-3) / 1e9, "unit": "Gpoints/s", "n_gpus": 1, "steps": K,
+        "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": desc, "fields": 1, "alpha": ALPHA, "per_gpu_batch": bs, "global_batch": bs,
+                   "l2": "inputs (1.7 GB) exceed the 126 MB L2; no flush needed", "qhat": qhat,
+                   "empirical_joint_coverage": float(cov), "target_coverage": 1 - ALPHA},
+        "roofline": {"bound": "hbm", "kernel": "joint calibration of the calibration half: K1 STORE + K2 moments + K2 score",
+                     "achieved": cal_bytes / (cal_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": cal_bytes / (cal_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "bytes_per_point": 16, "kernel_ms": cal_ms, "share_of_step": cal_ms / ms},
+        "cpu_baseline": None, "e2e": None, "gpu_launches": int(_lib.launch_count() - l0), "clocks": clk.summary(),
+    }))
+
+
 # ----------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -312,10 +385,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS) + sorted(JOINT_WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.workload in JOINT_WORKLOADS:
+        return run_joint(args)
     if args.impl == "reference":
         return run_reference(args)
 
