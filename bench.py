@@ -390,6 +390,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.workload in JOINT_WORKLOADS:
+        if args.impl == "reference":
+            if int(os.environ.get("RANK", "0")) == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "the reference arm is defined on the headline workload (ns) only"}))
+            return
         return run_joint(args)
     if args.impl == "reference":
         return run_reference(args)
