@@ -540,6 +540,7 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "star_kernel<NS_MOMENTUM> (K1: TMA stencil + |.| epilogue, STORE)"
                          if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "frac_of_nominal_8000_gbs": achieved / 8000.0,
                          "traffic": (k1_traffic(args.workload) or {}).get("bytes"), "traffic_detail": k1_traffic(args.workload),
                          "peak_source": peak_src, "bytes_per_point": bpp,
                          "kernel_ms": k1_ms, "kernel_gpoints_s": k1_pts / (k1_ms * 1e-3) / 1e9,
