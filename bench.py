@@ -1,30 +1,41 @@
 #!/usr/bin/env python
 """bench.py -- the hot-path benchmark (driver contract in the task statement).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ns|wave|burgers]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload ns|wave|wave-joint|burgers|mhd] [--equation momentum|...] [--global-batch G]
 
-Workload (default): BASELINE.json configs[3] -- 2-D Navier-Stokes vector PRE (momentum residual via
-the live ConvOperator kernels) + marginal per-cell CP, BS=512, Nt=50, 256x256, fp32, the shape the
-north_star target is quoted on.  One "step" = one pass of the hot path over one synthetic batch:
+Default workload: BASELINE.json configs[3] -- 2-D Navier-Stokes vector PRE (momentum residual via the
+live ConvOperator kernels) + marginal per-cell CP, BS=512, Nt=50, 256x256, fp32, the shape the
+north_star target is quoted on and the largest configuration that is quoted per GPU.  One "step" =
+one pass of the hot path over one synthetic batch:
 
-    scores = |R_momentum(u,v,p)|                         K1 fused TMA stencil + |.| epilogue, STORE  (calibration half)
-    qhat   = per-cell ceil((n+1)(1-a))/n quantile        K3 order statistics                         (calibration half)
-    cov    = mean(-qhat <= R <= qhat) on the other half  K1 again, COVER epilogue: residuals and sets
-                                                         of the validation half are never written    (validation half)
+  marginal (ns, wave)                                    [ref: Marginal/NS_Residuals_CP.py:327-337]
+    scores = |R(u)|                      K1 fused TMA stencil + |.| epilogue, STORE  (calibration half)
+    qhat   = per-cell conformal quantile K3 order statistics                         (calibration half)
+    cov    = mean(-qhat <= R <= qhat)    K1 again, COVER epilogue: residuals and sets of the
+                                         validation half are never written            (validation half)
+  joint (burgers = configs[1], wave-joint = configs[2], mhd = configs[4])
+                                                         [ref: Joint/MHD_Residuals_CP.py:405-420]
+    res    = R(u)                        K1 STORE                                     (calibration half)
+    mod    = std over samples per cell   K2 (fp64 moments; merged over NCCL when the batch is sharded)
+    score  = max_cells |res| / mod       K2
+    qhat   = conformal quantile of the scores over ALL ranks: K3d radix select, state on the device,
+             257-counter histograms all-reduced over NCCL between passes -- never crosses to the host
+    cov    = mean(all cells |R| <= qhat*mod)   K1 COVER, qhat read from the device scalar
 
-`value` (Gpoints/s) = grid points of the logical [BS,Nt,Nx,Ny] field per second, inputs resident in
+`value` (Gpoints/s) = grid points of the logical [BS,Nt,Nx(,Ny)] field per second, inputs resident in
 HBM, CUDA-event timed, max over ranks.  `e2e` = the same step through the public API with HOST
-(pinned) inputs streamed to the device in batch chunks and qhat + coverage read back.
-`roofline` is for the dominant kernel (K1): algorithmic bytes (4F+4 = 16 B/point) / its own
-CUDA-event duration (STORE launch over the calibration half) vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` times the
-reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host
-threads) on a bounded sample.  With --gpus N (torchrun) the batch axis is sharded: every rank owns
-BS samples (weak scaling); the only exchange is the marginal quantile's candidate-window exchange
-(K3x: peer stores over NVLink from inside the kernels, cp_pre_b200/dist.py).
+(pinned) inputs streamed to the device in batch chunks and qhat + coverage read back.  `roofline` is
+for the dominant kernel (K1 STORE): algorithmic bytes (4F+4 per point) / its own CUDA-event duration
+vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` / `--impl reference` time the
+reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host threads)
+on a bounded sample of the same workload: the full batch on a slab of time planes -- measured, not
+extrapolated.  With --gpus N (torchrun) the batch axis is sharded (cp_pre_b200/dist.py).
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -39,13 +50,21 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ALPHA = 0.1
+MHD_EQUATIONS = {"continuity": 3, "momentum": 6, "energy": 6, "induction": 4, "gauss": 2}   # fields read
 WORKLOADS = {
-    # name: (BS, F, Nt, Nx, Ny, description)
-    "ns": (512, 3, 50, 256, 256, "configs[3]: 2D Navier-Stokes momentum PRE + marginal per-cell CP, BS=512 Nt=50 256x256"),
-    "wave": (1024, 1, 80, 128, 128, "configs[2]: 2D wave PRE + marginal per-cell CP, BS=1024 Nt=80 128x128"),
+    # kind, per-GPU batch (None: from the global batch), fields in `vars`, grid, description
+    "ns": dict(kind="marginal", bs=512, nf=3, grid=(50, 256, 256),
+               desc="configs[3]: 2D Navier-Stokes momentum PRE + marginal per-cell CP, BS=512 Nt=50 256x256"),
+    "wave": dict(kind="marginal", bs=1024, nf=1, grid=(80, 128, 128),
+                 desc="configs[2] shape: 2D wave PRE + marginal per-cell CP, BS=1024 Nt=80 128x128"),
+    "wave-joint": dict(kind="joint", bs=1024, nf=1, grid=(80, 128, 128),
+                       desc="configs[2]: 2D wave PRE (D_tt - c^2 Laplacian) + Joint CP, BS=1024 Nt=80 128x128"),
+    "burgers": dict(kind="joint", bs=4096, nf=1, grid=(100, 1024),
+                    desc="configs[1]: 1D Burgers nonlinear-residual PRE + Joint CP, BS=4096 Nt=100 Nx=1024"),
+    "mhd": dict(kind="joint", bs=None, nf=6, grid=(100, 256, 256),
+                desc="configs[4]: 2D MHD multi-field vector PRE + Joint CP, BS=2048 Nt=100 256x256 sharded over 8 GPUs"),
 }
-# secondary line (own JSON, single GPU): BASELINE configs[1], 1-D Burgers nonlinear-residual PRE + Joint CP
-JOINT_WORKLOADS = {"burgers": (4096, 100, 1024, "configs[1]: 1D Burgers nonlinear-residual PRE + Joint CP, BS=4096 Nt=100 Nx=1024")}
+MHD_GLOBAL, MHD_PER_GPU_MAX = 2048, 512      # 512 samples = 80.5 GB of fp32 inputs per GPU
 
 
 # ----------------------------------------------------------------------------------------
@@ -56,18 +75,27 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def k1_traffic(workload):
+def kernel_source_sha():
+    """Fingerprint of the K1 sources: an ncu traffic capture only stands for the kernel it was taken from."""
+    h = hashlib.sha256()
+    for f in ("stencil_tma_impl.cuh", "programs.cuh", "common.cuh"):
+        h.update(open(os.path.join(ROOT, "cp_pre_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def k1_traffic(workload, equation=None):
     """DRAM bytes per K1 STORE launch from the committed `ncu --set full` capture (dram__bytes_read.sum +
-    dram__bytes_write.sum), or None when no capture of this workload is committed."""
-    p = os.path.join(ROOT, "profiles", "r01_k1_traffic.json")
+    dram__bytes_write.sum) of THIS workload and THIS kernel source; None when there is no such capture or
+    the kernel has changed since (a stale capture is never reported)."""
+    name = f"k1_traffic_{workload}" + (f"_{equation}" if workload == "mhd" else "") + ".json"
     try:
-        d = json.load(open(p))
-        if d.get("workload") == workload:
-            return {"bytes": d["dram_bytes_read"] + d["dram_bytes_write"], "read": d["dram_bytes_read"],
-                    "write": d["dram_bytes_write"], "algorithmic": d["algorithmic_bytes"], "source": d["source"]}
+        d = json.load(open(os.path.join(ROOT, "profiles", name)))
+        if d.get("kernel_source_sha") != kernel_source_sha():
+            return None
+        return {"bytes": d["dram_bytes_read"] + d["dram_bytes_write"], "read": d["dram_bytes_read"],
+                "write": d["dram_bytes_write"], "algorithmic": d["algorithmic_bytes"], "source": d["source"]}
     except (OSError, ValueError, KeyError):
-        pass
-    return None
+        return None
 
 
 class ClockSampler:
@@ -109,66 +137,118 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------
-def synth_fields_gpu(bs, nf, nt, nx, ny, device, seed, out=None, chunk=16):
-    """oracle/synth.py's smooth-plus-noise fields evaluated on the device (same formula, torch
-    RNG): random-init surrogate outputs, no downloaded data."""
+# workload geometry, synthetic inputs, programs
+# ----------------------------------------------------------------------------------------
+def geometry(args, world):
+    """(per-GPU batch, global batch, scaling label).  Every workload but mhd keeps the per-GPU batch of
+    its config (weak scaling: the calibration set grows with N).  mhd is the sharded config: global batch
+    2048 split over the ranks; below 4 GPUs that does not fit (512 samples = 80.5 GB per GPU), so the
+    global batch is 512 x N there.  --global-batch fixes it (strong-scaling runs)."""
+    w = WORKLOADS[args.workload]
+    if args.workload != "mhd":
+        if args.global_batch:
+            assert args.global_batch % world == 0
+            return args.global_batch // world, args.global_batch, "strong"
+        return w["bs"], w["bs"] * world, "weak"
+    G = args.global_batch or min(MHD_GLOBAL, MHD_PER_GPU_MAX * world)
+    assert G % (2 * world) == 0, "the global batch must split into equal calibration / validation halves per rank"
+    assert G // world <= MHD_PER_GPU_MAX, f"{G // world} samples per GPU do not fit (max {MHD_PER_GPU_MAX})"
+    return G // world, G, ("strong" if (args.global_batch or G == MHD_GLOBAL) else "weak")
+
+
+def config_dict(args, world):
+    """Identical for both arms (`--impl ours` / `--impl reference`) of the same command line."""
+    w = WORKLOADS[args.workload]
+    per, G, _ = geometry(args, world)
+    nf = MHD_EQUATIONS[args.equation] if args.workload == "mhd" else w["nf"]
+    gb = per * nf * int(np.prod(w["grid"])) * 4 / 1e9
+    c = {"workload": w["desc"], "cp": w["kind"], "fields": nf, "alpha": ALPHA, "per_gpu_batch": per, "global_batch": G,
+         "sharding": "batch axis", "split": "first half of every rank's shard = calibration, second half = validation",
+         "l2": f"inputs ({gb:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed"}
+    if args.workload == "mhd":
+        c["equation"] = args.equation
+    return c
+
+
+def synth_fields_gpu(bs, nf, grid, device, seed, positive=(), chunk=16):
+    """oracle/synth.py's smooth-plus-noise fields evaluated on the device (same formula, torch RNG):
+    random-init surrogate outputs, no downloaded data.  [bs, nf, *grid]; fields listed in `positive`
+    are 1 + 0.1 u / 4 (MHD density and pressure: divisors, strictly positive)."""
     g = torch.Generator(device=device).manual_seed(seed)
-    if out is None:
-        out = torch.empty((bs, nf, nt, nx, ny), dtype=torch.float32, device=device)
-    t = torch.linspace(0, 1, nt, device=device).view(1, 1, nt, 1, 1)
-    x = (torch.arange(nx, device=device) / nx).view(1, 1, 1, nx, 1)
-    y = (torch.arange(ny, device=device) / ny).view(1, 1, 1, 1, ny)
+    nd = len(grid)
+    out = torch.empty((bs, nf) + tuple(grid), dtype=torch.float32, device=device)
+    view = lambda v, ax: v.view((1, 1) + tuple(-1 if i == ax else 1 for i in range(nd)))
+    t = view(torch.linspace(0, 1, grid[0], device=device), 0)
+    x = view(torch.arange(grid[1], device=device) / grid[1], 1)
+    y = view(torch.arange(grid[2], device=device) / grid[2], 2) if nd == 3 else None
+    chunk = max(1, min(chunk, (1 << 28) // max(1, nf * int(np.prod(grid)))))
     for b0 in range(0, bs, chunk):
         b1 = min(bs, b0 + chunk)
-        acc = 0.01 * torch.randn((b1 - b0, nf, nt, nx, ny), device=device, generator=g)
+        acc = 0.01 * torch.randn((b1 - b0, nf) + tuple(grid), device=device, generator=g)
         for m in range(1, 5):
-            a, phi, psi, lam = (torch.rand((b1 - b0, nf, 1, 1, 1), device=device, generator=g) for _ in range(4))
-            acc += (0.5 + 0.5 * a) * torch.sin(2 * np.pi * (m * x + phi)) * torch.cos(2 * np.pi * (m * y + psi)) \
-                * torch.exp(-(0.1 + 0.9 * lam) * t)
+            a, phi, psi, lam = (torch.rand((b1 - b0, nf) + (1,) * nd, device=device, generator=g) for _ in range(4))
+            term = (0.5 + 0.5 * a) * torch.sin(2 * np.pi * (m * x + phi)) * torch.exp(-(0.1 + 0.9 * lam) * t)
+            if y is not None:
+                term = term * torch.cos(2 * np.pi * (m * y + psi))
+            acc += term
+        for j in positive:
+            acc[:, j] = 1.0 + 0.025 * acc[:, j]
         out[b0:b1] = acc
     return out
 
 
-def make_program(workload):
+def make_inputs(workload, bs, device, seed):
+    w = WORKLOADS[workload]
+    v = synth_fields_gpu(bs, w["nf"], w["grid"], device, seed, positive=(0, 3) if workload == "mhd" else ())
+    return v if w["nf"] > 1 else v[:, 0]       # single-field programs take [BS, Nt, Nx(, Ny)]
+
+
+def make_program(workload, equation="momentum"):
     import cp_pre_b200
     from cp_pre_b200 import programs
-    from oracle import synth
+    from oracle import synth                   # physical constants of the configs only
     cp_pre_b200.install()
     import Utils.ConvOps_2d as C2
     if workload == "ns":
         c = synth.NS
         D = [C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1), C2.ConvOperator(("x", "y"), 2)]
         return programs.ns_momentum(*D, c["dx"], c["dy"], c["dt"], c["nu"])
+    if workload == "mhd":
+        return programs.mhd(equation, C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1),
+                            synth.MHD["gamma"])
+    if workload == "burgers":
+        import ConvOps_1d as C1
+        c = synth.BURGERS
+        return programs.burgers(C1.ConvOperator("t", 1), C1.ConvOperator("x", 1), C1.ConvOperator("x", 2),
+                                c["dx"], c["dt"], c["nu"])
     W = C2.ConvOperator()
     W.kernel = C2.ConvOperator("t", 2).kernel - synth.WAVE["c2"] * C2.ConvOperator(("x", "y"), 2).kernel
     return programs.linear(W)
 
 
-class Step:
-    """One pass of the hot path over a device-resident batch (per rank):
-        K1 STORE  |R(cal half)|            -> scores [n_cal, Nt, Nx, Ny]
-        K3        per-cell quantile        -> qhat   [Nt, Nx, Ny]
-        K1 COVER  -qhat <= R(val half) <= qhat counted per sample (interior cells); the validation
-                  residuals and the prediction sets are never written."""
+# ----------------------------------------------------------------------------------------
+# the step (device-resident inputs)
+# ----------------------------------------------------------------------------------------
+class StepBase:
+    """Shared plumbing: inputs, calibration / validation split, CUDA-event brackets around K1."""
 
-    def __init__(self, workload, device, world, seed):
+    def __init__(self, args, device, world, rank):
         from cp_pre_b200 import ops
-        from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
         self.ops = ops
-        self.bs, self.nf, self.nt, self.nx, self.ny, _ = WORKLOADS[workload]
-        self.workload, self.device, self.world = workload, device, world
-        self.prog = make_program(workload)
-        self.vars = synth_fields_gpu(self.bs, self.nf, self.nt, self.nx, self.ny, device, seed)
+        self.args, self.device, self.world, self.rank = args, device, world, rank
+        w = WORKLOADS[args.workload]
+        self.bs, _, _ = geometry(args, world)
+        self.grid = tuple(w["grid"])
+        self.prog = make_program(args.workload, args.equation)
+        self.nf = len(self.prog.field_index) if self.prog.field_index else 1
+        self.vars = make_inputs(args.workload, self.bs, device, seed=1234 + rank)
         self.n_cal = self.bs // 2
-        self.rank_k = calibrate_rank(self.n_cal * world, self.n_cal * world, ALPHA)
-        self.scores = torch.empty((self.n_cal, self.nt, self.nx, self.ny), dtype=torch.float32, device=device)
-        self.points = self.bs * self.nt * self.nx * self.ny
-        self.interior_cells = (self.nt - 2) * (self.nx - 2) * (self.ny - 2)
+        self.cells = int(np.prod(self.grid))
+        self.points = self.bs * self.cells
+        self.interior_cells = self.prog.interior_cells(self.vars.shape)
+        self.store = torch.empty((self.n_cal,) + self.grid, dtype=torch.float32, device=device)
         self.k1_events, self.k1c_events = [], []
-        self.defer = world > 1     # overflow counters of the fused quantile are settled after the timed loop
-
-    def _input(self, v):
-        return v if self.workload == "ns" else v[:, 0]
+        self.group = None
 
     def _timed(self, fn, sink, timed):
         if not timed:
@@ -180,201 +260,308 @@ class Step:
         sink.append((e0, e1))
         return out
 
-    def pre_cal(self, v, out, timed=False):
-        return self._timed(lambda: self.prog.abs_scores(self._input(v), boundary=True, out=out), self.k1_events, timed)
+    def run(self, timed=False):
+        self.pre_cal(self.vars[: self.n_cal], self.store, timed)
+        cal = self.calibrate()
+        inside = self.cover_val(self.vars[self.n_cal:], cal, timed)
+        return cal, self.tally(inside)
 
-    def quantile(self):
+
+class MarginalStep(StepBase):
+    """K1 STORE |R(cal half)| -> scores; K3 per-cell quantile -> qhat [Nt,Nx,Ny]; K1 COVER on the
+    validation half with the band +-qhat (interior cells): residuals and sets never written."""
+    metric = "PRE+marginal-CP throughput"
+    store_flags_abs = True
+
+    def __init__(self, *a):
+        super().__init__(*a)
+        from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+        n = self.n_cal * self.world
+        self.rank_k = calibrate_rank(n, n, ALPHA)
+        self.defer = self.world > 1    # overflow counters of the fused quantile are settled after the timed loop
+
+    def pre_cal(self, v, out, timed=False):
+        return self._timed(lambda: self.prog.abs_scores(v, boundary=True, out=out), self.k1_events, timed)
+
+    def calibrate(self):
         from cp_pre_b200 import dist as D
         if self.world > 1:
-            return D.marginal_quantiles(self.scores, [self.rank_k], defer=self.defer)[0]
-        return self.ops.select_ranks(self.scores, [self.rank_k])[0]
+            return D.marginal_quantiles(self.store, [self.rank_k], defer=self.defer)[0]
+        return self.ops.select_ranks(self.store, [self.rank_k])[0]
 
     def cover_val(self, v, qhat, timed=False):
-        return self._timed(lambda: self.prog.coverage_counts(self._input(v), 1.0, half=qhat), self.k1c_events, timed)
+        return self._timed(lambda: self.prog.coverage_counts(v, 1.0, half=qhat), self.k1c_events, timed)
 
-    def run(self, timed=False):
-        self.pre_cal(self.vars[: self.n_cal], self.scores, timed)
-        qhat = self.quantile()
-        inside = self.cover_val(self.vars[self.n_cal:], qhat, timed)
-        return qhat, inside.to(torch.int64).sum()
+    def tally(self, inside):
+        return inside.to(torch.int64).sum()           # cells inside, this rank
+
+    def coverage_denominator(self):
+        return (self.bs - self.n_cal) * self.interior_cells
+
+    def spot_check(self, qhat):
+        """4096 random cells of the timed qhat against an independent path: torch.kthvalue (a library sort,
+        not one of this repo's kernels) on the gathered score columns of all ranks."""
+        gsel = torch.Generator(device="cpu").manual_seed(7)
+        ids = torch.randint(0, self.cells, (4096,), generator=gsel).to(self.device)
+        cols = self.store.reshape(self.n_cal, -1)[:, ids].contiguous()
+        if self.world > 1:
+            parts = [torch.empty_like(cols) for _ in range(self.world)]
+            torch.distributed.all_gather(parts, cols)
+            cols = torch.cat(parts)
+        want = torch.kthvalue(cols, self.rank_k + 1, dim=0).values
+        return bool(torch.equal(want, qhat.reshape(-1)[ids]))
+
+    def stage_bytes(self):
+        F = self.nf
+        return {"K1 STORE": 4 * F + 4, "K3 re-read": 4, "K1 COVER": 4 * F}
+
+
+class JointStep(StepBase):
+    """K1 STORE R(cal half) -> K2 modulation (global over ranks) -> K2 scores -> K3d quantile on the device
+    (histograms all-reduced) -> K1 COVER on the validation half with the band qhat*modulation."""
+    metric = "PRE+joint-CP throughput"
+
+    def __init__(self, *a):
+        super().__init__(*a)
+        from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+        n = self.n_cal * self.world
+        self.rank_k = calibrate_rank(n, n, ALPHA)
+        self.eps = 1e-6 if self.args.workload == "mhd" else 0.0      # Joint/MHD_Residuals_CP.py:350
+        self.cal_events = []
+
+    def pre_cal(self, v, out, timed=False):
+        # signed residual of the calibration samples, stored once (full field, shell included)
+        return self._timed(lambda: self.prog._run(v, out=self.prog._unsq(out)), self.k1_events, timed)
+
+    def calibrate(self):
+        from cp_pre_b200 import dist as D
+        if self.world > 1:
+            mod, _ = D.global_cell_std(self.store, None, self.eps)
+        else:
+            mod, _ = self.ops.cell_modulation(self.store, None, self.eps)
+        masked = torch.full_like(mod, float("inf"))                  # the max runs over the interior cells
+        self.prog._crop(masked).copy_(self.prog._crop(mod))
+        scores = self.ops.joint_score(self.store, None, masked)
+        qhat = D.joint_quantile_device(scores, self.rank_k)          # one-element device tensor
+        return qhat, mod
+
+    def cover_val(self, v, cal, timed=False):
+        qhat, mod = cal
+        return self._timed(lambda: self.prog.coverage_counts(v, qhat, mod), self.k1c_events, timed)
+
+    def tally(self, inside):
+        return (inside == self.interior_cells).to(torch.int64).sum()   # samples entirely inside, this rank
+
+    def coverage_denominator(self):
+        return self.bs - self.n_cal
+
+    def spot_check(self, cal):
+        """The device-side radix select against torch.kthvalue on the gathered scores, and the merged
+        modulation against a direct fp64 std of 4096 gathered columns."""
+        qhat, mod = cal
+        masked = torch.full_like(mod, float("inf"))
+        self.prog._crop(masked).copy_(self.prog._crop(mod))
+        scores = self.ops.joint_score(self.store, None, masked)
+        gsel = torch.Generator(device="cpu").manual_seed(7)
+        ids = torch.randint(0, self.cells, (4096,), generator=gsel).to(self.device)
+        cols = self.store.reshape(self.n_cal, -1)[:, ids].contiguous()
+        if self.world > 1:
+            parts = [torch.empty_like(scores) for _ in range(self.world)]
+            torch.distributed.all_gather(parts, scores)
+            scores = torch.cat(parts)
+            cparts = [torch.empty_like(cols) for _ in range(self.world)]
+            torch.distributed.all_gather(cparts, cols)
+            cols = torch.cat(cparts)
+        want_q = torch.kthvalue(scores, self.rank_k + 1).values
+        want_mod = (cols.double().std(dim=0, unbiased=False).float() + self.eps)
+        rel = float(((mod.reshape(-1)[ids] - want_mod).abs() / want_mod).max())
+        return bool(torch.equal(want_q.reshape(1), qhat)) and rel <= 1e-6
+
+    def stage_bytes(self):
+        F = self.nf
+        return {"K1 STORE": 4 * F + 4, "K2 moments": 4, "K2 scores": 4, "K1 COVER": 4 * F}
 
 
 class E2E:
     """The same step through the public API with HOST inputs: pinned host batch -> chunked,
     double-buffered H2D on a copy stream overlapped with K1 on the compute stream -> calibration
-    -> qhat + coverage read back to the host."""
+    -> qhat (+ modulation) + coverage read back to the host."""
 
-    def __init__(self, step: Step, chunk=32):
-        self.s, self.chunk = step, chunk
-        s = step
-        self.host = torch.empty(s.vars.shape, dtype=torch.float32, pin_memory=True)
-        self.host.copy_(s.vars)                            # synthetic host batch (one-off, untimed)
-        self.stage = [torch.empty((chunk,) + tuple(s.vars.shape[1:]), dtype=torch.float32, device=s.device)
+    def __init__(self, step: StepBase, chunk_bytes=1280 << 20):
+        s = self.s = step
+        per_sample = s.vars[0].numel() * 4
+        # ~1.25 GB per staged chunk (NS: 32 samples), at least four chunks per half so copies and kernels
+        # overlap, and a divisor of the calibration half so the calibration point falls on a chunk boundary
+        want = max(1, min(chunk_bytes // per_sample, s.n_cal // 4))
+        self.chunk = max(d for d in range(1, want + 1) if s.n_cal % d == 0)
+        free = 0
+        try:
+            for line in open("/proc/meminfo"):
+                if line.startswith("MemAvailable"):
+                    free = int(line.split()[1]) * 1024
+        except OSError:
+            pass
+        need = s.vars.numel() * 4
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(s.world)))
+        # the whole host batch when the box has room for every rank's copy, else a window that is re-streamed
+        full_ok = need <= (48 << 30) and (free == 0 or need * local_world < 0.6 * free)
+        self.rows = s.bs if full_ok else max(self.chunk, min(s.bs, (24 << 30) // per_sample) // self.chunk * self.chunk)
+        self.host = torch.empty((self.rows,) + tuple(s.vars.shape[1:]), dtype=torch.float32, pin_memory=True)
+        self.host.copy_(s.vars[: self.rows])                   # synthetic host batch (one-off, untimed)
+        self.stage = [torch.empty((self.chunk,) + tuple(s.vars.shape[1:]), dtype=torch.float32, device=s.device)
                       for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=s.device)
-        self.q_host = torch.empty((s.nt, s.nx, s.ny), dtype=torch.float32, pin_memory=True)
-        self.h2d_bytes = self.host.numel() * 4
+        self.q_host = torch.empty(s.grid, dtype=torch.float32, pin_memory=True)
+        self.h2d_bytes = need
         self.d2h_bytes = self.q_host.numel() * 4 + 8
+        self.copy_events = []
 
-    def run(self):
+    def describe(self):
+        s = self.s
+        buf = "whole host batch pinned" if self.rows == s.bs else \
+            f"pinned window of {self.rows} of {s.bs} samples re-streamed (host RAM bound); every byte still crosses PCIe each step"
+        return (f"pinned host batch -> {self.chunk}-sample double-buffered H2D (one cudaMemcpyAsync per chunk) overlapped "
+                f"with K1 -> calibration -> qhat+coverage D2H; {buf}")
+
+    def run(self, timed=False):
         s = self.s
         main = torch.cuda.current_stream(s.device)
         ready = [torch.cuda.Event() for _ in range(2)]
         freed = [torch.cuda.Event() for _ in range(2)]
-        qhat, inside = None, []
+        cal, inside = None, []
         for i, b0 in enumerate(range(0, s.bs, self.chunk)):
             b1 = min(s.bs, b0 + self.chunk)
             buf = self.stage[i % 2]
+            h0 = b0 % self.rows
             with torch.cuda.stream(self.copy_stream):
                 if i >= 2:
                     self.copy_stream.wait_event(freed[i % 2])
-                buf[: b1 - b0].copy_(self.host[b0:b1], non_blocking=True)
+                if timed:
+                    c0 = torch.cuda.Event(enable_timing=True)
+                    c0.record(self.copy_stream)
+                buf[: b1 - b0].copy_(self.host[h0:h0 + b1 - b0], non_blocking=True)
+                if timed:
+                    c1 = torch.cuda.Event(enable_timing=True)
+                    c1.record(self.copy_stream)
+                    self.copy_events.append((c0, c1, (b1 - b0) * s.vars[0].numel() * 4))
                 ready[i % 2].record(self.copy_stream)
-            if b0 == s.n_cal:                          # calibration half is on the device: qhat
-                qhat = s.quantile()
+            if b0 == s.n_cal:                          # calibration half is on the device
+                cal = s.calibrate()
             main.wait_event(ready[i % 2])
             if b0 < s.n_cal:
-                s.pre_cal(buf[: b1 - b0], s.scores[b0:b1])
+                s.pre_cal(buf[: b1 - b0], s.store[b0:b1])
             else:
-                inside.append(s.cover_val(buf[: b1 - b0], qhat))
+                inside.append(s.cover_val(buf[: b1 - b0], cal))
             freed[i % 2].record(main)
-        self.q_host.copy_(qhat, non_blocking=True)
-        total = torch.cat(inside).to(torch.int64).sum()
-        cov = int(total.item()) / float((s.bs - s.n_cal) * s.interior_cells)    # D2H + sync
-        return cov
+        q = cal if isinstance(cal, torch.Tensor) else cal[1]       # marginal: qhat[cells]; joint: modulation[cells]
+        self.q_host.copy_(q.reshape(s.grid), non_blocking=True)
+        total = s.tally(torch.cat(inside))
+        return int(total.item()) / float(s.coverage_denominator())    # D2H + sync
+
+    def h2d_gbs(self):
+        """Per-rank H2D rate while a copy is in flight (sum of bytes / sum of copy durations)."""
+        if not self.copy_events:
+            return None
+        ms = sum(a.elapsed_time(b) for a, b, _ in self.copy_events)
+        return sum(n for _, _, n in self.copy_events) / (ms * 1e-3) / 1e9 if ms > 0 else None
 
 
 # ----------------------------------------------------------------------------------------
-def cpu_reference_sample(workload, threads=None, bs_pre=8, nt_cp=6):
-    """The reference's CPU path on a bounded sample of the same workload; returns
-    (Gpoints/s normalised to the whole step, description, seconds)."""
+# the reference's CPU path (oracle/torch_port.py) -- cpu_baseline leg and --impl reference
+# ----------------------------------------------------------------------------------------
+def cpu_pipeline(args, bs, nt, seed=99, threads=None, chunk=32):
+    """One UN-EXTRAPOLATED pass of the reference's CPU path over a [bs, F, nt, Nx(, Ny)] batch: PRE on every
+    sample (F.conv3d + elementwise algebra, torch intra-op threads; evaluated in batch chunks only to bound
+    host RAM), then the conformal step on the calibration half and coverage on the validation half.
+    Returns (points processed, seconds, per-stage seconds)."""
     from oracle import cpu_oracle as O
     from oracle import synth, torch_port as TP
-    bs, nf, nt, nx, ny, _ = WORKLOADS[workload]
-    threads = threads or os.cpu_count()
-    torch.set_num_threads(threads)
-    v = torch.from_numpy(synth.fields(99, nf, (bs_pre, nt, nx, ny)))
-    c = synth.NS
-    t0 = time.perf_counter()
-    if workload == "ns":
-        res = TP.ns_momentum(v, c["dx"], c["dy"], c["dt"], c["nu"])
-    else:
-        res = TP.wave(v[:, 0], synth.WAVE["c2"])
-    t_pre = time.perf_counter() - t0
-    pts_pre = bs_pre * nt * nx * ny
-    # calibration / coverage on [n_cal, nt_cp, Nx-2, Ny-2] residual-like scores
+    w = WORKLOADS[args.workload]
+    torch.set_num_threads(threads or os.cpu_count())
+    grid = (nt,) + tuple(w["grid"][1:])
     n_cal = bs // 2
-    rng = np.random.default_rng(0)
-    cal = torch.from_numpy((res.numpy()[:1, :nt_cp].std() * rng.standard_normal((n_cal, nt_cp, nx - 2, ny - 2))).astype(np.float32))
-    val = cal[: n_cal // 2]
+    pos = (0, 3) if args.workload == "mhd" else ()
+    ops2 = TP.Ops2D() if len(grid) == 3 else None
+    t_pre = 0.0
+    res = []
+    for b0 in range(0, bs, chunk):
+        b1 = min(bs, b0 + chunk)
+        v = torch.from_numpy(synth.fields(seed + b0, w["nf"], (b1 - b0,) + grid, positive=pos))   # untimed: data
+        t0 = time.perf_counter()
+        if args.workload == "ns":
+            c = synth.NS
+            r = TP.ns_momentum(v, c["dx"], c["dy"], c["dt"], c["nu"], ops2)
+        elif args.workload == "mhd":
+            r = TP.mhd(args.equation, v, synth.MHD["gamma"], ops2)
+        elif args.workload == "burgers":
+            c = synth.BURGERS
+            r = TP.burgers(v[:, 0], c["dx"], c["dt"], c["nu"])
+        else:
+            r = TP.wave(v[:, 0], synth.WAVE["c2"])
+        res.append(r.contiguous())
+        t_pre += time.perf_counter() - t0
     t0 = time.perf_counter()
-    scores = np.abs(cal.numpy())
-    qhat = O.calibrate(scores, len(scores), ALPHA)
-    t_q = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    O.emp_cov([-qhat, qhat], val.numpy())
-    t_cov = time.perf_counter() - t0
-    P = bs * nt * nx * ny
-    full = t_pre * (P / pts_pre) + t_q * ((P / 2) / scores.size) + t_cov * ((P / 2) / val.numel())
-    desc = (f"PRE on BS={bs_pre} of {bs} ({t_pre:.2f}s); np.abs+np.quantile on [{n_cal},{nt_cp},{nx-2},{ny-2}] "
-            f"({t_q:.2f}s); emp_cov on [{n_cal//2},{nt_cp},{nx-2},{ny-2}] ({t_cov:.2f}s); per-unit times scaled to the full step")
-    return P / full / 1e9, desc, t_pre + t_q + t_cov, threads
+    res = torch.cat(res)
+    cal, val = res[:n_cal], res[n_cal:]
+    if w["kind"] == "marginal":
+        TP.marginal_cp(cal, val, ALPHA)
+    else:
+        TP.joint_cp(cal, val, ALPHA, 1e-6 if args.workload == "mhd" else 0.0)
+    t_cp = time.perf_counter() - t0
+    pts = bs * int(np.prod(grid))
+    return pts, t_pre + t_cp, {"pre_s": t_pre, "cp_s": t_cp}
+
+
+CPU_SAMPLE = {   # (batch, time planes) of the bounded CPU sample: the FULL per-GPU batch (the calibration set keeps
+    # its size n, which is what np.quantile's cost depends on) on a slab of time planes; ~5-10 s on 16 cores
+    "ns": (512, 4), "wave": (1024, 8), "wave-joint": (1024, 8), "burgers": (4096, 25), "mhd": (256, 3),
+}
+
+
+def cpu_sample(args, full=False):
+    w = WORKLOADS[args.workload]
+    bs, nt = CPU_SAMPLE[args.workload]
+    if full:
+        bs, nt = (w["bs"] or 256), w["grid"][0]
+    pts, secs, stages = cpu_pipeline(args, bs, nt)
+    threads = torch.get_num_threads()
+    shape = (bs, w["nf"], nt) + tuple(w["grid"][1:])
+    desc = (f"whole pipeline (PRE {stages['pre_s']:.2f}s + conformal step {stages['cp_s']:.2f}s) measured on a "
+            f"{list(shape)} batch = {'the full configuration' if full else f'the full batch on {nt} of {w['grid'][0]} time planes'}; "
+            f"value = its points / its seconds, nothing extrapolated")
+    return pts / secs / 1e9, desc, secs, threads, pts
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path (oracle port: same
-    torch/NumPy calls, all host threads), each step a bounded sample.  Rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path (oracle port: same torch/NumPy
+    calls, all host threads), each step a bounded sample measured as it is.  With --steps <= 2 one step of the
+    FULL configuration is timed as well, so the sample's throughput can be checked against it.  Rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    W = args.warmup
-    for _ in range(min(W, 1)):
-        cpu_reference_sample(args.workload, bs_pre=2, nt_cp=2)
-    vals, secs = [], []
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(args)
+    vals, secs, pts = [], [], 0
     for _ in range(args.steps):
-        v, desc, s, threads = cpu_reference_sample(args.workload)
+        v, desc, s, threads, pts = cpu_sample(args)
         vals.append(v)
         secs.append(s)
-    bs, nf, nt, nx, ny, wdesc = WORKLOADS[args.workload]
-    value = float(np.mean(vals))
-    P = bs * nt * nx * ny
+    value = pts / float(np.mean(secs)) / 1e9
+    full = None
+    if args.steps <= 2 and args.workload in ("ns", "wave", "wave-joint", "burgers") and not args.no_full_cpu:
+        fv, fdesc, fs, _, fpts = cpu_sample(args, full=True)
+        full = {"value": fv, "unit": "Gpoints/s", "seconds": fs, "points": fpts, "what": fdesc,
+                "sample_over_full": value / fv}
+    step = {"marginal": MarginalStep, "joint": JointStep}[WORKLOADS[args.workload]["kind"]]
+    _, _, scaling = geometry(args, world)
     print(json.dumps({
-        "impl": "reference", "metric": "PRE+marginal-CP throughput", "value": value, "unit": "Gpoints/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": W, "ms_per_step": 1e3 * P / (value * 1e9),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wdesc, "fields": nf, "alpha": ALPHA},
-        "cpu_baseline": {"value": value, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc},
+        "impl": "reference", "metric": step.metric, "value": value, "unit": "Gpoints/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(secs)),
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args, world),
+        "cpu_baseline": {"value": value, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc,
+                         "points_per_step": pts, "extrapolated": False, "full_configuration_step": full},
         "e2e": {"value": value, "unit": "Gpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
-
-
-def run_joint(args):
-    """--workload burgers: BASELINE configs[1] on ONE GPU, data-free Joint CP [ref: Joint/Burgers_Residuals_CP.py:
-    182-260]: K1 STORE (residual of the calibration half) -> K2 (per-cell std = modulation, per-sample max of
-    |res|/modulation) -> joint quantile -> K1 COVER on the validation half with the band qhat*modulation (sets never
-    built).  qhat crosses to the host once per step (the band factor is a by-value argument of the ABI)."""
-    import cp_pre_b200
-    from cp_pre_b200 import _lib, ops, programs
-    from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
-    from oracle import synth
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
-    cp_pre_b200.install()
-    import ConvOps_1d as C1
-    bs, nt, nx, desc = JOINT_WORKLOADS[args.workload]
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(dev)
-    c = synth.BURGERS
-    prog = programs.burgers(C1.ConvOperator("t", 1), C1.ConvOperator("x", 1), C1.ConvOperator("x", 2), c["dx"], c["dt"], c["nu"])
-    g = torch.Generator(device=dev).manual_seed(1235)
-    x = torch.linspace(0, 1, nx, device=dev)
-    u = torch.sin(2 * np.pi * (x[None, None, :] + torch.rand(bs, 1, 1, device=dev, generator=g))) \
-        * torch.exp(-torch.linspace(0, 1, nt, device=dev))[None, :, None] + 0.01 * torch.randn(bs, nt, nx, device=dev, generator=g)
-    n_cal = bs // 2
-    k = calibrate_rank(n_cal, n_cal, ALPHA)
-    cells_in = prog.interior_cells(u.shape)
-    k1 = []
-
-    def step(timed=False):
-        if timed:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-        mod, inv, scores = programs.joint_calibration(prog, u[:n_cal])
-        if timed:
-            e1.record()
-            k1.append((e0, e1))
-        qhat = float(ops.select_ranks(scores.reshape(-1, 1), [k])[0].item())
-        inside = prog.coverage_counts(u[n_cal:], qhat, mod)
-        return qhat, (inside == cells_in).float().mean()
-
-    W, K = max(args.warmup, 3), args.steps
-    for _ in range(W):
-        step()
-    torch.cuda.synchronize()
-    l0 = _lib.launch_count()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(0) as clk:
-        torch.cuda.synchronize()
-        a.record()
-        for _ in range(K):
-            qhat, cov = step(timed=True)
-        b.record()
-        torch.cuda.synchronize()
-    ms = a.elapsed_time(b) / K
-    cal_ms = float(np.mean([p.elapsed_time(q) for p, q in k1]))
-    P = bs * nt * nx
-    peak, peak_src = peaks()
-    cal_bytes = (4 + 4 + 4 + 4) * (P // 2)          # K1 STORE read + write, K2 moments read, K2 score read
-    print(json.dumps({
-        "metric": "PRE+joint-CP throughput", "value": P / (ms * 1e-3) / 1e9, "unit": "Gpoints/s", "n_gpus": 1, "steps": K,
-        "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": desc, "fields": 1, "alpha": ALPHA, "per_gpu_batch": bs, "global_batch": bs,
-                   "l2": "inputs (1.7 GB) exceed the 126 MB L2; no flush needed", "qhat": qhat,
-                   "empirical_joint_coverage": float(cov), "target_coverage": 1 - ALPHA},
-        "roofline": {"bound": "hbm", "kernel": "joint calibration of the calibration half: K1 STORE + K2 moments + K2 score",
-                     "achieved": cal_bytes / (cal_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": cal_bytes / (cal_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
-                     "bytes_per_point": 16, "kernel_ms": cal_ms, "share_of_step": cal_ms / ms},
-        "cpu_baseline": None, "e2e": None, "gpu_launches": int(_lib.launch_count() - l0), "clocks": clk.summary(),
     }))
 
 
@@ -385,16 +572,13 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS) + sorted(JOINT_WORKLOADS))
+    ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS))
+    ap.add_argument("--equation", default="momentum", choices=sorted(MHD_EQUATIONS))
+    ap.add_argument("--global-batch", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-full-cpu", action="store_true")
     args = ap.parse_args()
-    if args.workload in JOINT_WORKLOADS:
-        if args.impl == "reference":
-            if int(os.environ.get("RANK", "0")) == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "the reference arm is defined on the headline workload (ns) only"}))
-            return
-        return run_joint(args)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -407,7 +591,8 @@ def main():
     rank, world, device = D.init_from_env()
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
     W, K = max(args.warmup, 3), args.steps
-    step = Step(args.workload, device, world, seed=1234 + rank)
+    kind = WORKLOADS[args.workload]["kind"]
+    step = (MarginalStep if kind == "marginal" else JointStep)(args, device, world, rank)
 
     def barrier():
         if world > 1:
@@ -433,9 +618,9 @@ def main():
             barrier()
         return out, l0, e0, e1, clk
 
-    (qhat, inside), l0, e0, e1, clk = timed_loop()
-    quantile_check = "n/a (single GPU: direct select)"
-    if world > 1:
+    (cal, inside), l0, e0, e1, clk = timed_loop()
+    quantile_check = "n/a"
+    if world > 1 and kind == "marginal":
         # deferred mode: every step's quantile was consumed without a host round trip; settle all
         # overflow counters now.  Any cell that could not be answered from its window voids the
         # timing: repeat the loop in the checked mode (host sync + exact redo inside every step).
@@ -444,7 +629,7 @@ def main():
         quantile_check = "deferred: 0 overflowing cells in every warm-up and timed step"
         if int(bad.item()) > 0:
             step.defer = False
-            (qhat, inside), l0, e0, e1, clk = timed_loop()
+            (cal, inside), l0, e0, e1, clk = timed_loop()
             quantile_check = f"checked per step ({int(bad.item())} overflowing cells seen in deferred mode)"
     torch.cuda.profiler.stop()
     launches = _lib.launch_count() - l0
@@ -455,28 +640,20 @@ def main():
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms, k1_ms, k1c_ms = float(t[0]), float(t[1]), float(t[2])
-    tot_inside, tot_cells = D.allreduce_counts(int(inside.item()), (step.bs - step.n_cal) * step.interior_cells,
-                                               device=device)
-    coverage = tot_inside / tot_cells
+    tot_inside, tot_den = D.allreduce_counts(int(inside.item()), step.coverage_denominator(), device=device)
+    coverage = tot_inside / tot_den
     P_all = step.points * world
     value = P_all / (ms * 1e-3) / 1e9
 
-    # multi-GPU: spot-check the distributed qhat against a direct select on gathered columns
-    verified = None
-    if world > 1:
-        gsel = torch.Generator(device="cpu").manual_seed(7)
-        ids = torch.randint(0, step.scores[0].numel(), (4096,), generator=gsel).to(device)
-        cols = step.scores.reshape(step.n_cal, -1)[:, ids].contiguous()
-        parts = [torch.empty_like(cols) for _ in range(world)]
-        torch.distributed.all_gather(parts, cols)
-        want = step.ops.select_ranks(torch.cat(parts), [step.rank_k])[0]
-        verified = bool(torch.equal(want, qhat.reshape(-1)[ids]))
-        assert verified, "distributed per-cell quantile differs from the direct select"
+    # the calibration result of the last timed step against an independent (torch library) path
+    verified = step.spot_check(cal)
+    assert verified, "calibration result differs from the independent check"
 
     # end-to-end through the public API with host inputs
     e2e = None
     if not args.no_e2e:
-        step.defer = False            # e2e is PCIe-bound: keep the per-step overflow check + exact redo
+        if kind == "marginal":
+            step.defer = False        # e2e is PCIe-bound: keep the per-step overflow check + exact redo
         ee = E2E(step)
         for _ in range(2):
             ee.run()
@@ -485,15 +662,18 @@ def main():
         a.record()
         ke = max(2, min(K, 5))
         for _ in range(ke):
-            ee.run()
+            e2e_cov = ee.run(timed=True)
         b.record()
         barrier()
-        t = torch.tensor([a.elapsed_time(b) / ke], dtype=torch.float64, device=device)
+        rate = ee.h2d_gbs() or 0.0
+        t = torch.tensor([a.elapsed_time(b) / ke, -rate, rate], dtype=torch.float64, device=device)
         if world > 1:
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         e2e = {"value": P_all / (float(t[0]) * 1e-3) / 1e9, "unit": "Gpoints/s", "h2d_bytes_per_step": ee.h2d_bytes * world,
                "d2h_bytes_per_step": ee.d2h_bytes * world, "ms_per_step": float(t[0]),
-               "path": "pinned host batch -> 32-sample double-buffered H2D overlapped with K1 -> K3/K5 -> qhat+coverage D2H"}
+               "h2d_gbs_per_rank_min_max": [-float(t[1]), float(t[2])],
+               "h2d_gbs_aggregate": ee.h2d_bytes * world / (float(t[0]) * 1e-3) / 1e9,
+               "coverage_rank0": e2e_cov, "path": ee.describe()}
         del ee
 
     # bf16-input mode, stated separately (north_star): the same K1 STORE launch on bf16 fields --
@@ -502,15 +682,15 @@ def main():
     if world == 1 and args.workload == "ns":
         vb = step.vars[: step.n_cal].bfloat16()
         for _ in range(2):
-            step.prog.abs_scores(vb, boundary=True, out=step.scores)
+            step.prog.abs_scores(vb, boundary=True, out=step.store)
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
         for i in range(5):
             ev[i].record()
-            step.prog.abs_scores(vb, boundary=True, out=step.scores)
+            step.prog.abs_scores(vb, boundary=True, out=step.store)
         ev[5].record()
         torch.cuda.synchronize()
         bms = float(np.median([ev[i].elapsed_time(ev[i + 1]) for i in range(5)]))
-        bpts = step.n_cal * step.nt * step.nx * step.ny
+        bpts = step.n_cal * step.cells
         bf16 = {"what": "K1 STORE on bf16 fields (fp32 arithmetic and output), calibration half", "kernel_ms": bms,
                 "bytes_per_point": 2 * step.nf + 4, "achieved": (2 * step.nf + 4) * bpts / (bms * 1e-3) / 1e9,
                 "kernel_gpoints_s": bpts / (bms * 1e-3) / 1e9}
@@ -520,34 +700,46 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         bpp = 4 * step.nf + 4
-        k1_pts = step.n_cal * step.nt * step.nx * step.ny          # points one K1 STORE launch processes
+        k1_pts = step.n_cal * step.cells                # points one K1 STORE launch processes
         k1c_pts = step.points - k1_pts
         achieved = bpp * k1_pts / (k1_ms * 1e-3) / 1e9
         cover_gbs = 4 * step.nf * k1c_pts / (k1c_ms * 1e-3) / 1e9
+        stages = step.stage_bytes()
+        cal_b = sum(v for k_, v in stages.items() if k_ != "K1 COVER")
+        step_bytes = cal_b * k1_pts + stages["K1 COVER"] * k1c_pts      # bytes the step moves by construction
+        alg_bytes = 4 * step.nf * (k1_pts + k1c_pts)                      # every input element read once
         cpu = None
         if world == 1 and not args.no_cpu:
-            v, desc, secs, threads = cpu_reference_sample(args.workload)
-            cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc}
+            v, desc, secs, threads, pts = cpu_sample(args)
+            cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc,
+                   "points_per_step": pts, "seconds": secs, "extrapolated": False}
+        _, _, scaling = geometry(args, world)
+        traffic = k1_traffic(args.workload, args.equation)
         print(json.dumps({
-            "metric": "PRE+marginal-CP throughput", "value": value, "unit": "Gpoints/s", "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][5], "fields": step.nf, "alpha": ALPHA,
-                       "per_gpu_batch": step.bs, "global_batch": step.bs * world, "sharding": "batch axis",
-                       "l2": f"inputs ({step.vars.numel() * 4 / 1e9:.1f} GB/GPU) far exceed the 126 MB L2; no flush needed",
-                       "empirical_coverage": coverage, "target_coverage": 1 - ALPHA,
-                       "qhat_spot_check_4096_cells_equal": verified, "quantile_overflow_check": quantile_check},
-            "roofline": {"bound": "hbm", "kernel": "star_kernel<NS_MOMENTUM> (K1: TMA stencil + |.| epilogue, STORE)"
-                         if args.workload == "ns" else "star_kernel<LINEAR> (K1)",
+            "metric": step.metric, "value": value, "unit": "Gpoints/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config_dict(args, world),
+            "checks": {"empirical_coverage": coverage, "target_coverage": 1 - ALPHA,
+                       "calibration_equals_independent_torch_path": verified,
+                       "what": "marginal: 4096 random cells of qhat == torch.kthvalue on the gathered score columns; joint: "
+                               "qhat == torch.kthvalue on the gathered scores and modulation == fp64 std of 4096 gathered columns (1e-6)",
+                       "quantile_overflow_check": quantile_check},
+            "roofline": {"bound": "hbm", "kernel": f"star_kernel<{step.prog.name}> (K1: TMA stencil, STORE epilogue)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_nominal_8000_gbs": achieved / 8000.0,
-                         "traffic": (k1_traffic(args.workload) or {}).get("bytes"), "traffic_detail": k1_traffic(args.workload),
+                         "traffic": (traffic or {}).get("bytes"), "traffic_detail": traffic,
                          "peak_source": peak_src, "bytes_per_point": bpp,
                          "kernel_ms": k1_ms, "kernel_gpoints_s": k1_pts / (k1_ms * 1e-3) / 1e9,
                          "points_per_launch": k1_pts, "share_of_step": k1_ms / ms,
                          "cover_kernel": {"what": "same K1 kernel, COVER epilogue (no residual written), validation half",
                                           "bytes_per_point": 4 * step.nf, "kernel_ms": k1c_ms, "achieved": cover_gbs,
-                                          "frac": cover_gbs / peak, "share_of_step": k1c_ms / ms},
+                                          "frac": cover_gbs / peak, "frac_of_nominal_8000_gbs": cover_gbs / 8000.0,
+                                          "share_of_step": k1c_ms / ms},
+                         "step": {"bytes_per_point_by_stage": stages, "bytes_moved_per_gpu": step_bytes,
+                                  "algorithmic_bytes_per_gpu": alg_bytes,
+                                  "moved_gbs": step_bytes / (ms * 1e-3) / 1e9, "moved_frac": step_bytes / (ms * 1e-3) / 1e9 / peak,
+                                  "algorithmic_gbs": alg_bytes / (ms * 1e-3) / 1e9,
+                                  "algorithmic_frac": alg_bytes / (ms * 1e-3) / 1e9 / peak},
                          "bf16_input_mode": bf16},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
         }))

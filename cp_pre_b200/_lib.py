@@ -48,7 +48,7 @@ class Epilogue(C.Structure):
     _fields_ = [("mode", C.c_int32), ("flags", C.c_int32), ("reduce", C.c_int32),
                 ("band_q", C.c_float), ("d_ref", C.c_void_p), ("ref_stride", C.c_int64 * 4),
                 ("d_weight", C.c_void_p), ("d_out", C.c_void_p), ("out_stride", C.c_int64 * 4),
-                ("d_scores", C.c_void_p)]
+                ("d_scores", C.c_void_p), ("d_band_q", C.c_void_p)]
 
 
 class BC(C.Structure):
@@ -69,6 +69,7 @@ SIGNATURES = {
                                               C.POINTER(Epilogue)]),
     "cppre_cell_moments": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P, _P, _P]),
     "cppre_cell_std": (C.c_int, [_P, C.c_double, C.c_float, _I64, _P, _P, _P]),
+    "cppre_cell_modulation": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, C.c_float, _P, _P, _P]),
     "cppre_joint_score": (C.c_int, [_P, _I64, _P, _I64, _P, _I64, _I64, _P, _P]),
     "cppre_select_workspace_bytes": (C.c_size_t, [_I64, _I64]),
     "cppre_select_ranks": (C.c_int, [_P, _I64, _I64, _I64, C.POINTER(C.c_int32), C.c_int32, _P, _P, _P]),
@@ -83,6 +84,9 @@ SIGNATURES = {
     "cppre_owner_select": (C.c_int, [_P, C.c_int32, C.c_int32, _I64, _I64, C.c_int32, C.c_int32, _I64,
                                      C.POINTER(C.c_void_p), C.c_int32, _P, _P, C.c_int32, _P]),
     "cppre_radix_hist": (C.c_int, [_P, _I64, C.c_uint32, C.c_uint32, C.c_int32, _P, _P]),
+    "cppre_radix_select_begin": (C.c_int, [_P, _P, _I64, _P]),
+    "cppre_radix_select_hist": (C.c_int, [_P, _I64, _P, C.c_int32, _P, _P]),
+    "cppre_radix_select_pick": (C.c_int, [_P, _P, C.c_int32, _P, _P]),
     "cppre_inside_count": (C.c_int, [_P, _I64, _P, _I64, _P, _I64, _I64, _I64, _P, _P]),
     "cppre_inside_count_band": (C.c_int, [_P, _I64, _P, _I64, _P, C.c_float, _I64, _I64, _P, _P]),
     "cppre_transpose_inner": (C.c_int, [_P, _I64, _I64, _I64, _I64, _P, _P]),

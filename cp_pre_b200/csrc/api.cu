@@ -112,6 +112,7 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
     P.epi.o0 = epi->out_stride[3];
     P.epi.scores = epi->d_scores;
     P.epi.band_q = epi->band_q;
+    P.epi.band_qp = epi->d_band_q;
     const bool empty_out = (int64_t)P.g.B * P.g.O2 * P.g.O1 * P.g.O0 == 0;
     if (epi->mode == CPPRE_EPI_STORE) {
         CPPRE_REQUIRE(epi->d_out != nullptr || empty_out, CPPRE_ERR_BAD_ARG, "STORE epilogue without d_out");

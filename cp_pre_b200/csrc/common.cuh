@@ -88,6 +88,7 @@ struct EpiDev {
     int64_t ob, o2, o1, o0;
     float* scores;
     float band_q;
+    const float* band_qp;   // device scalar overriding band_q (COVER), or null
 };
 
 struct Geometry {

@@ -39,17 +39,22 @@ bool vec4_ok(int64_t cells, std::initializer_list<const void*> ptrs, std::initia
 // ------------------------------------------------------------------------------------------
 // K2: shifted-sum moments in fp64, V cells per thread, 4 samples in flight per load stream
 // ------------------------------------------------------------------------------------------
-template <int V>
+// FINAL: std (+ eps) and 1/std are written straight away (single-GPU modulation: one launch, no
+// fp64 intermediates in HBM); otherwise (mean, M2) for the cross-rank merge.
+template <int V, bool FINAL>
 __global__ void __launch_bounds__(kThreads)
 cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
-                    int64_t n, int64_t cells, double* __restrict__ mean, double* __restrict__ m2) {
+                    int64_t n, int64_t cells, double* __restrict__ mean, double* __restrict__ m2,
+                    float add_eps, float* __restrict__ sd, float* __restrict__ inv) {
     const int64_t c = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * V;
     if (c >= cells) return;
     const float* pa = a + c;
     const float* pb = b ? b + c : nullptr;
     if (n == 0) {
+        if constexpr (!FINAL) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) { mean[c + e] = 0.0; m2[c + e] = 0.0; }
+            for (int e = 0; e < V; ++e) { mean[c + e] = 0.0; m2[c + e] = 0.0; }
+        }
         return;
     }
     // shifted sums in fp64: d = x - x_0, so sum(d^2) - sum(d)^2/n does not cancel unless the
@@ -94,9 +99,16 @@ cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __rest
     }
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        mean[c + e] = (double)x0[e] + s1[e] / (double)n;
-        const double v = s2[e] - s1[e] * s1[e] / (double)n;
-        m2[c + e] = v > 0.0 ? v : (v == v ? 0.0 : v);   // clamp round-off negatives, keep NaN
+        double v = s2[e] - s1[e] * s1[e] / (double)n;
+        v = v > 0.0 ? v : (v == v ? 0.0 : v);           // clamp round-off negatives, keep NaN
+        if constexpr (FINAL) {                          // same arithmetic as cell_std_kernel
+            const float s = __fadd_rn((float)sqrt(v / (double)n), add_eps);
+            sd[c + e] = s;
+            if (inv) inv[c + e] = __fdiv_rn(1.0f, s);
+        } else {
+            mean[c + e] = (double)x0[e] + s1[e] / (double)n;
+            m2[c + e] = v;
+        }
     }
 }
 
@@ -974,6 +986,85 @@ radix_hist_kernel(const float* __restrict__ x, int64_t n, uint32_t prefix, uint3
     if (sh[threadIdx.x]) atomicAdd(hist + threadIdx.x, sh[threadIdx.x]);
 }
 
+// K3d: the same radix pass with its (prefix, mask) read from DEVICE state, and the digit choice as a
+// kernel of its own, so the four passes of the Joint quantile run back to back on the stream with
+// nothing but the all-reduce of the 257 counters between them (no host round trip).
+//   state = {prefix, mask, k (remaining rank, 0-based), flags (bit 0: a NaN was seen, bit 1: rank out of range)}
+//   hist  = 256 digit counters + 1 NaN counter (pass 0 only)
+__global__ void __launch_bounds__(kThreads)
+radix_hist_dev_kernel(const float* __restrict__ x, int64_t n, const uint32_t* __restrict__ state, int pass,
+                      uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[257];
+    sh[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) sh[256] = 0u;
+    __syncthreads();
+    const uint32_t prefix = state[0], mask = state[1];
+    const int shift = 24 - 8 * pass;
+    uint32_t nan = 0u;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+        const uint32_t bits = __float_as_uint(__ldg(x + i));
+        const uint32_t key = float_to_key(bits);
+        if (pass == 0) nan += (bits & 0x7fffffffu) > 0x7f800000u ? 1u : 0u;
+        if ((key & mask) == prefix) atomicAdd(&sh[(key >> shift) & 255u], 1u);
+    }
+    if (pass == 0) {
+        nan = __reduce_add_sync(0xffffffffu, nan);
+        if ((threadIdx.x & 31) == 0 && nan) atomicAdd(&sh[256], nan);
+    }
+    __syncthreads();
+    if (sh[threadIdx.x]) atomicAdd(hist + threadIdx.x, sh[threadIdx.x]);
+    if (threadIdx.x == 0 && sh[256]) atomicAdd(hist + 256, sh[256]);
+}
+
+__global__ void __launch_bounds__(kThreads)
+radix_begin_kernel(uint32_t* __restrict__ state, uint32_t* __restrict__ hist, uint32_t k) {
+    const int i = blockIdx.x * kThreads + threadIdx.x;
+    if (i < 257) hist[i] = 0u;
+    if (i < 4) state[i] = i == 2 ? k : 0u;
+}
+
+// One CTA: picks the digit that holds rank k in the (all-reduced) histogram, narrows the state,
+// clears the histogram for the next pass; after the last pass writes the selected value.
+__global__ void __launch_bounds__(kThreads)
+radix_pick_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ state, int pass, float* __restrict__ out) {
+    __shared__ uint32_t warp_tot[8];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const uint32_t c = hist[t];
+    // inclusive scan of the 256 counters: shuffles within a warp, then the 8 warp totals
+    uint32_t s = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += v;
+    }
+    if (lane == 31) warp_tot[w] = s;
+    __syncthreads();
+    uint32_t before = 0u;
+    for (int i = 0; i < w; ++i) before += warp_tot[i];
+    const uint32_t incl = s + before, excl = incl - c;
+    const uint32_t k = state[2];
+    const uint32_t nan_seen = pass == 0 ? hist[256] : 0u;
+    __syncthreads();                                 // everyone has read state / hist
+    const int shift = 24 - 8 * pass;
+    if (c != 0u && k >= excl && k < incl) {          // exactly one thread (or none: rank out of range)
+        state[0] |= (uint32_t)t << shift;
+        state[1] |= 255u << shift;
+        state[2] = k - excl;
+    }
+    if (t == 255 && k >= incl) state[3] |= 2u;       // rank beyond the number of scores
+    if (t == 0 && nan_seen) state[3] |= 1u;
+    hist[t] = 0u;
+    if (t == 0) hist[256] = 0u;
+    if (pass == 3 && out != nullptr) {
+        __syncthreads();
+        if (t == 0) {
+            __threadfence_block();
+            const uint32_t flags = state[3];
+            *out = flags ? __uint_as_float(0x7fc00000u) : __uint_as_float(key_to_float_bits(state[0]));
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // K5: coverage
 // ------------------------------------------------------------------------------------------
@@ -1036,12 +1127,30 @@ int cppre_cell_moments(const float* d_a, int64_t as, const float* d_b, int64_t b
     CPPRE_REQUIRE(d_mean && d_m2 && (d_a || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
     if (vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0})) {
         const int64_t blocks = (cells / 4 + kThreads - 1) / kThreads;
-        cell_moments_kernel<4><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
-                                                                                      d_mean, d_m2);
+        cell_moments_kernel<4, false><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            d_a, as, d_b, bs, n, cells, d_mean, d_m2, 0.0f, nullptr, nullptr);
     } else {
         const int64_t blocks = (cells + kThreads - 1) / kThreads;
-        cell_moments_kernel<1><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_a, as, d_b, bs, n, cells,
-                                                                                      d_mean, d_m2);
+        cell_moments_kernel<1, false><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            d_a, as, d_b, bs, n, cells, d_mean, d_m2, 0.0f, nullptr, nullptr);
+    }
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_cell_modulation(const float* d_a, int64_t as, const float* d_b, int64_t bs, int64_t n, int64_t cells,
+                          float add_eps, float* d_std, float* d_inv, void* stream) {
+    CPPRE_REQUIRE(n >= 1 && cells >= 0, CPPRE_ERR_BAD_ARG, "bad size (n=%lld)", (long long)n);
+    if (cells == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(d_a && d_std, CPPRE_ERR_BAD_ARG, "null pointer");
+    if (vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0})) {
+        const int64_t blocks = (cells / 4 + kThreads - 1) / kThreads;
+        cell_moments_kernel<4, true><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            d_a, as, d_b, bs, n, cells, nullptr, nullptr, add_eps, d_std, d_inv);
+    } else {
+        const int64_t blocks = (cells + kThreads - 1) / kThreads;
+        cell_moments_kernel<1, true><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            d_a, as, d_b, bs, n, cells, nullptr, nullptr, add_eps, d_std, d_inv);
     }
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
@@ -1303,6 +1412,34 @@ int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask
     int64_t blocks = (n + kThreads - 1) / kThreads;
     if (blocks > 148 * 8) blocks = 148 * 8;
     radix_hist_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_x, n, prefix, mask, shift, d_hist);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_radix_select_begin(uint32_t* d_state, uint32_t* d_hist, int64_t k, void* stream) {
+    CPPRE_REQUIRE(d_state && d_hist, CPPRE_ERR_BAD_ARG, "null pointer");
+    CPPRE_REQUIRE(k >= 0 && k < (int64_t(1) << 32), CPPRE_ERR_BAD_ARG, "rank out of range");
+    radix_begin_kernel<<<2, kThreads, 0, (cudaStream_t)stream>>>(d_state, d_hist, (uint32_t)k);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_radix_select_hist(const float* d_x, int64_t n, const uint32_t* d_state, int32_t pass, uint32_t* d_hist,
+                            void* stream) {
+    CPPRE_REQUIRE(n >= 0 && pass >= 0 && pass <= 3, CPPRE_ERR_BAD_ARG, "bad argument");
+    CPPRE_REQUIRE(d_state && d_hist && (d_x || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
+    if (n == 0) return CPPRE_OK;
+    int64_t blocks = (n + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    radix_hist_dev_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_x, n, d_state, pass, d_hist);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_radix_select_pick(uint32_t* d_hist, uint32_t* d_state, int32_t pass, float* d_out, void* stream) {
+    CPPRE_REQUIRE(pass >= 0 && pass <= 3, CPPRE_ERR_BAD_ARG, "bad pass");
+    CPPRE_REQUIRE(d_state && d_hist && (d_out || pass < 3), CPPRE_ERR_BAD_ARG, "null pointer");
+    radix_pick_kernel<<<1, kThreads, 0, (cudaStream_t)stream>>>(d_hist, d_state, pass, d_out);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

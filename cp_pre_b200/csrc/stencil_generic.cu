@@ -69,7 +69,8 @@ generic_kernel(const __grid_constant__ GenericParams p) {
         v = Prog<KIND>::template eval<0>(c, p.scalars);
         const float rf = p.e.ref ? __ldg(p.e.ref + b * p.e.rb + o2 * p.e.r2 + o1 * p.e.r1 + o0 * p.e.r0) : 0.0f;
         if (p.e.mode == CPPRE_EPI_COVER) {
-            const float h = p.e.weight ? __fmul_rn(p.e.band_q, __ldg(p.e.weight + cell)) : p.e.band_q;
+            const float q = p.e.band_qp ? __ldg(p.e.band_qp) : p.e.band_q;
+            const float h = p.e.weight ? __fmul_rn(q, __ldg(p.e.weight + cell)) : q;
             v = (v >= __fsub_rn(rf, h) && v <= __fadd_rn(rf, h)) ? 1.0f : 0.0f;
         } else {
             if (p.e.ref) v = __fsub_rn(v, rf);

@@ -127,48 +127,6 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
         : "memory");
 }
 
-// Register-resident neighbourhood of one thread: RX rows x 4 columns per field.
-template <int NF, int RX, uint64_t MASKS>
-struct StarCtx {
-    const StarCoef& k;
-    float (&prev)[NF][RX][4];
-    float (&cur)[NF][RX][4];
-    float (&next)[NF][RX][4];
-    float (&xm)[NF][4];
-    float (&xp)[NF][4];
-    float (&ym)[NF][RX];
-    float (&yp)[NF][RX];
-
-    // Two neighbouring columns (2h, 2h+1) of row j per evaluation: IP = 2*j + h.  Every arm is
-    // one FFMA2 whose coefficient is a broadcast uniform-register operand; pairs that are not a
-    // register pair of the 128-bit shared-memory loads (the y+-1 arms) cost one extra MOV.
-    template <int SLOT, int FD, int IP>
-    __device__ __forceinline__ f2 D() const {
-        constexpr int j = IP / 2, h = IP % 2, i0 = 2 * h, i1 = 2 * h + 1;
-        constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
-        constexpr int jm = j > 0 ? j - 1 : 0, jp = j < RX - 1 ? j + 1 : RX - 1;
-        const float* c = k.c[SLOT];
-        // accumulation in row-major tap order (t-, x-, y-, centre, y+, x+, t+), like the oracle
-        f2 acc = mk2(0.0f, 0.0f);
-        if constexpr ((m >> ARM_TM) & 1) acc = pfma(mk2(prev[FD][j][i0], prev[FD][j][i1]), c[ARM_TM], acc);
-        if constexpr ((m >> ARM_XM) & 1)
-            acc = pfma(j > 0 ? mk2(cur[FD][jm][i0], cur[FD][jm][i1]) : mk2(xm[FD][i0], xm[FD][i1]), c[ARM_XM], acc);
-        if constexpr ((m >> ARM_YM) & 1)
-            acc = pfma(mk2(h == 0 ? ym[FD][j] : cur[FD][j][1], cur[FD][j][i0]), c[ARM_YM], acc);
-        if constexpr ((m >> ARM_C) & 1) acc = pfma(mk2(cur[FD][j][i0], cur[FD][j][i1]), c[ARM_C], acc);
-        if constexpr ((m >> ARM_YP) & 1)
-            acc = pfma(mk2(cur[FD][j][i1], h == 1 ? yp[FD][j] : cur[FD][j][2]), c[ARM_YP], acc);
-        if constexpr ((m >> ARM_XP) & 1)
-            acc = pfma(j < RX - 1 ? mk2(cur[FD][jp][i0], cur[FD][jp][i1]) : mk2(xp[FD][i0], xp[FD][i1]), c[ARM_XP], acc);
-        if constexpr ((m >> ARM_TP) & 1) acc = pfma(mk2(next[FD][j][i0], next[FD][j][i1]), c[ARM_TP], acc);
-        return acc;
-    }
-    template <int FD, int IP>
-    __device__ __forceinline__ f2 V() const {
-        return mk2(cur[FD][IP / 2][2 * (IP % 2)], cur[FD][IP / 2][2 * (IP % 2) + 1]);
-    }
-};
-
 __device__ __forceinline__ float4 lds128(uint32_t a) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
@@ -201,6 +159,88 @@ __device__ __forceinline__ float lds_cell(uint32_t a) {
     }
 }
 
+// two staged field cells (a 64-bit / 32-bit aligned pair) -> an fp32x2 operand
+__device__ __forceinline__ f2 lds_cells2(uint32_t a) {
+    if constexpr (kBF16) {
+        uint32_t w;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(a));
+        return mk2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+    } else {
+        float x, y;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x), "=f"(y) : "r"(a));
+        return mk2(x, y);
+    }
+}
+
+// Register-resident neighbourhood of one thread: RX rows x 4 columns per field.
+// LAZY (programs with >= 4 fields): the x+-1 rows and the y+-1 edge cells are NOT preloaded into
+// registers for all fields at once (6 fields x (2 x 4 + 2) values = 60 registers, which pushed the
+// MHD momentum / energy kernels past the 128-register budget of 2 CTAs per SM and into local-memory
+// spills); each derivative arm reads its two / one cells from the shared-memory tile at the point
+// of use instead (64-bit / 32-bit ld.shared), so they live for one FFMA2 only.
+template <int NF, int RX, uint64_t MASKS, bool LAZY, uint32_t BUF, uint32_t ROW>
+struct StarCtx {
+    const StarCoef& k;
+    float (&prev)[NF][RX][4];
+    float (&cur)[NF][RX][4];
+    float (&next)[NF][RX][4];
+    float (&xm)[NF][4];
+    float (&xp)[NF][4];
+    float (&ym)[NF][RX];
+    float (&yp)[NF][RX];
+    uint32_t cur_a;      // shared address of this thread's first centre cell of field 0 in the slot of plane t
+
+    // Two neighbouring columns (2h, 2h+1) of row j per evaluation: IP = 2*j + h.  Every arm is
+    // one FFMA2 whose coefficient is a broadcast uniform-register operand; pairs that are not a
+    // register pair of the 128-bit shared-memory loads (the y+-1 arms) cost one extra MOV.
+    template <int SLOT, int FD, int IP>
+    __device__ __forceinline__ f2 D() const {
+        constexpr int j = IP / 2, h = IP % 2, i0 = 2 * h, i1 = 2 * h + 1;
+        constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
+        constexpr int jm = j > 0 ? j - 1 : 0, jp = j < RX - 1 ? j + 1 : RX - 1;
+        const float* c = k.c[SLOT];
+        const uint32_t fa = cur_a + FD * BUF + j * ROW;     // this thread's cell 0 of row j, field FD
+        // accumulation in row-major tap order (t-, x-, y-, centre, y+, x+, t+), like the oracle
+        f2 acc = mk2(0.0f, 0.0f);
+        if constexpr ((m >> ARM_TM) & 1) acc = pfma(mk2(prev[FD][j][i0], prev[FD][j][i1]), c[ARM_TM], acc);
+        if constexpr ((m >> ARM_XM) & 1) {
+            f2 v;
+            if constexpr (j > 0) v = mk2(cur[FD][jm][i0], cur[FD][jm][i1]);
+            else if constexpr (LAZY) v = lds_cells2(fa - ROW + i0 * kES);
+            else v = mk2(xm[FD][i0], xm[FD][i1]);
+            acc = pfma(v, c[ARM_XM], acc);
+        }
+        if constexpr ((m >> ARM_YM) & 1) {
+            float e;
+            if constexpr (h != 0) e = cur[FD][j][1];
+            else if constexpr (LAZY) e = lds_cell(fa - kES);
+            else e = ym[FD][j];
+            acc = pfma(mk2(e, cur[FD][j][i0]), c[ARM_YM], acc);
+        }
+        if constexpr ((m >> ARM_C) & 1) acc = pfma(mk2(cur[FD][j][i0], cur[FD][j][i1]), c[ARM_C], acc);
+        if constexpr ((m >> ARM_YP) & 1) {
+            float e;
+            if constexpr (h != 1) e = cur[FD][j][2];
+            else if constexpr (LAZY) e = lds_cell(fa + 4u * kES);
+            else e = yp[FD][j];
+            acc = pfma(mk2(cur[FD][j][i1], e), c[ARM_YP], acc);
+        }
+        if constexpr ((m >> ARM_XP) & 1) {
+            f2 v;
+            if constexpr (j < RX - 1) v = mk2(cur[FD][jp][i0], cur[FD][jp][i1]);
+            else if constexpr (LAZY) v = lds_cells2(fa + ROW + i0 * kES);
+            else v = mk2(xp[FD][i0], xp[FD][i1]);
+            acc = pfma(v, c[ARM_XP], acc);
+        }
+        if constexpr ((m >> ARM_TP) & 1) acc = pfma(mk2(next[FD][j][i0], next[FD][j][i1]), c[ARM_TP], acc);
+        return acc;
+    }
+    template <int FD, int IP>
+    __device__ __forceinline__ f2 V() const {
+        return mk2(cur[FD][IP / 2][2 * (IP % 2)], cur[FD][IP / 2][2 * (IP % 2) + 1]);
+    }
+};
+
 // OPER: which optional epilogue operands exist, known at compile time (bit 0 = ref, bit 1 =
 // weight) or -1 = decided at run time (any combination; a few predicated instructions more).
 template <int KIND, bool BATCH_ROWS, int RX, uint64_t MASKS, int MODE, int OPER>
@@ -223,6 +263,8 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     constexpr uint32_t WBUF_BYTES = WTMA ? (uint32_t)(TX * kTW * sizeof(float)) : 0u;
     constexpr uint32_t STAGE_BYTES = NF * BUF_BYTES + WBUF_BYTES;
     constexpr uint32_t ROW_BYTES = kTWP * kES;
+    // see StarCtx: the halo operands of programs with many fields are read at the point of use
+    constexpr bool LAZY = NF >= 4 && !BATCH_ROWS;
     (void)SCORE;
 
     // Shared memory is addressed by 32-bit shared-window addresses only (ld.shared / TMA /
@@ -312,6 +354,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     const bool skip_last = !STORE && in0 && y + 3 == p.N0 - 1;
     const bool has_ref = OPER < 0 ? (p.e.ref != nullptr) : ((OPER & 1) != 0);
     const bool has_w = OPER < 0 ? (p.e.weight != nullptr) : ((OPER & 2) != 0);
+    // COVER: q by value, or read once from the device scalar the quantile kernel wrote
+    const float band_q = (COVER && p.e.band_qp != nullptr) ? __ldg(p.e.band_qp) : p.e.band_q;
+    (void)band_q;
 
     // Per-thread row state, fixed over the time loop: which of the RX rows exist (live) and
     // which of them count in a reduction (cnt: not on the x-shell when INTERIOR_1 is set).
@@ -403,7 +448,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 yp[f][j] = lds_cell(a + j * ROW_BYTES + 4u * kES);
             }
         };
-        const StarCtx<NF, RX, MASKS> ctx{p.coef, P, C, N, xm, xp, ym, yp};
+        const StarCtx<NF, RX, MASKS, LAZY, BUF_BYTES, ROW_BYTES> ctx{p.coef, P, C, N, xm, xp, ym, yp, cur_a};
 
         // Slot `stage` (plane t) is read for the last time by the halo loads of the last row.
         // Every warp but the refiller of this step signals that on the slot's named barrier and
@@ -415,9 +460,11 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
         if (plane_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
-                row_halo(J);
-                if constexpr (j == RX - 1)
-                    if (!refiller) bar_arrive(stage + 1, kThreads);
+                if constexpr (!LAZY) {
+                    row_halo(J);
+                    if constexpr (j == RX - 1)
+                        if (!refiller) bar_arrive(stage + 1, kThreads);
+                }
                 if constexpr (j + 1 < RX) fetch_operands(std::integral_constant<int, j + 1>{});
                 if (live & (1u << j)) {
                     const f2 r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
@@ -430,7 +477,7 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                         uint32_t cnt = 0u;
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            const float h = has_w ? __fmul_rn(p.e.band_q, ww[i]) : p.e.band_q;
+                            const float h = has_w ? __fmul_rn(band_q, ww[i]) : band_q;
                             bool in;
                             if (has_ref) {
                                 const float lo = __fsub_rn(rr[i], h), hi = __fadd_rn(rr[i], h);
@@ -470,6 +517,9 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 }
             });
         }
+        // LAZY: the tile of plane t is read by the arms themselves, so the slot is free only now
+        if constexpr (LAZY)
+            if (plane_live && !refiller) bar_arrive(stage + 1, kThreads);
         if constexpr (STORE) outp += p.e.o2;
         if (has_ref) refp += p.e.r2;
         if (has_w) wp += w_plane;

@@ -68,16 +68,43 @@ def _world(group=None) -> int:
 # ---------------------------------------------------------------------------------------
 # Joint: modulation over the global batch
 # ---------------------------------------------------------------------------------------
+_N_CACHE = {}
+
+
+def global_count(n_local: int, group=None, require_equal: bool = False) -> int:
+    """Sum of the ranks' local sample counts.  One tiny all-reduce + host read the first time a
+    (group, n_local) pair is seen, cached afterwards, so steady-state steps have no host round
+    trip.  ``require_equal`` raises when the shards are uneven (``shard_range`` produces such
+    shards whenever BS % world != 0; the windowed marginal quantile and the equal-count gathers
+    assume equal shards and would otherwise return a wrong quantile or hang in NCCL)."""
+    w = _world(group)
+    if w == 1:
+        return int(n_local)
+    key = (0 if group is None else id(group), int(n_local))
+    if key not in _N_CACHE:
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        t = torch.tensor([n_local, -n_local], dtype=torch.int64, device=dev)
+        s = torch.tensor([n_local], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(s, group=group)
+        _N_CACHE[key] = (int(s.item()), int(t[0].item()), -int(t[1].item()))
+    total, n_max, n_min = _N_CACHE[key]
+    if require_equal and n_max != n_min:
+        raise ValueError(f"uneven batch shards (between {n_min} and {n_max} samples per rank): this exchange needs the "
+                         "same number of samples on every rank -- pad or trim the batch to a multiple of the world size")
+    return total
+
+
 def merge_moments(mean: torch.Tensor, m2: torch.Tensor, count: float, group=None):
     """Chan et al. pairwise merge of per-rank (count, mean, M2) -> global (mean, M2, count) with
-    two all-reduces of [cells] fp64:  mean = sum(n_r mean_r)/N;  M2 = sum(M2_r + n_r (mean_r - mean)^2)."""
+    two all-reduces of [cells] fp64:  mean = sum(n_r mean_r)/N;  M2 = sum(M2_r + n_r (mean_r - mean)^2).
+    The global count comes from ``global_count`` (cached), so no host round trip sits between
+    the two all-reduces."""
     if _world(group) == 1:
         return mean, m2, count
-    n = torch.tensor([float(count)], dtype=torch.float64, device=mean.device)
+    total = float(global_count(int(count), group))
     s = mean * float(count)
-    dist.all_reduce(n, group=group)
     dist.all_reduce(s, group=group)
-    total = float(n.item())
     gmean = s / total
     g2 = m2 + float(count) * (mean - gmean) ** 2
     dist.all_reduce(g2, group=group)
@@ -107,6 +134,7 @@ def joint_quantile_gather(scores: torch.Tensor, ranks: Sequence[int], group=None
         select_fn = ops.select_ranks
     w = _world(group)
     if w > 1:
+        global_count(scores.shape[0], group, require_equal=True)
         parts = [torch.empty_like(scores) for _ in range(w)]
         dist.all_gather(parts, scores.contiguous(), group=group)
         scores = torch.cat(parts)
@@ -145,6 +173,22 @@ def joint_quantile_hist(scores: torch.Tensor, rank_k: int, group=None,
         prefix |= d << shift
         mask |= 255 << shift
     return float("nan") if int(nan.item()) else _key_to_float(prefix)
+
+
+def joint_quantile_device(scores: torch.Tensor, rank_k: int, group=None, select_fn: Optional[Callable] = None) -> torch.Tensor:
+    """``joint_quantile_hist`` with the radix state on the device (kernels K3d): four passes of
+    (local 257-counter histogram -> all-reduce -> pick digit on the device) enqueued back to back
+    on the current stream.  Returns a one-element float32 device tensor that the coverage launch
+    takes as ``band_q`` -- no host round trip anywhere between calibration and coverage.
+    ``select_fn(scores, k, allreduce)`` replaces the CUDA kernels in the CPU tests."""
+    if select_fn is None:
+        from . import ops
+        select_fn = ops.radix_select
+    n_total = global_count(scores.numel(), group)
+    if not 0 <= int(rank_k) < n_total:
+        raise ValueError(f"rank {rank_k} out of range for {n_total} scores")
+    ar = (lambda h: dist.all_reduce(h, group=group)) if _world(group) > 1 else None
+    return select_fn(scores, int(rank_k), ar)
 
 
 # ---------------------------------------------------------------------------------------
@@ -215,6 +259,7 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     w = _world(group)
     me = dist.get_rank(group)
     n = scores.shape[0]
+    global_count(n, group, require_equal=True)
     flat = scores.reshape(n, -1)
     cells = flat.shape[1]
     dev = scores.device
@@ -293,6 +338,7 @@ def _exchange_quantiles(scores: torch.Tensor, ranks: Sequence[int], group, selec
     all-to-all, select on [world*n, slab], all-gather the slabs of qhat."""
     w = _world(group)
     n = scores.shape[0]
+    global_count(n, group, require_equal=True)
     flat = scores.reshape(n, -1)
     cells = flat.shape[1]
     slab = (cells + w - 1) // w
@@ -324,6 +370,7 @@ def _window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int)
     w = _world(group)
     me = dist.get_rank(group)
     n = scores.shape[0]
+    global_count(n, group, require_equal=True)
     flat = scores.reshape(n, -1)
     cells = flat.shape[1]
     kt = w * n - int(rank_k)

@@ -108,7 +108,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
                 ref: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None,
                 path: int = L.PATH_AUTO, canonicalise: bool = True,
-                out: Optional[torch.Tensor] = None, band_q: float = 0.0) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, band_q=0.0) -> torch.Tensor:
     """Runs one fused residual program.
 
     fields   CUDA fp32 tensors, all of logical shape [B, N2, N1, N0], any strides (views welcome)
@@ -116,6 +116,8 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     pads     per-slot zero padding (p2, p1, p0)
     Returns the [B, O2, O1, O0] field (STORE), the [B] fp32 scores (SCORE) or the [B] int32
     counts of cells with ref - band_q*weight <= residual <= ref + band_q*weight (COVER).
+    ``band_q`` is a Python float or a one-element float32 CUDA tensor (e.g. the device scalar
+    ``radix_select`` returns): the kernel then reads q itself and nothing crosses to the host.
     """
     lib = L.load()
     require_cuda()
@@ -185,9 +187,16 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         for d in range(4):
             fl[i].stride[d] = f.stride(d)
     epi = L.Epilogue()
-    epi.mode, epi.flags, epi.reduce, epi.band_q = mode, flags | (L.FLAG_IN_BF16 if bf16 else 0), reduce, float(band_q)
+    epi.mode, epi.flags, epi.reduce = mode, flags | (L.FLAG_IN_BF16 if bf16 else 0), reduce
     dev = f0.device
     keep = []
+    if isinstance(band_q, torch.Tensor):
+        if band_q.numel() != 1 or band_q.dtype != torch.float32 or band_q.device != dev:
+            raise ValueError(f"band_q must be a Python float or a one-element float32 tensor on {dev}")
+        epi.d_band_q = band_q.data_ptr()
+        keep.append(band_q)
+    else:
+        epi.band_q = float(band_q)
     if ref is not None:
         if tuple(ref.shape) != (B, *O):
             raise ValueError(f"reference residual has shape {tuple(ref.shape)}, expected {(B, *O)}")
@@ -263,6 +272,23 @@ def cell_std(a: torch.Tensor, b: Optional[torch.Tensor] = None, eps: float = 0.0
     if want_inv:
         return res[0].reshape(a.shape[1:]), res[1].reshape(a.shape[1:])
     return res.reshape(a.shape[1:])
+
+
+def cell_modulation(a: torch.Tensor, b: Optional[torch.Tensor] = None, eps: float = 0.0):
+    """(std + eps, 1/(std + eps)) of a-b over axis 0 in ONE launch (single-GPU modulation_func;
+    same arithmetic as cell_moments + cell_std_from_m2), shaped like a[0]."""
+    if a.shape[0] == 0:
+        raise ValueError("std over an empty sample axis")
+    lib = L.load()
+    fa, sa = _rows(a)
+    fb, sb = (None, 0) if b is None else _rows(b)
+    n, cells = fa.shape
+    sd = torch.empty(cells, dtype=torch.float32, device=a.device)
+    inv = torch.empty(cells, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        L.check(lib.cppre_cell_modulation(_ptr(fa), sa, _ptr(fb), sb, n, cells, float(eps), _ptr(sd), _ptr(inv),
+                                          _stream(a.device)))
+    return sd.reshape(a.shape[1:]), inv.reshape(a.shape[1:])
 
 
 def joint_score(a: torch.Tensor, b: Optional[torch.Tensor], mod: torch.Tensor) -> torch.Tensor:
@@ -413,6 +439,31 @@ def radix_hist(x: torch.Tensor, prefix: int, mask: int, shift: int, hist: torch.
         L.check(lib.cppre_radix_hist(_ptr(flat), flat.numel(), prefix, mask, shift, _ptr(hist),
                                      _stream(x.device)))
     return hist
+
+
+def radix_select(scores, k: int, allreduce=None) -> torch.Tensor:
+    """The k-th smallest (0-based) of a flat score array -- or of the union of a LIST of arrays (scores
+    that arrive in chunks) and, when ``allreduce`` (a callable that sums an int32 CUDA tensor over the
+    ranks in place) is given, of ALL ranks' scores -- as a one-element float32 CUDA tensor.  Four 8-bit
+    radix passes whose state lives on the device: nothing crosses to the host, so the result can be
+    handed to the coverage launch as ``band_q`` right away.  NaN when a score is NaN (np.quantile) or
+    k is out of range."""
+    lib = L.load()
+    parts = [t.reshape(-1).contiguous() for t in (scores if isinstance(scores, (list, tuple)) else [scores])]
+    dev = parts[0].device
+    state = torch.empty(4, dtype=torch.int32, device=dev)
+    hist = torch.empty(257, dtype=torch.int32, device=dev)
+    out = torch.empty(1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        L.check(lib.cppre_radix_select_begin(_ptr(state), _ptr(hist), int(k), st))
+        for p in range(4):
+            for flat in parts:
+                L.check(lib.cppre_radix_select_hist(_ptr(flat), flat.numel(), _ptr(state), p, _ptr(hist), st))
+            if allreduce is not None:
+                allreduce(hist)
+            L.check(lib.cppre_radix_select_pick(_ptr(hist), _ptr(state), p, _ptr(out), st))
+    return out
 
 
 def inside_count(y: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor) -> torch.Tensor:

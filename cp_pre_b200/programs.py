@@ -127,8 +127,11 @@ class ResidualProgram:
         staged = ops.Staged(vars_)
         w = None if half is None else self._unsq(ops.to_cuda(half))
         r = None if centre is None else self._unsq(ops.to_cuda(centre))
+        # q: Python float, or the one-element device tensor a device-side quantile returned (the
+        # kernel reads it itself: no host round trip between calibrate and coverage)
+        band = q if isinstance(q, torch.Tensor) and q.is_cuda else float(q)
         out = self._run(vars_, mode=L.EPI_COVER, flags=self._interior_flags() if interior else 0,
-                        weight=w, ref=r, band_q=float(q))
+                        weight=w, ref=r, band_q=band)
         return staged.back(out)
 
     def interior_cells(self, vars_shape):
@@ -198,25 +201,50 @@ def jorek(equation, D_t, D_R, D_Z, D_RR, D_ZZ, R, coef, gamma=5 / 3):
 # ---------------------------------------------------------------------------------------
 # calibration pipelines
 # ---------------------------------------------------------------------------------------
-def joint_calibration(program: ResidualProgram, cal_pred, cal_out=None, eps: float = 0.0):
-    """Joint CP calibration [ref: Joint/NS_Residuals_CP.py:289-306]:
+def joint_calibration(program: ResidualProgram, cal_pred, cal_out=None, eps: float = 0.0, group=None,
+                      out: Optional[torch.Tensor] = None):
+    """Joint CP calibration [ref: Joint/NS_Residuals_CP.py:289-306, Joint/MHD_Residuals_CP.py:350-351]:
         modulation = std_samples(res(cal_out) - res(cal_pred)) (+ eps)
         scores[i]  = max_cells |res(cal_out)_i - res(cal_pred)_i| / modulation
-    cal_out=None is the data-free PRE form (residual of the prediction alone).
+    cal_out=None is the data-free PRE form (residual of the prediction alone).  With an initialised
+    ``torch.distributed`` process group of more than one rank the inputs are this rank's shard of
+    the batch: the modulation is the std over the GLOBAL batch (per-rank fp64 moments merged over
+    NCCL, dist.global_cell_std) and the scores are rank-local.  ``out`` is an optional caller-owned
+    FULL-size [n, Nt, Nx(, Ny)] CUDA buffer for the stored signed difference.
     Returns (modulation_full, inv_modulation_full, scores); the *_full arrays cover every cell
-    ([Nt,Nx(,Ny)]); the reference's arrays are their ``[1:-1,...]`` interior."""
+    ([Nt,Nx(,Ny)]); the reference's arrays are their ``[1:-1,...]`` interior.
+
+    Bytes per calibration point: 4F + 4 (K1 STORE) + 4 (K2 moments) + 4 (K2 scores) = 4F + 12, against
+    8F for the recompute form (modulation pass + score pass with nothing stored): storing wins from
+    F = 4 fields up (MHD momentum / energy: 36 vs 48 B/point)."""
+    from . import dist as D
     ref = None if cal_out is None else program.residual(ops.to_cuda(cal_out), boundary=True)
     # signed difference res_pred - res_out, stored once (full field, shell included)
-    signed = program._run(ops.to_cuda(cal_pred), ref=None if ref is None else program._unsq(ref))
+    signed = program._run(ops.to_cuda(cal_pred), ref=None if ref is None else program._unsq(ref),
+                          out=program._unsq(out))
     if program.nd == 2:
         signed = signed.squeeze(2)
-    mod, inv = ops.cell_std(signed, None, eps, want_inv=True)
+    if D._world(group) > 1:
+        mod, inv = D.global_cell_std(signed, None, eps, group)
+    else:
+        mod, inv = ops.cell_modulation(signed, None, eps)
     # the max runs over the interior only: shell cells get modulation = +inf, so |d|/inf = 0
     # never wins -- no cropped copy of the residual tensor is made
     masked = torch.full_like(mod, float("inf"))
     program._crop(masked).copy_(program._crop(mod))
     scores = ops.joint_score(signed, None, masked)
     return mod, inv, scores
+
+
+def joint_quantile(scores: torch.Tensor, n: int, alpha: float, group=None) -> torch.Tensor:
+    """calibrate(scores, n, alpha) for the 1-D joint scores, over all ranks of ``group``, as a
+    one-element DEVICE tensor (K3d radix select; the 257-counter histograms are all-reduced over
+    NCCL between passes).  Hand it to ``coverage_counts`` as ``q``.
+    [ref: Joint/MHD_Residuals_CP.py:399, Joint/NS_Residuals_CP.py:311]"""
+    from . import dist as D
+    from .Neural_PDE.UQ.inductive_cp import calibrate_rank
+    total = D.global_count(scores.numel(), group)
+    return D.joint_quantile_device(scores, calibrate_rank(total, n, alpha), group)
 
 
 def marginal_calibration(program: ResidualProgram, cal_pred, cal_out=None, n=None, alphas=(0.1,)):

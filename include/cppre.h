@@ -146,6 +146,10 @@ typedef struct cppre_epilogue {
     float* d_out;          /* STORE: [B, O2, O1, O0] with out_stride */
     int64_t out_stride[4];
     float* d_scores;       /* SCORE: [B] fp32 / COVER: [B] uint32; contiguous, overwritten */
+    /* COVER: optional DEVICE scalar that replaces band_q.  The Joint flow selects qhat on the device
+     * (cppre_radix_select / cppre_select_ranks) and hands the pointer straight to the coverage launch:
+     * no host round trip between calibrate() and emp_cov_joint()  Joint/MHD_Residuals_CP.py:399-401 */
+    const float* d_band_q;
 } cppre_epilogue_t;
 
 /* ---- library state -------------------------------------------------------------------- */
@@ -176,6 +180,10 @@ int cppre_cell_moments(const float* d_a, int64_t a_row_stride, const float* d_b,
 /* std[c] = sqrt(m2[c]/count) + add_eps (fp32); inv[c] = 1/std[c] if d_inv != NULL. */
 int cppre_cell_std(const double* d_m2, double count, float add_eps, int64_t cells,
                    float* d_std, float* d_inv, void* stream);
+/* Both in ONE launch (single-GPU modulation_func: nothing but std / 1/std is written):
+ * std[c] = population std over i < n of a[i,c]-b[i,c], + add_eps; inv[c] = 1/std[c] if d_inv != NULL. */
+int cppre_cell_modulation(const float* d_a, int64_t a_row_stride, const float* d_b, int64_t b_row_stride,
+                          int64_t n, int64_t cells, float add_eps, float* d_std, float* d_inv, void* stream);
 /* scores[i] = max_c |a[i,c]-b[i,c]| / mod[c]  (IEEE division, NaN-propagating max)
  * replaces ncf_metric_joint on stored residuals   Joint/NS_Residuals_CP.py:306 */
 int cppre_joint_score(const float* d_a, int64_t a_row_stride, const float* d_b,
@@ -198,6 +206,24 @@ int cppre_select_ranks(const float* d_scores, int64_t row_stride, int64_t n, int
  * The caller all-reduces d_hist over ranks (NCCL) between passes. */
 int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask, int32_t shift,
                      uint32_t* d_hist, void* stream);
+
+/* The same radix select with its state on the DEVICE, so the four passes run back to back on the
+ * stream and the Joint quantile never crosses to the host (the north_star's "single radix-select
+ * over the per-sample scores" + "all-reduce radix histograms for the global quantile"):
+ *     cppre_radix_select_begin(state, hist, k)                      state = {0, 0, k, 0}, hist = 0
+ *     for pass in 0..3:  cppre_radix_select_hist(x, n, state, pass, hist)
+ *                        [all-reduce SUM of the 257 words of hist over ranks, multi-GPU only]
+ *                        cppre_radix_select_pick(hist, state, pass, out)
+ * d_state: 4 x uint32 {key prefix, key mask, remaining rank, flags}; d_hist: 257 x uint32 (256 digit
+ * bins + the NaN count of pass 0).  pick narrows the state, clears hist for the next pass and, on
+ * pass 3, writes *d_out = the k-th smallest (0-based) of all scores, or NaN when some score is a
+ * NaN (np.quantile) or k is out of range (flags bit 1).  d_out can be passed on as
+ * cppre_epilogue_t::d_band_q.          replaces np.quantile inside calibrate() for 1-D scores
+ *                                      Joint/MHD_Residuals_CP.py:399, Joint/NS_Residuals_CP.py:311 */
+int cppre_radix_select_begin(uint32_t* d_state, uint32_t* d_hist, int64_t k, void* stream);
+int cppre_radix_select_hist(const float* d_x, int64_t n, const uint32_t* d_state, int32_t pass,
+                            uint32_t* d_hist, void* stream);
+int cppre_radix_select_pick(uint32_t* d_hist, uint32_t* d_state, int32_t pass, float* d_out, void* stream);
 
 /* ---- K3w: multi-GPU marginal quantile (batch axis sharded over ranks) --------------------
  * No counterpart in the reference (it is single-process); these three calls replace the naive

@@ -74,6 +74,29 @@ def mhd_momentum(vars_: torch.Tensor, ops: Ops2D | None = None, boundary=False):
     return r if boundary else r[..., 1:-1, 1:-1, 1:-1]
 
 
+def mhd(equation: str, vars_: torch.Tensor, gamma=5.0 / 3.0, ops: Ops2D | None = None, boundary=False):
+    """All five ideal-MHD residuals [ref: Joint/MHD_Residuals_CP.py:225-278]."""
+    o = ops or Ops2D()
+    rho, u, v, p, Bx, By = (vars_[:, j] for j in range(6))
+    D_t, D_x, D_y = o.D_t, o.D_x, o.D_y
+    if equation == "momentum":
+        return mhd_momentum(vars_, o, boundary)
+    if equation == "continuity":
+        r = D_t(rho) + u*D_x(rho) + rho*D_x(u) + v*D_y(rho) + rho*D_y(v)
+    elif equation == "energy":
+        p_gas = p - 0.5*(Bx**2 + By**2)
+        r = D_t(rho) + u*D_x(p) + v*D_y(p) + (gamma-2)*(u*Bx+v*By)*(D_x(Bx) + D_y(By)) + (gamma*p_gas+By**2)*D_x(u) \
+            + (gamma*p_gas+Bx**2)*D_y(v) - Bx*By*(D_y(u) + D_x(v))
+    elif equation == "induction":
+        r = (D_t(Bx) - By*D_y(u) + Bx*D_y(v) - v*D_y(Bx) + u*D_y(By)) \
+            + (D_t(By) + By*D_x(u) - Bx*D_x(v) - v*D_x(Bx) + u*D_x(By))
+    elif equation in ("gauss", "divergence"):
+        r = D_x(Bx) + D_y(By)
+    else:
+        raise ValueError(equation)
+    return r if boundary else r[..., 1:-1, 1:-1, 1:-1]
+
+
 def marginal_cp(cal_res: torch.Tensor, val_res: torch.Tensor, alpha: float):
     """[ref: Marginal/NS_Residuals_CP.py:327-337] data-free marginal CP on stored residuals."""
     scores = np.abs(cal_res.numpy())

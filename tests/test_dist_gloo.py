@@ -54,6 +54,35 @@ def _np_top(cand, cnt, kt, overflow, overflow_cells, cell_offset, network):
     return torch.from_numpy(out)
 
 
+def _np_radix_select(scores, k, allreduce):
+    """NumPy stand-in for ops.radix_select: the same four passes over (prefix, mask, k) state, the
+    257-counter histogram summed over ranks by the injected all-reduce."""
+    x = scores.numpy().reshape(-1)
+    keys = O.float_order_key(x)
+    prefix = mask = 0
+    flags = 0
+    for p in range(4):
+        shift = 24 - 8 * p
+        sel = (keys & np.uint32(mask)) == np.uint32(prefix)
+        h = np.bincount((keys[sel] >> np.uint32(shift)) & np.uint32(255), minlength=256)
+        hist = torch.from_numpy(np.concatenate([h, [np.isnan(x).sum() if p == 0 else 0]]).astype(np.int32))
+        if allreduce is not None:
+            allreduce(hist)
+        c = np.cumsum(hist.numpy()[:256].astype(np.int64))
+        if p == 0 and int(hist[256]):
+            flags |= 1
+        if k >= c[-1]:
+            flags |= 2
+            break
+        d = int(np.searchsorted(c, k, side="right"))
+        k -= int(c[d - 1]) if d else 0
+        prefix |= d << shift
+        mask |= 255 << shift
+    from cp_pre_b200.dist import _key_to_float
+    val = np.nan if flags else _key_to_float(prefix)
+    return torch.tensor([val], dtype=torch.float32)
+
+
 NP_KERNELS = {"select": _np_select, "keys": _np_keys, "window": _np_window, "top": _np_top}
 
 
@@ -96,6 +125,20 @@ def _worker(rank, world, port, out):
     assert np.isnan(D.joint_quantile_hist(nan_scores, 5, hist_fn=_np_hist))
     with pytest.raises(ValueError):
         D.joint_quantile_hist(my_scores, 40, hist_fn=_np_hist)
+    # device-state form (K3d orchestration): same answers, result stays a one-element tensor
+    for k in (0, 13, 39):
+        got = D.joint_quantile_device(my_scores, k, select_fn=_np_radix_select)
+        assert got.shape == (1,) and float(got[0]) == float(want[k])
+    assert np.isnan(float(D.joint_quantile_device(nan_scores, 5, select_fn=_np_radix_select)[0]))
+    with pytest.raises(ValueError):
+        D.joint_quantile_device(my_scores, 40, select_fn=_np_radix_select)
+    # uneven shards: the equal-count exchanges refuse instead of hanging / answering wrongly
+    assert D.global_count(lo + 1 if world > 1 else 1) == sum(D.shard_range(40, r, world)[0] + 1 for r in range(world))
+    uneven = torch.from_numpy(np.abs(full[: 3 + rank]))
+    with pytest.raises(ValueError, match="uneven batch shards"):
+        D.marginal_quantiles(uneven, [1], select_fn=_np_select)
+    with pytest.raises(ValueError, match="uneven batch shards"):
+        D.joint_quantile_gather(torch.from_numpy(scores[: 3 + rank]), [1], select_fn=_np_select)
     # marginal per-cell quantiles through the all-to-all (42 cells: exercises the padding to a
     # multiple of the world size when world == 4; divisible when world == 2)
     q = D.marginal_quantiles(torch.from_numpy(np.abs(full[lo:hi])), [5, 20, 36], select_fn=_np_select)

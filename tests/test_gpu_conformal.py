@@ -391,3 +391,126 @@ def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_
         assert np.isnan(got[11]) and np.isnan(want[11])
     if alpha != 0.5:                                           # 32 slots: the odd wide bracket at world = 8 is listed
         assert len(listed - {17}) <= cells // 50
+
+
+# ----------------------------------------------------------------------------------------------
+# round 2: device-resident Joint flow (K3d radix select, fused modulation, COVER with a device q)
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [1, 19, 256, 1000, 4096, 50000])
+def test_device_radix_select_equals_sorted_order_statistic(n):
+    """K3d: four radix passes with the state on the device return sorted(x)[k] bit for bit, for
+    negative values, ties, +-inf, -0.0; NaN anywhere -> NaN; k out of range -> NaN."""
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(n) * 5).astype(np.float32)
+    if n >= 19:
+        x[:6] = [np.inf, -np.inf, 0.0, -0.0, 1.5, 1.5]
+    want = np.sort(x)
+    xc = cuda(x)
+    for k in sorted({0, n // 3, n // 2, int(0.9 * (n - 1)), n - 1}):
+        got = ops.radix_select(xc, k)
+        assert got.shape == (1,) and got.is_cuda
+        assert float(got) == float(want[k])         # == : +0.0 and -0.0 tie in np.sort's order too
+    assert np.isnan(float(ops.radix_select(xc, n)))                       # rank out of range
+    if n >= 19:
+        y = x.copy()
+        y[7] = np.nan
+        assert np.isnan(float(ops.radix_select(cuda(y), n // 2)))
+        y[7] = -np.float32(np.nan)                                        # NaN with the sign bit set
+        assert np.isnan(float(ops.radix_select(cuda(y), n // 2)))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_device_radix_select_over_emulated_ranks(world):
+    """The multi-GPU Joint quantile with the CUDA kernels: every rank's shard adds its 257 counters to
+    the same histogram (what the NCCL all-reduce does between passes); the pick runs on the summed
+    counters.  Equal to the order statistic of the concatenated scores; NaN on one rank -> NaN."""
+    rng = np.random.default_rng(world)
+    shards = [np.abs(rng.standard_normal(128 + 0 * r) * (1 + r)).astype(np.float32) for r in range(world)]
+    allx = np.sort(np.concatenate(shards))
+    cs = [cuda(s) for s in shards]
+    for k in (0, len(allx) // 2, int(np.ceil((len(allx) + 1) * 0.9)) - 1, len(allx) - 1):
+        got = ops.radix_select(cs, k)
+        assert float(got) == float(allx[k])
+    shards[world - 1][5] = np.nan
+    assert np.isnan(float(ops.radix_select([cuda(s) for s in shards], 3)))
+
+
+def test_fused_modulation_equals_two_kernel_path_and_chan_merge_of_emulated_ranks():
+    """cppre_cell_modulation (one launch) == cell_moments + cell_std_from_m2 bit for bit, and the Chan
+    merge of per-rank fp64 moments (the multi-GPU modulation, dist.merge_moments) reproduces the std
+    over the whole batch: emulated ranks = batch shards on one GPU, CUDA kernels throughout."""
+    rng = np.random.default_rng(11)
+    a = (0.3 * rng.standard_normal((96, 7, 40))).astype(np.float32) + np.float32(2.0)
+    ta = cuda(a)
+    sd, inv = ops.cell_modulation(ta, None, 1e-6)
+    sd2, inv2 = ops.cell_std(ta, None, 1e-6, want_inv=True)
+    assert torch.equal(sd, sd2) and torch.equal(inv, inv2)
+    assert_close_rel(sd.cpu().numpy(), O.modulation_func(a, np.zeros_like(a)) + np.float32(1e-6), 2e-6, "fused modulation")
+    for world in (2, 3, 8):
+        cuts = np.linspace(0, 96, world + 1).astype(int)
+        parts = [ops.cell_moments(ta[lo:hi]) for lo, hi in zip(cuts[:-1], cuts[1:])]
+        ns = [float(hi - lo) for lo, hi in zip(cuts[:-1], cuts[1:])]
+        total = sum(ns)
+        gmean = sum(m * n for (m, _), n in zip(parts, ns)) / total
+        g2 = sum(m2 + n * (m - gmean) ** 2 for (m, m2), n in zip(parts, ns))
+        merged = ops.cell_std_from_m2(g2, total, 1e-6).reshape(sd.shape)
+        assert float(((merged - sd).abs() / sd).max()) <= 2e-7, world
+
+
+def test_coverage_with_a_device_resident_q_equals_the_host_scalar_form():
+    """COVER reads q from a device scalar (cppre_epilogue_t::d_band_q): same counts as q by value,
+    on both kernel paths; and the whole Joint flow stays on the device."""
+    import Utils.ConvOps_2d as C2
+    from cp_pre_b200 import _lib as L
+    n = synth.NS
+    prog = programs.ns_momentum(C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1),
+                                C2.ConvOperator(("x", "y"), 2), n["dx"], n["dy"], n["dt"], n["nu"])
+    v = cuda(synth.fields(3, 3, (40, 6, 16, 128)))
+    mod, inv, scores = programs.joint_calibration(prog, v[:20])
+    qd = programs.joint_quantile(scores, 20, 0.1)
+    assert qd.is_cuda and qd.shape == (1,)
+    assert float(qd) == float(O.calibrate(scores.cpu().numpy(), 20, 0.1))
+    for path in (L.PATH_TMA, L.PATH_GENERIC):
+        prog.path = path
+        a = prog.coverage_counts(v[20:], qd, mod)
+        b = prog.coverage_counts(v[20:], float(qd), mod)
+        assert torch.equal(a, b) and int(a.sum()) > 0
+    prog.path = L.PATH_AUTO
+    with pytest.raises(ValueError):
+        prog.coverage_counts(v[20:], torch.ones(2, device="cuda"), mod)
+
+
+@pytest.mark.parametrize("equation", ["continuity", "momentum", "energy", "induction", "gauss"])
+def test_mhd_joint_cp_flow_against_the_oracle(equation):
+    """BASELINE config 5's flow (data-free Joint CP on an MHD residual, Joint/MHD_Residuals_CP.py:225-278,
+    405-420) on a small slab against the oracle's formulas: residual 1e-5, modulation 2e-5, scores 5e-5;
+    given the oracle's score array qhat is bit-equal, and the fused coverage counts (band qhat*modulation
+    read from the device) equal NumPy's on the stored residual."""
+    import Utils.ConvOps_2d as C2
+    c = synth.MHD
+    prog = programs.mhd(equation, C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1), c["gamma"])
+    shape = (28, 8, 12, 128)
+    v = synth.fields(77, 6, shape, positive=(0, 3))
+    n_cal = 16
+    res_o = O.residual_mhd(equation, *[v[:, j] for j in range(6)], gamma=c["gamma"], ops=O.ops_2d())
+    inner = (slice(None), slice(1, -1), slice(1, -1), slice(1, -1))
+    cal_o, val_o = res_o[:n_cal][inner], res_o[n_cal:][inner]
+    mod_o = O.modulation_func(cal_o, np.zeros_like(cal_o)) + np.float32(1e-6)
+    sc_o = O.ncf_metric_joint(cal_o, np.zeros_like(cal_o), mod_o)
+    vc = cuda(v)
+    mod, inv, sc = programs.joint_calibration(prog, vc[:n_cal], eps=1e-6)
+    from cp_pre_b200 import _lib as L
+    assert L.last_path() != "", equation
+    assert_close_rel(mod[1:-1, 1:-1, 1:-1].cpu().numpy(), mod_o, 2e-5, equation + " modulation")
+    assert_close_rel(sc.cpu().numpy(), sc_o, 5e-5, equation + " joint scores")
+    # identical scores -> identical qhat, bit for bit, through the device-side radix select
+    qd = programs.joint_quantile(cuda(sc_o), n_cal, 0.1)
+    assert float(qd) == float(O.calibrate(sc_o, n_cal, 0.1))
+    # coverage: fused COVER with the library's own residual of the validation samples as ground truth
+    mine = prog.residual(vc[n_cal:], boundary=True).cpu().numpy()
+    q, m = np.float32(float(qd)), mod.cpu().numpy()
+    want = ((mine >= -(q * m)) & (mine <= q * m))[inner].sum(axis=(1, 2, 3))
+    got = prog.coverage_counts(vc[n_cal:], qd, mod).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+    cells = prog.interior_cells(vc.shape)
+    assert O.emp_cov_joint([-(q * m)[inner[1:]], (q * m)[inner[1:]]], mine[inner]) == float((got == cells).mean())
