@@ -43,6 +43,30 @@ inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_o
         CPPRE_CHECK_CUDA(cudaGetLastError());                                              \
     } while (0)
 
+// ---- dynamic shared memory opt-in ----------------------------------------------------------
+// cudaFuncSetAttribute acts on the CURRENT device only, so the "already opted in" memo is kept per
+// device: a process that launches on cuda:0 and later on cuda:1 configures the kernel on both.
+constexpr int kMaxDevices = 64;
+struct SmemOptIn {               // static storage: zero-initialised
+    size_t bytes[kMaxDevices];   // largest dynamic shared memory size opted into, per device
+    bool seen[kMaxDevices];
+};
+template <class Kernel>
+int ensure_dynamic_smem(Kernel kern, SmemOptIn& memo, size_t smem, int carveout_percent = -1) {
+    int dev = 0;
+    CPPRE_CHECK_CUDA(cudaGetDevice(&dev));
+    dev &= kMaxDevices - 1;
+    if (!memo.seen[dev] || smem > memo.bytes[dev]) {
+        if (smem > 48 * 1024)    // sizes up to 48 KB need no opt-in
+            CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (carveout_percent >= 0 && !memo.seen[dev])
+            CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carveout_percent));
+        if (smem > memo.bytes[dev]) memo.bytes[dev] = smem;
+        memo.seen[dev] = true;
+    }
+    return CPPRE_OK;
+}
+
 // ---- order-preserving float <-> uint32 key ------------------------------------------------
 // Unsigned order of the key == total order np.sort uses: negatives (reversed), zeros,
 // positives, +inf, then NaNs whose sign bit is clear.

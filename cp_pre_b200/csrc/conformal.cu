@@ -343,10 +343,10 @@ int launch_regsort(const float* x, int64_t xs, int64_t n, int64_t cells, const R
     constexpr int N = L * R;
     const size_t smem = ((size_t)N * (TC + 1) + TC) * sizeof(uint32_t);
     auto kern = select_regsort_kernel<L, R, TC, COMPACT>;
-    static bool configured = false;
-    if (!configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+    static SmemOptIn memo;
+    {
+        const int rc = ensure_dynamic_smem(kern, memo, smem);
+        if (rc != CPPRE_OK) return rc;
     }
     const int64_t blocks = (cells + TC - 1) / TC;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
@@ -903,10 +903,10 @@ int launch_owner(const float* recv, int32_t w, int32_t W, int64_t slab, int64_t 
     constexpr int N = L * R, TC = 32;
     const size_t smem = ((size_t)N * (TC + 1) + 3 * TC + 1) * sizeof(uint32_t);
     auto kern = owner_select_kernel<L, R, TC>;
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    static SmemOptIn memo;
+    {
+        const int rc = ensure_dynamic_smem(kern, memo, smem);
+        if (rc != CPPRE_OK) return rc;
     }
     const int64_t blocks = (cells + TC - 1) / TC;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
@@ -1266,11 +1266,10 @@ int cppre_window_compact(const float* d_scores, int64_t row_stride, int64_t n, i
     const int64_t blocks = (cells + 127) / 128;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
     const size_t smem = (size_t)slots * 128 * sizeof(float);
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem));
-        configured = smem;
+    static SmemOptIn memo;
+    {
+        const int rc = ensure_dynamic_smem(window_compact_kernel, memo, smem);
+        if (rc != CPPRE_OK) return rc;
     }
     window_compact_kernel<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
         d_scores, row_stride, (int32_t)n, cells, d_lo, d_hi, slots, slab, d_win, d_cnt, d_overflow,
@@ -1341,13 +1340,10 @@ int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, 
     const int64_t blocks = (cells + T - 1) / T;
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
     const size_t smem = (size_t)slots * T * sizeof(float);
-    static size_t configured = 0;
-    if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem));
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(window_exchange_kernel<T>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                              72));
-        configured = smem;
+    static SmemOptIn memo;
+    {
+        const int rc = ensure_dynamic_smem(window_exchange_kernel<T>, memo, smem, 72);
+        if (rc != CPPRE_OK) return rc;
     }
     window_exchange_kernel<T><<<(unsigned)blocks, T, smem, (cudaStream_t)stream>>>(
         d_scores, row_stride, (int32_t)n, cells, d_keys, cells_pad, key_mode, slots, slab, d_overflow,

@@ -46,10 +46,10 @@ extern "C" int cppre_transpose_inner(const float* d_src, int64_t src_batch_strid
     CPPRE_REQUIRE(N <= 256, CPPRE_ERR_UNSUPPORTED, "inner extent %lld > 256: use a plain copy", (long long)N);
     CPPRE_REQUIRE(M < (int64_t(1) << 31) && batch < 65536, CPPRE_ERR_UNSUPPORTED, "problem too large for one launch");
     const size_t smem = (size_t)kTM * (N + 1) * sizeof(float);
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(transpose_inner_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    static SmemOptIn memo;
+    {
+        const int rc = ensure_dynamic_smem(transpose_inner_kernel, memo, smem);
+        if (rc != CPPRE_OK) return rc;
     }
     const dim3 grid((unsigned)((M + kTM - 1) / kTM), (unsigned)batch);
     transpose_inner_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(d_src, src_batch_stride, d_dst, (int32_t)M,

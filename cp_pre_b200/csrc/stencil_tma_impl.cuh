@@ -729,12 +729,10 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     CPPRE_REQUIRE(smem <= 227 * 1024, CPPRE_ERR_UNSUPPORTED, "tile ring of %zu bytes exceeds shared memory", smem);
 
     auto kern = star_kernel<KIND, BR, RX, MASKS, CPPRE_TMA_MODE, CPPRE_TMA_OPER>;
-    static size_t configured = 0;   // per instantiation
-    if (smem > configured) {
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CPPRE_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                              cudaSharedmemCarveoutMaxShared));
-        configured = smem;
+    static SmemOptIn memo;          // per instantiation, per device
+    {
+        const int rc = ensure_dynamic_smem(kern, memo, smem, cudaSharedmemCarveoutMaxShared);
+        if (rc != CPPRE_OK) return rc;
     }
     const int64_t blocks = (int64_t)sp.col_tiles * sp.row_tiles * (BR ? 1 : g.B);
     CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");

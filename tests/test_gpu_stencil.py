@@ -491,3 +491,54 @@ def test_fno_layout_views_are_transposed_by_the_library_and_match_the_contiguous
         want = prog.residual(view.contiguous(), boundary=True)
         got = prog.residual(view, boundary=True)
         assert got.shape == want.shape and torch.equal(got, want), (nx, ny, nt)
+
+
+def test_ns_marginal_cp_at_full_config_size():
+    """The HEADLINE configuration at its full size (BASELINE config 4: NS momentum PRE + marginal per-cell
+    CP, [512,3,50,256,256], Marginal/NS_Residuals_CP.py:327-337), the exact pipeline bench.py times:
+    K1 STORE on the TMA path -> K3 per-cell quantile -> K1 COVER.  A 2-sample slab of the residual against
+    the oracle at 1e-5; qhat of 4096 random cells bit-equal to the oracle's calibrate() on the downloaded
+    score columns; COVER counts of 4 validation samples bit-equal to NumPy on their stored residual."""
+    import bench
+    from Neural_PDE.UQ.inductive_cp import calibrate_rank
+    bs, nt, n = 512, 50, 256
+    n_cal = bs // 2
+    c = synth.NS
+    prog = bench.make_program("ns")
+    v = bench.synth_fields_gpu(bs, 3, (nt, n, n), torch.device("cuda"), seed=1234)
+    scores = torch.empty((n_cal, nt, n, n), device="cuda")
+    prog.abs_scores(v[:n_cal], boundary=True, out=scores)
+    assert L.last_path() == "tma"
+    f = v[:2].cpu().numpy()
+    want = O.residual_ns_momentum(f[:, 0], f[:, 1], f[:, 2], c["dx"], c["dy"], c["dt"], c["nu"], O.ops_2d())
+    assert_close_rel(scores[:2].cpu().numpy(), np.abs(want), TOL, "|R| slab vs oracle")
+    k = calibrate_rank(n_cal, n_cal, 0.1)
+    qhat = ops.select_ranks(scores, [k])[0]
+    ids = torch.randint(0, nt * n * n, (4096,), generator=torch.Generator().manual_seed(3)).cuda()
+    cols = scores.reshape(n_cal, -1)[:, ids].cpu().numpy()
+    np.testing.assert_array_equal(qhat.reshape(-1)[ids].cpu().numpy(), O.calibrate(cols, n_cal, 0.1))
+    inside = prog.coverage_counts(v[n_cal:], 1.0, half=qhat)
+    assert L.last_path() == "tma" and inside.shape == (bs - n_cal,)
+    r4 = prog.residual(v[n_cal:n_cal + 4], boundary=True).cpu().numpy()
+    q = qhat.cpu().numpy()
+    want_cnt = ((r4 >= -q) & (r4 <= q))[:, 1:-1, 1:-1, 1:-1].sum(axis=(1, 2, 3))
+    np.testing.assert_array_equal(inside[:4].cpu().numpy(), want_cnt)
+    cov = float(inside.to(torch.int64).sum()) / ((bs - n_cal) * prog.interior_cells(v.shape))
+    assert 0.88 <= cov <= 0.92, cov                                    # exchangeable halves: ~1 - alpha
+    del v, scores
+    torch.cuda.empty_cache()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_tma_path_on_two_devices_in_one_process():
+    """Function attributes (the dynamic shared memory opt-in of the TMA ring, ~88 KB for NS momentum) are
+    per device: the same process must be able to run the TMA kernel on cuda:0 and then on cuda:1."""
+    prog = __import__("bench").make_program("ns")
+    outs = []
+    for d in (0, 1, 0):
+        v = cuda(synth.fields(9, 3, (4, 6, 16, 128))).to(f"cuda:{d}")
+        outs.append(prog.residual(v, boundary=True).cpu())
+        assert L.last_path() == "tma"
+        s = ops.select_ranks(outs[-1].abs().to(f"cuda:{d}"), [2])      # K3 opt-in path on the same device
+        assert s.device.index == d
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
