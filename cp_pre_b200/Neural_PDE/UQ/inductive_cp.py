@@ -29,13 +29,24 @@ def calibrate_level(n, alpha):
     return np.ceil((n + 1) * (1 - alpha)) / n
 
 
-def calibrate_rank(n_rows, n, alpha):
-    """0-based order statistic that ``np.quantile(..., method='higher')`` returns for the level
-    above: ceil((n_rows-1)*q) in float64.  q outside [0,1] raises like NumPy."""
+def calibrate_rank(n_rows, n, alpha, dtype=np.float32):
+    """0-based order statistic that ``np.quantile(scores, q, method='higher')`` returns for the level
+    above: ceil((n_rows-1)*q) evaluated in the dtype of the SCORE array, as NumPy 2.x does (a Python /
+    NumPy float q is cast to the array's dtype first, ``numpy/lib/_function_base_impl.py: quantile``):
+    float32 for the float32 score arrays this library processes, float64 when the caller hands over
+    float64 scores.  The two differ when n != n_rows (rows=14, n=13, alpha=0.5: index 8 in float32
+    arithmetic, 7 in float64).  q outside [0,1] raises like NumPy."""
     q = calibrate_level(n, alpha)
     if not (0.0 <= q <= 1.0):
         raise ValueError("Quantiles must be in the range [0, 1]")
-    return int(np.ceil((n_rows - 1) * q))
+    ft = np.dtype(dtype).type
+    return int(np.ceil((n_rows - 1) * ft(q)))
+
+
+def _rank_dtype(scores):
+    """float64 score arrays keep NumPy's float64 index arithmetic; everything else is float32."""
+    dt = scores.dtype if isinstance(scores, np.ndarray) else getattr(scores, "dtype", None)
+    return np.float64 if dt in (np.float64, torch.float64) else np.float32
 
 
 def _out(staged, t, scalar):
@@ -53,7 +64,7 @@ def calibrate_many(scores, n, alphas):
     s = ops.to_cuda(scores)
     if s.dim() == 0 or s.shape[0] == 0:
         raise ValueError("calibrate needs at least one score along axis 0")
-    ranks = [calibrate_rank(s.shape[0], n, a) for a in alphas]
+    ranks = [calibrate_rank(s.shape[0], n, a, _rank_dtype(scores)) for a in alphas]
     out = ops.select_ranks(s, ranks)
     return out.detach().cpu().numpy() if staged.numpy else staged.back(out)
 
@@ -65,7 +76,7 @@ def calibrate(scores, n, alpha):
     s = ops.to_cuda(scores)
     if s.dim() == 0 or s.shape[0] == 0:
         raise ValueError("calibrate needs at least one score along axis 0")
-    k = calibrate_rank(s.shape[0], n, alpha)
+    k = calibrate_rank(s.shape[0], n, alpha, _rank_dtype(scores))
     out = ops.select_ranks(s, [k])[0]
     return _out(staged, out, scalar=(s.dim() == 1))
 

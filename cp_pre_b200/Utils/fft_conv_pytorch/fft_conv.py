@@ -68,7 +68,11 @@ def fft_conv(signal: Tensor, kernel: Tensor, bias: Tensor = None,
         padding_ = to_ntuple(padding, n=n)
 
     home = signal.device
-    if not force_fft and _direct_eligible(signal, kernel, bias, padding_, padding_mode, stride_, dilation_,
+    # autograd: the fused kernels carry no graph, so a call whose signal / kernel / bias requires grad
+    # (an _FFTConv layer being trained, a PRE loss through the spectral path) runs the same arithmetic
+    # in torch ops (cuFFT + complex elementwise), which is differentiable in all three
+    grad_path = ops.needs_grad(signal, kernel, bias)
+    if not force_fft and not grad_path and _direct_eligible(signal, kernel, bias, padding_, padding_mode, stride_, dilation_,
                                           inverse):
         # forward spectral == direct correlation (relation R2): one pass of K1, no FFT
         x = ops.to_cuda(signal)[:, 0]
@@ -80,8 +84,8 @@ def fft_conv(signal: Tensor, kernel: Tensor, bias: Tensor = None,
         out = out.reshape((out.shape[0], 1) + tuple(out.shape[1 + (3 - n):]))
         return out if out.device == home else out.to(home)
 
-    sig = ops.to_cuda(signal)
-    ker = ops.to_cuda(kernel)
+    sig = ops.to_cuda(signal, keep_graph=grad_path)
+    ker = ops.to_cuda(kernel, keep_graph=grad_path)
     # dilation: spread the taps with zeros (kron with a one-hot offset), trimming the tail
     if any(d != 1 for d in dilation_):
         offset = torch.zeros(1, 1, *dilation_, device=sig.device, dtype=sig.dtype)
@@ -98,7 +102,12 @@ def fft_conv(signal: Tensor, kernel: Tensor, bias: Tensor = None,
     sig_hat = rfftn(sig.float(), dim=dims)
     ker_hat = rfftn(f.pad(ker, kpad).float(), dim=dims)
     flags = L.SPEC_CONJ_FIRST | (L.SPEC_INVERSE if inverse else 0)
-    if ker_hat.shape[0] == 1 and ker_hat.shape[1] == 1:
+    if grad_path:
+        gk = ker_hat.conj()
+        if inverse:
+            gk = 1.0 / (gk + 1e-6)
+        prod = sig_hat * gk
+    elif ker_hat.shape[0] == 1 and ker_hat.shape[1] == 1:
         prod = ops.spectral_pointwise(sig_hat, ker_hat[0, 0], flags, 1e-6)
     else:
         # multi-channel kernels broadcast against the signal spectrum like the reference's
@@ -111,7 +120,7 @@ def fft_conv(signal: Tensor, kernel: Tensor, bias: Tensor = None,
         slice(0, size[i] - ker.size(i) + 1, stride_[i - 2]) for i in range(2, sig.ndim))
     out = out[crop].contiguous()
     if bias is not None:
-        out = out + ops.to_cuda(bias).view((1, -1) + (1,) * n)
+        out = out + ops.to_cuda(bias, keep_graph=grad_path).view((1, -1) + (1,) * n)
     return out if out.device == home else out.to(home)
 
 

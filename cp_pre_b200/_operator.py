@@ -152,22 +152,52 @@ def taps_of(kernel: torch.Tensor) -> np.ndarray:
 
 
 class _LinearStencilFn(torch.autograd.Function):
-    """Autograd through ``D(field)`` w.r.t. the field (PRE as a training loss,
-    [ref: Physics_Informed/Wave_FNO_PI.py:202-228]): the adjoint of a zero-padded
-    cross-correlation is the cross-correlation with the flipped taps and padding k-1-p."""
+    """Autograd through ``D(field)`` (PRE as a training loss, [ref: Physics_Informed/Wave_FNO_PI.py:202-228]).
+    d/d(field): the adjoint of a zero-padded cross-correlation is the cross-correlation with the flipped
+    taps and padding k-1-p -- one more K1 launch.  d/d(kernel) (``D.kernel.requires_grad = True``, :206):
+    grad_K[a,b,c] = sum over samples and cells of grad[o] * field[o + (a,b,c) - pad], one reduction per
+    entry of the dense kernel tensor (training-time only; every entry, zeros included, gets its gradient
+    because the optimiser sees the dense tensor)."""
 
     @staticmethod
-    def forward(ctx, field4, k3, pad):
-        ctx.k3, ctx.pad, ctx.in_shape = k3, pad, field4.shape
-        return ops.run_program(L.PROG_LINEAR, [field4], [k3], [pad])
+    def forward(ctx, field4, kern, k3, pad):
+        ctx.k3, ctx.pad = k3, pad
+        ctx.kern_shape = None if kern is None else tuple(kern.shape)
+        ctx.kern_device = None if kern is None else kern.device
+        if kern is not None and kern.requires_grad:
+            ctx.save_for_backward(field4)
+        return ops.run_program(L.PROG_LINEAR, [field4.detach()], [k3], [pad])
 
     @staticmethod
     def backward(ctx, grad):
+        import torch.nn.functional as F
         k3, pad = ctx.k3, ctx.pad
-        flipped = np.ascontiguousarray(k3[::-1, ::-1, ::-1])
-        adj_pad = tuple(k - 1 - p for k, p in zip(k3.shape, pad))
-        g = ops.run_program(L.PROG_LINEAR, [grad.contiguous()], [flipped], [adj_pad])
-        return g, None, None
+        grad = grad.contiguous()
+        g_field = g_kern = None
+        if ctx.needs_input_grad[0]:
+            flipped = np.ascontiguousarray(k3[::-1, ::-1, ::-1])
+            adj_pad = tuple(k - 1 - p for k, p in zip(k3.shape, pad))
+            g_field = ops.run_program(L.PROG_LINEAR, [grad], [flipped], [adj_pad])
+        if ctx.kern_shape is not None and ctx.needs_input_grad[1]:
+            (x4,) = ctx.saved_tensors
+            xp = F.pad(x4.detach(), (pad[2], pad[2], pad[1], pad[1], pad[0], pad[0]))
+            O2, O1, O0 = grad.shape[1:]
+            gk = torch.empty(k3.shape, dtype=torch.float32, device=grad.device)
+            for a in range(k3.shape[0]):
+                for b in range(k3.shape[1]):
+                    for c in range(k3.shape[2]):
+                        gk[a, b, c] = (xp[:, a:a + O2, b:b + O1, c:c + O0] * grad).sum()
+            g_kern = gk.reshape(ctx.kern_shape).to(ctx.kern_device)
+        return g_field, g_kern, None, None
+
+
+def differentiable_apply(op, x4: torch.Tensor) -> torch.Tensor:
+    """``op``'s kernel applied to a library-layout field [B,N2,N1,N0] on the autograd graph (w.r.t. the
+    field and, if it requires grad, the kernel tensor)."""
+    kern = op.kernel
+    k3 = op._fl.kernel3(op._taps(kern))
+    pad = tuple(s // 2 for s in k3.shape) if op._fl.same_padding else (0, 0, 0)
+    return _LinearStencilFn.apply(x4, kern if kern.requires_grad else None, k3, pad)
 
 
 class StencilOperator:
@@ -248,15 +278,11 @@ class StencilOperator:
             raise RuntimeError(f"weight of ndim {kern.dim()} does not fit a {fl.name} operator")
         x, staged, _ = self._prep_field(field)
         pad = tuple(s // 2 for s in k3.shape) if fl.same_padding else (0, 0, 0)
-        needs_grad = torch.is_grad_enabled() and x.requires_grad
-        xc = x if x.is_cuda else ops.to_cuda(x)
-        if needs_grad and not x.is_cuda:
-            xc = x.cuda()                   # keeps the graph
-        x4 = fl.field4(xc if needs_grad else xc.detach())
-        if needs_grad:
-            out = _LinearStencilFn.apply(x4, k3, pad)
+        if ops.needs_grad(x, kern):         # differentiable w.r.t. the field and the kernel tensor
+            x4 = fl.field4(ops.to_cuda(x, keep_graph=True))
+            out = _LinearStencilFn.apply(x4, kern if kern.requires_grad else None, k3, pad)
         else:
-            out = ops.run_program(L.PROG_LINEAR, [x4], [k3], [pad])
+            out = ops.run_program(L.PROG_LINEAR, [fl.field4(ops.to_cuda(x))], [k3], [pad])
         return staged.back(fl.unfield4(out))
 
     # --- a5: spectral path ----------------------------------------------------------------
@@ -280,14 +306,15 @@ class StencilOperator:
         kern = self._kernel(kernel)
         fl = self._fl
         x, staged, _ = self._prep_field(field)
-        xc = ops.to_cuda(x)
+        grad_path = ops.needs_grad(x, kern)
+        xc = ops.to_cuda(x, keep_graph=grad_path)
         if fl.name != "spatial":
             xc = xc.unsqueeze(1)
         nd = fl.kernel_ndim
         p = kern.size(-1) // 2
         padded = F.pad(xc, (p, p) * nd) if pad_field else xc
         dims = tuple(range(2, padded.ndim))
-        k = ops.to_cuda(kern)
+        k = ops.to_cuda(kern, keep_graph=grad_path)
         kpad = []
         for i in reversed(range(nd)):
             kpad += [0, padded.size(2 + i) - k.size(i)]
@@ -301,7 +328,15 @@ class StencilOperator:
                 flags |= L.SPEC_CONJ_LAST
         elif correlation:
             flags |= L.SPEC_CONJ_FIRST
-        prod = ops.spectral_pointwise(f_hat, k_hat, flags, eps)
+        if grad_path:       # same arithmetic in torch complex ops: differentiable w.r.t. field and kernel
+            g = k_hat.conj() if flags & L.SPEC_CONJ_FIRST else k_hat
+            if flags & L.SPEC_INVERSE:
+                g = 1.0 / (g + eps)
+            if flags & L.SPEC_CONJ_LAST:
+                g = g.conj()
+            prod = f_hat * g
+        else:
+            prod = ops.spectral_pointwise(f_hat, k_hat, flags, eps)
         out = torch.fft.irfftn(prod, dim=dims)          # no size given, like the reference
         if slice_pad:
             crop = (slice(None), slice(None)) + tuple(

@@ -48,11 +48,18 @@ class Staged:
         return t
 
 
-def to_cuda(x, dtype=torch.float32) -> torch.Tensor:
-    """Host array / CPU tensor -> current CUDA device (H2D); CUDA tensor -> itself."""
+def needs_grad(*xs) -> bool:
+    """True when autograd is recording and one of ``xs`` is a tensor that requires grad: such calls
+    take the differentiable paths (the fused kernels have no graph), never a silent detach."""
+    return torch.is_grad_enabled() and any(isinstance(x, torch.Tensor) and x.requires_grad for x in xs)
+
+
+def to_cuda(x, dtype=torch.float32, keep_graph: bool = False) -> torch.Tensor:
+    """Host array / CPU tensor -> current CUDA device (H2D); CUDA tensor -> itself.  Detached unless
+    ``keep_graph`` (the differentiable paths), in which case dtype / device moves stay on the graph."""
     require_cuda()
     if isinstance(x, torch.Tensor):
-        t = x.detach()
+        t = x if (keep_graph and needs_grad(x)) else x.detach()
     else:
         t = torch.from_numpy(np.ascontiguousarray(x))
     if t.dtype != dtype:

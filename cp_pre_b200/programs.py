@@ -82,13 +82,44 @@ class ResidualProgram:
         ks, pads = self._slots()
         return ops.run_program(self.kind, self._fields(vars_), ks, pads, self.scalars, path=self.path, **kw)
 
+    # -- autograd -----------------------------------------------------------
+    def _needs_grad(self, vars_):
+        return ops.needs_grad(vars_, *[getattr(op, "kernel", None) for op in self.operators])
+
+    def _residual_autograd(self, vars_):
+        """The FULL residual field on the autograd graph: every derivative slot is one differentiable
+        K1 launch (``_LinearStencilFn``: backward = K1 with the adjoint taps, plus the per-tap reduction
+        for ``kernel.requires_grad``) and the program's algebra is torch elementwise ops, so the product
+        rule of the nonlinear programs is autograd's.  Used only when a gradient is asked for (a PRE loss,
+        [ref: Physics_Informed/Wave_FNO_PI.py:202-228]); values agree with the fused kernel to fp32 rounding."""
+        from ._operator import differentiable_apply
+        v = ops.to_cuda(vars_, keep_graph=True)
+        fs = [v] if self.field_index is None else [v[:, j] for j in self.field_index]
+        if self.nd == 2:
+            fs = [f.unsqueeze(2) for f in fs]
+        if getattr(self, "coef_field", None) is not None:
+            cf = ops.to_cuda(self.coef_field, keep_graph=True).reshape(-1)
+            fs.append(cf.view(1, 1, 1, -1).expand(fs[0].shape))
+        cache = {}
+
+        def D(slot, f):
+            if (slot, f) not in cache:
+                cache[(slot, f)] = differentiable_apply(self.operators[slot], fs[f].contiguous())
+            return cache[(slot, f)]
+
+        full = _FORMULAS[self.kind](lambda f: fs[f], D, self.scalars)
+        return full.squeeze(2) if self.nd == 2 else full
+
     # -- the reference-facing call ------------------------------------------------------
     def residual(self, vars_, boundary=False):
         """The PDE residual; interior view (``[...,1:-1,1:-1(,1:-1)]``) unless boundary=True."""
         staged = ops.Staged(vars_)
-        full = self._run(vars_)
-        if self.nd == 2:
-            full = full.squeeze(2)
+        if self._needs_grad(vars_):
+            full = self._residual_autograd(vars_)
+        else:
+            full = self._run(vars_)
+            if self.nd == 2:
+                full = full.squeeze(2)
         return staged.back(full if boundary else self._crop(full))
 
     __call__ = residual
@@ -99,6 +130,14 @@ class ResidualProgram:
         residual field (boundary=True form) or None; ``out`` an optional caller-owned FULL-size
         CUDA destination (e.g. a batch slice of a larger score tensor)."""
         staged = ops.Staged(vars_)
+        if self._needs_grad(vars_) or ops.needs_grad(ref):
+            full = self._residual_autograd(vars_)
+            if ref is not None:
+                full = full - ops.to_cuda(ref, keep_graph=True)
+            full = full.abs()
+            if out is not None:
+                raise ValueError("out= cannot be combined with a gradient-carrying call")
+            return staged.back(full if boundary else self._crop(full))
         r = None if ref is None else self._unsq(ops.to_cuda(ref))
         full = self._run(vars_, flags=L.FLAG_ABS, ref=r, out=self._unsq(out))
         if self.nd == 2:
@@ -109,6 +148,12 @@ class ResidualProgram:
         """Per-sample reduce over cells of |residual - ref| * inv_modulation; only [BS] floats
         are written.  ``inv_modulation`` / ``ref`` are FULL-size ([Nt,Nx(,Ny)] / [BS,Nt,...])."""
         staged = ops.Staged(vars_)
+        if self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation):
+            v = self.abs_scores(vars_, ref=ref, boundary=True)
+            if inv_modulation is not None:
+                v = v * ops.to_cuda(inv_modulation, keep_graph=True)
+            v = (self._crop(v) if interior else v).flatten(1)
+            return staged.back(v.amax(dim=1) if reduce == "max" else v.sum(dim=1))
         w = None if inv_modulation is None else self._unsq(ops.to_cuda(inv_modulation))
         r = None if ref is None else self._unsq(ops.to_cuda(ref))
         flags = L.FLAG_ABS | (self._interior_flags() if interior else 0)
@@ -141,6 +186,69 @@ class ResidualProgram:
         for d in dims:
             n *= max(int(d) - 2, 0)
         return n
+
+
+# ---------------------------------------------------------------------------------------
+# the programs' algebra in torch ops (autograd path only; csrc/programs.cuh is the fused form).
+# V(f): field f of the program; D(slot, f): derivative slot applied to field f; s: scalars.
+# ---------------------------------------------------------------------------------------
+def _f_ns_momentum(V, D, s):
+    u, v = V(0), V(1)
+    a, b, c, d = s[:4]
+    rx = a * D(0, 0) + b * (u * D(1, 0)) + c * (v * D(2, 0)) - d * D(3, 0) + b * D(1, 2)
+    ry = a * D(0, 1) + c * (u * D(1, 1)) + b * (v * D(2, 1)) - d * D(3, 1) + c * D(2, 2)
+    return rx + ry
+
+
+def _f_mhd_momentum(V, D, s):
+    rho, u, v, Bx, By = V(0), V(1), V(2), V(4), V(5)
+    ir = 1.0 / rho
+    rx = D(0, 1) + u * D(1, 1) + ir * D(1, 3) - 2 * (Bx * ir) * D(1, 4) + v * D(2, 1) - (By * ir) * D(2, 4) - (Bx * ir) * D(2, 5)
+    ry = D(0, 2) + u * D(1, 2) + ir * D(2, 3) - 2 * (By * ir) * D(2, 5) + v * D(2, 2) - (By * ir) * D(1, 4) - (Bx * ir) * D(1, 5)
+    return rx + ry
+
+
+def _f_mhd_energy(V, D, s):
+    g = s[0]
+    u, v, p, Bx, By = V(1), V(2), V(3), V(4), V(5)
+    pg = p - 0.5 * (Bx ** 2 + By ** 2)
+    return (D(0, 0) + u * D(1, 3) + v * D(2, 3) + (g - 2) * (u * Bx + v * By) * (D(1, 4) + D(2, 5))
+            + (g * pg + By ** 2) * D(1, 1) + (g * pg + Bx ** 2) * D(2, 2) - Bx * By * (D(2, 1) + D(1, 2)))
+
+
+def _f_mhd_induction(V, D, s):
+    u, v, Bx, By = V(0), V(1), V(2), V(3)
+    rx = D(0, 2) - By * D(2, 0) + Bx * D(2, 1) - v * D(2, 2) + u * D(2, 3)
+    ry = D(0, 3) + By * D(1, 0) - Bx * D(1, 1) - v * D(1, 2) + u * D(1, 3)
+    return rx + ry
+
+
+def _f_jorek_continuity(V, D, s):
+    rho, R = V(0), V(3)
+    return (D(0, 0) - R * (D(1, 0) * D(2, 1) - D(1, 1) * D(2, 0)) - 2 * rho * D(2, 1)
+            - s[0] * (D(3, 0) + (1.0 / R) * D(1, 0) + D(4, 0)))
+
+
+def _f_jorek_temperature(V, D, s):
+    rho, T, R = V(0), V(2), V(3)
+    return (T * D(0, 0) + rho * D(0, 2) - rho * R * (D(1, 2) * D(2, 1) - D(1, 1) * D(2, 2))
+            + T * R * (D(1, 0) * D(2, 1) - D(1, 1) * D(2, 0)) + 2 * s[1] * rho * T * D(2, 1)
+            + s[0] * (D(3, 2) + (1.0 / R) * D(1, 2) + D(4, 2)))
+
+
+_FORMULAS = {
+    L.PROG_LINEAR: lambda V, D, s: D(0, 0),
+    L.PROG_BURGERS: lambda V, D, s: s[0] * D(0, 0) + s[1] * (V(0) * D(1, 0)) - s[2] * D(2, 0),
+    L.PROG_NS_CONTINUITY: lambda V, D, s: D(0, 0) + s[0] * D(1, 1),
+    L.PROG_NS_MOMENTUM: _f_ns_momentum,
+    L.PROG_MHD_CONTINUITY: lambda V, D, s: D(0, 0) + V(1) * D(1, 0) + V(0) * D(1, 1) + V(2) * D(2, 0) + V(0) * D(2, 2),
+    L.PROG_MHD_MOMENTUM: _f_mhd_momentum,
+    L.PROG_MHD_ENERGY: _f_mhd_energy,
+    L.PROG_MHD_INDUCTION: _f_mhd_induction,
+    L.PROG_MHD_GAUSS: lambda V, D, s: D(1, 0) + D(2, 1),
+    L.PROG_JOREK_CONTINUITY: _f_jorek_continuity,
+    L.PROG_JOREK_TEMPERATURE: _f_jorek_temperature,
+}
 
 
 # ---------------------------------------------------------------------------------------

@@ -447,12 +447,13 @@ def calibrate_quantile_level(n, alpha):
     return np.ceil((n + 1) * (1 - alpha)) / n
 
 
-def calibrate_rank(n_rows, n, alpha):
-    """0-based order statistic NumPy's method='higher' selects: ceil((n_rows-1)*q)."""
+def calibrate_rank(n_rows, n, alpha, dtype=F32):
+    """0-based order statistic NumPy's method='higher' selects: ceil((n_rows-1)*q) in the dtype of
+    the score array (NumPy 2.x casts a scalar q to it), float32 for this path's score arrays."""
     q = calibrate_quantile_level(n, alpha)
     if not (0.0 <= q <= 1.0):
         raise ValueError("Quantiles must be in the range [0, 1]")
-    return int(np.ceil((n_rows - 1) * q))
+    return int(np.ceil((n_rows - 1) * np.dtype(dtype).type(q)))
 
 
 def calibrate(scores, n, alpha):

@@ -542,3 +542,57 @@ def test_tma_path_on_two_devices_in_one_process():
         s = ops.select_ranks(outs[-1].abs().to(f"cuda:{d}"), [2])      # K3 opt-in path on the same device
         assert s.device.index == d
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+def test_autograd_through_nonlinear_programs_kernel_tensor_and_spectral_paths():
+    """SURVEY 8 f-2 / ADVICE r1: a call whose input, kernel or weight requires grad must either produce
+    the gradient or raise -- never detach silently.  Nonlinear residual programs (product rule), d/d(kernel)
+    (D.kernel.requires_grad = True, Physics_Informed/Wave_FNO_PI.py:206), the spectral path and the
+    _FFTConv layers all backpropagate; checked against torch.autograd through plain PyTorch fp32
+    expressions of the same ops (oracle/torch_port.py)."""
+    import torch.nn.functional as F
+    from oracle import torch_port as TP
+    from fft_conv_pytorch.fft_conv import FFTConv2d, fft_conv
+    o, c = _programs_2d(), synth.NS
+    # NS momentum as a PRE loss: d(loss)/d(vars)
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], c["dx"], c["dy"], c["dt"], c["nu"])
+    v = cuda(synth.fields(5, 3, (2, 6, 12, 16))).requires_grad_(True)
+    r = prog.residual(v)
+    assert r.requires_grad
+    (r ** 2).sum().backward()
+    v2 = v.detach().cpu().clone().requires_grad_(True)
+    (TP.ns_momentum(v2, c["dx"], c["dy"], c["dt"], c["nu"]) ** 2).sum().backward()
+    assert_close_rel(v.grad.cpu().numpy(), v2.grad.numpy(), 2e-5, "d loss / d vars (NS momentum)")
+    # the fused forward of the same call (no grad) agrees with the autograd forward
+    assert_close_rel(prog.residual(v.detach()).cpu().numpy(), r.detach().cpu().numpy(), TOL, "fused vs autograd forward")
+    # MHD momentum (a division by rho inside the product rule) through the fused score epilogue's twin
+    m = synth.MHD
+    pm = programs.mhd("momentum", o["D_t"], o["D_x"], o["D_y"], m["gamma"])
+    w = cuda(synth.fields(6, 6, (2, 5, 10, 16), positive=(0, 3))).requires_grad_(True)
+    pm.joint_scores(w).sum().backward()
+    w2 = w.detach().cpu().clone().requires_grad_(True)
+    TP.mhd_momentum(w2).abs().flatten(1).amax(dim=1).sum().backward()
+    assert_close_rel(w.grad.cpu().numpy(), w2.grad.numpy(), 5e-5, "d score / d vars (MHD momentum)")
+    # d/d(kernel): a trainable operator
+    W = _wave_op()
+    W.kernel = W.kernel.clone().cuda().requires_grad_(True)
+    u = torch.randn(3, 6, 12, 16, device="cuda")
+    (W(u) ** 2).sum().backward()
+    k2 = W.kernel.detach().clone().requires_grad_(True)
+    (F.conv3d(u.unsqueeze(1), k2[None, None], padding=1).squeeze(1) ** 2).sum().backward()
+    assert_close_rel(W.kernel.grad.cpu().numpy(), k2.grad.cpu().numpy(), 2e-5, "d loss / d kernel")
+    # spectral path and the FFTConv layer: gradients w.r.t. signal, weight and bias
+    sig = torch.randn(2, 1, 16, 18, device="cuda", requires_grad=True)
+    ker = torch.randn(1, 1, 3, 3, device="cuda", requires_grad=True)
+    fft_conv(sig, ker, padding=1).sum().backward()
+    s2, k2 = sig.detach().clone().requires_grad_(True), ker.detach().clone().requires_grad_(True)
+    F.conv2d(s2, k2, padding=1).sum().backward()
+    assert_close_rel(sig.grad.cpu().numpy(), s2.grad.cpu().numpy(), 1e-4, "fft_conv d/d signal")
+    assert_close_rel(ker.grad.cpu().numpy(), k2.grad.cpu().numpy(), 1e-4, "fft_conv d/d kernel")
+    layer = FFTConv2d(1, 1, 3, padding=1).cuda()
+    layer(torch.randn(2, 1, 8, 8, device="cuda")).sum().backward()
+    assert layer.weight.grad is not None and layer.bias.grad is not None and float(layer.weight.grad.abs().sum()) > 0
+    # differentiate(): the manual spectral form keeps its graph too
+    x = torch.randn(2, 6, 8, 10, device="cuda", requires_grad=True)
+    o["D_x"].differentiate(x, correlation=True).sum().backward()
+    assert x.grad is not None and float(x.grad.abs().sum()) > 0

@@ -235,6 +235,19 @@ def test_calibrate_rank_and_level_match_numpy_formula():
                     calibrate_rank(n, n, alpha)
                 continue
             assert calibrate_rank(n, n, alpha) == want
+    # n != rows (the scripts pass len(other_array)): NumPy evaluates the index in the dtype of the score
+    # array; both dtypes are reproduced (rows=14, n=13, alpha=0.5 -> 8 in float32, 7 in float64)
+    assert calibrate_rank(14, 13, 0.5, np.float32) == 8 and calibrate_rank(14, 13, 0.5, np.float64) == 7
+    rng = np.random.default_rng(0)
+    for rows in list(range(2, 40)) + [100, 255, 256, 257, 1000]:
+        for n in {rows, rows - 1, rows + 1, rows + 7, 2 * rows}:
+            for alpha in np.arange(0.05, 0.96, 0.05):
+                q = calibrate_level(n, alpha) if n >= 1 else 2.0
+                if not 0 <= q <= 1:
+                    continue
+                for dt in (np.float32, np.float64):
+                    x = rng.permutation(rows).astype(dt)
+                    assert int(np.quantile(x, q, method="higher")) == calibrate_rank(rows, n, alpha, dt), (rows, n, alpha, dt)
 
 
 def test_axis_canonicalisation_of_permuted_views():
