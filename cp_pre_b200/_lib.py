@@ -84,6 +84,7 @@ SIGNATURES = {
     "cppre_owner_select": (C.c_int, [_P, C.c_int32, C.c_int32, _I64, _I64, C.c_int32, C.c_int32, _I64,
                                      C.POINTER(C.c_void_p), C.c_int32, _P, _P, C.c_int32, _P]),
     "cppre_radix_hist": (C.c_int, [_P, _I64, C.c_uint32, C.c_uint32, C.c_int32, _P, _P]),
+    "cppre_radix_select": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "cppre_radix_select_begin": (C.c_int, [_P, _P, _I64, _P]),
     "cppre_radix_select_hist": (C.c_int, [_P, _I64, _P, C.c_int32, _P, _P]),
     "cppre_radix_select_pick": (C.c_int, [_P, _P, C.c_int32, _P, _P]),

@@ -41,22 +41,24 @@ bool vec4_ok(int64_t cells, std::initializer_list<const void*> ptrs, std::initia
 // ------------------------------------------------------------------------------------------
 // FINAL: std (+ eps) and 1/std are written straight away (single-GPU modulation: one launch, no
 // fp64 intermediates in HBM); otherwise (mean, M2) for the cross-rank merge.
-template <int V, bool FINAL>
+// SPLIT: sample-lanes per cell.  1 = one thread streams the whole column.  8 = a block is 32 cell-lanes x
+// 8 warps, warp w takes samples w, w+8, ... and the eight partial sums meet in shared memory: for grids
+// with few cells (1-D Burgers: 102 400 cells = 100 blocks of the plain form on 148 SMs, 0.54 ms for
+// 0.84 GB) this is what fills the machine.
+template <int V, bool FINAL, int SPLIT>
 __global__ void __launch_bounds__(kThreads)
 cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
                     int64_t n, int64_t cells, double* __restrict__ mean, double* __restrict__ m2,
                     float add_eps, float* __restrict__ sd, float* __restrict__ inv) {
-    const int64_t c = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * V;
-    if (c >= cells) return;
+    static_assert(SPLIT == 1 || SPLIT * 32 == kThreads, "SPLIT lanes are the warps of a block");
+    __shared__ double part[SPLIT == 1 ? 1 : 2 * SPLIT * 32 * V];
+    const int lane = threadIdx.x & 31, w = SPLIT == 1 ? 0 : threadIdx.x >> 5;
+    const int64_t c = SPLIT == 1 ? ((int64_t)blockIdx.x * kThreads + threadIdx.x) * V
+                                 : ((int64_t)blockIdx.x * 32 + lane) * V;
+    const bool live = c < cells;
+    if (SPLIT == 1 && !live) return;
     const float* pa = a + c;
     const float* pb = b ? b + c : nullptr;
-    if (n == 0) {
-        if constexpr (!FINAL) {
-#pragma unroll
-            for (int e = 0; e < V; ++e) { mean[c + e] = 0.0; m2[c + e] = 0.0; }
-        }
-        return;
-    }
     // shifted sums in fp64: d = x - x_0, so sum(d^2) - sum(d)^2/n does not cancel unless the
     // column mean is > 1e6 standard deviations away from its first sample
     auto sample = [&](int64_t i, float (&x)[V]) {
@@ -69,36 +71,60 @@ cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __rest
         }
     };
     float x0[V];
-    sample(0, x0);
     double s1[V], s2[V];
 #pragma unroll
-    for (int e = 0; e < V; ++e) { s1[e] = 0.0; s2[e] = 0.0; }
-    int64_t i = 0;
-    for (; i + 4 <= n; i += 4) {
-        float x[4][V];
+    for (int e = 0; e < V; ++e) { x0[e] = 0.0f; s1[e] = 0.0; s2[e] = 0.0; }
+    if (live && n > 0) {
+        sample(0, x0);
+        int64_t i = w;
+        for (; i + 3 * SPLIT < n; i += 4 * SPLIT) {
+            float x[4][V];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) sample(i + u, x[u]);
+            for (int u = 0; u < 4; ++u) sample(i + u * SPLIT, x[u]);
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    const double d = (double)x[u][e] - (double)x0[e];
+                    s1[e] += d;
+                    s2[e] = fma(d, d, s2[e]);
+                }
+        }
+        for (; i < n; i += SPLIT) {
+            float x[V];
+            sample(i, x);
 #pragma unroll
             for (int e = 0; e < V; ++e) {
-                const double d = (double)x[u][e] - (double)x0[e];
+                const double d = (double)x[e] - (double)x0[e];
                 s1[e] += d;
                 s2[e] = fma(d, d, s2[e]);
             }
+        }
     }
-    for (; i < n; ++i) {
-        float x[V];
-        sample(i, x);
+    if constexpr (SPLIT > 1) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            const double d = (double)x[e] - (double)x0[e];
-            s1[e] += d;
-            s2[e] = fma(d, d, s2[e]);
+            part[((0 * SPLIT + w) * 32 + lane) * V + e] = s1[e];
+            part[((1 * SPLIT + w) * 32 + lane) * V + e] = s2[e];
+        }
+        __syncthreads();
+        if (w != 0 || !live) return;
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            s1[e] = 0.0;
+            s2[e] = 0.0;
+            for (int q = 0; q < SPLIT; ++q) {
+                s1[e] += part[((0 * SPLIT + q) * 32 + lane) * V + e];
+                s2[e] += part[((1 * SPLIT + q) * 32 + lane) * V + e];
+            }
         }
     }
 #pragma unroll
     for (int e = 0; e < V; ++e) {
+        if (n == 0) {
+            if constexpr (!FINAL) { mean[c + e] = 0.0; m2[c + e] = 0.0; }
+            continue;
+        }
         double v = s2[e] - s1[e] * s1[e] / (double)n;
         v = v > 0.0 ? v : (v == v ? 0.0 : v);           // clamp round-off negatives, keep NaN
         if constexpr (FINAL) {                          // same arithmetic as cell_std_kernel
@@ -112,6 +138,27 @@ cell_moments_kernel(const float* __restrict__ a, int64_t as, const float* __rest
     }
 }
 
+template <bool FINAL>
+int launch_moments(const float* d_a, int64_t as, const float* d_b, int64_t bs, int64_t n, int64_t cells, double* d_mean,
+                   double* d_m2, float add_eps, float* d_std, float* d_inv, cudaStream_t st) {
+    const bool v4 = vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0});
+    const int64_t items = v4 ? cells / 4 : cells;
+    // few cells and a long sample axis: spread each column over the 8 warps of a block
+    const bool split = items < (int64_t)148 * 2048 / 2 && n >= 64;
+    const int64_t blocks = split ? (items + 31) / 32 : (items + kThreads - 1) / kThreads;
+    CPPRE_REQUIRE(blocks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+#define CPPRE_MOMENTS(V, SP) \
+    cell_moments_kernel<V, FINAL, SP><<<(unsigned)blocks, kThreads, 0, st>>>(d_a, as, d_b, bs, n, cells, d_mean, d_m2, \
+                                                                            add_eps, d_std, d_inv)
+    if (v4 && split) CPPRE_MOMENTS(4, 8);
+    else if (v4) CPPRE_MOMENTS(4, 1);
+    else if (split) CPPRE_MOMENTS(1, 8);
+    else CPPRE_MOMENTS(1, 1);
+#undef CPPRE_MOMENTS
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
 __global__ void __launch_bounds__(kThreads)
 cell_std_kernel(const double* __restrict__ m2, double count, float add_eps, int64_t cells,
                 float* __restrict__ sd, float* __restrict__ inv) {
@@ -122,35 +169,64 @@ cell_std_kernel(const double* __restrict__ m2, double count, float add_eps, int6
     if (inv) inv[c] = __fdiv_rn(1.0f, v);
 }
 
-// scores[i] = max_c |a-b| / mod  -- `chunks` blocks per sample, V cells per thread per trip
-template <int V>
+// scores[i] = max_c |a-b| / mod.  A block owns one cell chunk and S consecutive samples: the modulation of
+// a cell is loaded (and its reciprocal approximated) once and used for S samples, which also puts S
+// independent load streams in flight per thread.
+// Exact IEEE quotients at a fraction of their cost: only the MAXIMUM quotient of a sample is wanted, so a
+// cell is screened with q~ = |x| * rcp(mod) (one FMUL; relative error < 2^-21 incl. the MUFU.RCP error) and
+// the correctly rounded division runs only where q~ reaches the running exact maximum less a 2^-19 guard --
+// any cell that is skipped has an exact quotient strictly below the maximum already found.  Comparisons are
+// written so that NaN (in x or mod) takes the exact path and wins the unsigned max, like np.max.
+template <int V, int S>
 __global__ void __launch_bounds__(kThreads)
 joint_score_kernel(const float* __restrict__ a, int64_t as, const float* __restrict__ b, int64_t bs,
-                   const float* __restrict__ mod, int64_t cells, int32_t chunks, float* scores) {
-    const int64_t i = blockIdx.x / chunks;
+                   const float* __restrict__ mod, int64_t n, int64_t cells, int32_t chunks, float* scores) {
+    const int64_t i0 = (int64_t)(blockIdx.x / chunks) * S;
     const int chunk = blockIdx.x % chunks;
-    uint32_t m = 0u;
+    uint32_t m[S];
+    float thr[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) { m[s] = 0u; thr[s] = 0.0f; }
     const int64_t step = (int64_t)chunks * kThreads * V;
-#pragma unroll 4
     for (int64_t c = ((int64_t)chunk * kThreads + threadIdx.x) * V; c < cells; c += step) {
-        float x[V], w[V];
-        ldv<V>(a + i * as + c, x);
+        float w[V], r[V], x[S][V];
         ldv<V>(mod + c, w);
-        if (b) {
-            float y[V];
-            ldv<V>(b + i * bs + c, y);
 #pragma unroll
-            for (int e = 0; e < V; ++e) x[e] = __fsub_rn(x[e], y[e]);
+        for (int s = 0; s < S; ++s) {
+            // rows past the batch re-read the last sample (their maxima are never written)
+            const int64_t i = i0 + s < n ? i0 + s : n - 1;
+            ldv<V>(a + i * as + c, x[s]);
+            if (b) {
+                float y[V];
+                ldv<V>(b + i * bs + c, y);
+#pragma unroll
+                for (int e = 0; e < V; ++e) x[s][e] = __fsub_rn(x[s][e], y[e]);
+            }
         }
 #pragma unroll
-        for (int e = 0; e < V; ++e) {
-            // |x|/mod is >= 0 or NaN for mod > 0; fabsf clears a sign a negative mod would give
-            const float v = __fdiv_rn(fabsf(x[e]), w[e]);
-            m = max(m, score_bits(fabsf(v)));
-        }
+        for (int e = 0; e < V; ++e) asm("rcp.approx.f32 %0, %1;" : "=f"(r[e]) : "f"(w[e]));
+#pragma unroll
+        for (int s = 0; s < S; ++s)
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const float ax = fabsf(x[s][e]);
+                if (!(ax * r[e] < thr[s])) {           // near or above the running maximum, or NaN: exact quotient
+                    // |x|/mod is >= 0 or NaN for mod > 0; fabsf clears a sign a negative mod would give
+                    const uint32_t q = score_bits(fabsf(__fdiv_rn(ax, w[e])));
+                    if (q > m[s]) {
+                        m[s] = q;
+                        // 1 - 2^-19; the relative-error argument needs normal numbers: a maximum below
+                        // 1e-30 keeps the threshold at 0, i.e. every cell takes the exact path
+                        thr[s] = __uint_as_float(q) >= 1e-30f ? __uint_as_float(q) * 0.999998093f : 0.0f;
+                    }
+                }
+            }
     }
-    m = __reduce_max_sync(0xffffffffu, m);
-    if ((threadIdx.x & 31) == 0 && m) atomicMax(reinterpret_cast<unsigned int*>(scores) + i, m);
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const uint32_t v = __reduce_max_sync(0xffffffffu, m[s]);
+        if ((threadIdx.x & 31) == 0 && v && i0 + s < n) atomicMax(reinterpret_cast<unsigned int*>(scores) + i0 + s, v);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -777,14 +853,38 @@ window_exchange_kernel(const float* __restrict__ x, int64_t xs, int32_t n, int64
         if (at < (uint32_t)overflow_cap) overflow_cells[at] = (int32_t)c;
         inside = (uint32_t)W;
     }
+    // Dense candidate rows.  The 32 candidate lists of a warp (= one 32-cell tile of the owner) are packed
+    // into ONE stream, slot-major: for s = 0, 1, ... the lanes whose list is longer than s, in lane
+    // order.  The owner rebuilds the same order from the 32 list lengths in the header row, so no index
+    // travels.  Packing is done in place in the warp's own 32 columns of the slot array (a write never
+    // lands beyond what the warp has already read: position <= 32*s + lane), and the tile's block
+    //     [header row | ceil(sum(inside) / 32) dense rows]  of 128-byte lines
+    // goes to the owner as whole lines only.  On |N(0,1)| scores at 8 GPUs that is 1 + 14/32 x 32 = ~15
+    // words per cell instead of 1 + the longest list of the warp (~29): half the NVLink bytes.
+    const int lane = tid & 31, wbase = tid & ~31;
+    const uint32_t lt = (1u << lane) - 1u;
     const uint32_t rows = __reduce_max_sync(0xffffffffu, inside);
-    if (!live) return;
-    float* dst = reinterpret_cast<float*>(peers.base[c / slab]) + (int64_t)peers.me * (W + 1) * slab + c % slab;
-    dst[0] = __uint_as_float(pack_header(above, inside, open));
-    // every lane stores every row up to the warp's longest list (its own rows beyond `inside` are
-    // don't-care words the owner never reads): a full warp row is four whole 32-byte sectors,
-    // which is what NVLink moves efficiently -- lane-predicated stores cost 2x here at 8 GPUs
-    for (uint32_t s = 0; s < rows; ++s) dst[(int64_t)(s + 1) * slab] = slots[s * T + tid];
+    uint32_t total = 0u;
+    for (uint32_t s = 0; s < rows; ++s) {
+        const bool act = s < inside;
+        const uint32_t bal = __ballot_sync(0xffffffffu, act);
+        const float v = act ? slots[s * T + tid] : 0.0f;
+        __syncwarp();
+        if (act) {
+            const uint32_t pos = total + __popc(bal & lt);
+            slots[(pos >> 5) * T + wbase + (pos & 31u)] = v;
+        }
+        total += __popc(bal);
+        __syncwarp();
+    }
+    const int64_t c0 = c - lane;                     // first cell of this warp's tile
+    if (c0 >= cells) return;                         // warp-uniform
+    const int64_t tiles_per_slab = slab >> 5;
+    float* dst = reinterpret_cast<float*>(peers.base[c0 / slab]) +
+                 ((int64_t)peers.me * tiles_per_slab + (c0 % slab) / 32) * (int64_t)(W + 1) * 32 + lane;
+    dst[0] = __uint_as_float(live ? pack_header(above, inside, open) : 0u);
+    const uint32_t dense_rows = (total + 31u) >> 5;
+    for (uint32_t r = 0; r < dense_rows; ++r) dst[(r + 1) * 32] = slots[r * T + tid];
 }
 
 // Owner side.  recv = [w][1 + W][slab]: row 0 of block r holds rank r's headers, rows 1.. its
@@ -812,30 +912,39 @@ owner_select_kernel(const float* recv, int32_t w, int32_t W, int64_t slab, int64
     const int64_t c0 = (int64_t)blockIdx.x * TC;
     if (tid < TC) { colcount[tid] = 0u; above[tid] = 0u; flag[tid] = 0u; }
     __syncthreads();
-    // Warp `wid` takes the lists of ranks wid, wid + WARPS, ...: lane = cell.  Header first, then
-    // as many candidate rows as the longest list among the 32 cells.  The tile is not cleared:
-    // the read-out below masks everything at or above the column's count to the padding key.
-    const int64_t block = (int64_t)(W + 1) * slab;
+    // Warp `wid` takes the blocks of ranks wid, wid + WARPS, ...: lane = cell.  A block is the header row
+    // (32 words) followed by the dense candidate stream of window_exchange_kernel; the slot-major order is
+    // rebuilt from the 32 list lengths (ballot + popc), so lane `col` finds its s-th candidate at stream
+    // position  sum_{s' < s} #{lists longer than s'} + #{lanes below col with a list longer than s}.
+    // The tile is not cleared: the read-out below masks everything at or above the column's count.
+    const int64_t tiles_per_slab = slab >> 5;
     {
         const int col = lane;
         const bool live = c0 + col < cells;
+        const uint32_t lt = (1u << lane) - 1u;
         for (int r = wid; r < w; r += WARPS) {
-            const float* src = recv + (int64_t)r * block + c0 + col;
+            const float* blk = recv + ((int64_t)r * tiles_per_slab + blockIdx.x) * (int64_t)(W + 1) * 32;
             uint32_t l = 0u;
             if (live) {
-                const uint32_t h = __float_as_uint(__ldcg(src));
+                const uint32_t h = __float_as_uint(__ldcg(blk + col));
                 atomicAdd(&above[col], h & 0xffffffu);
                 if (h >> 31) flag[col] = 1u;
                 l = (h >> 24) & 0x7fu;
             }
             const uint32_t rows = __reduce_max_sync(0xffffffffu, l);
-            // eight row loads in flight per lane before any is consumed: one load per trip made the
-            // fill a chain of L2 round trips (the whole kernel was latency-bound, 26 % issue-active)
+            const float* stream = blk + 32;
+            uint32_t total = 0u;
+            // eight loads in flight per lane before any is consumed: one load per trip made the fill a
+            // chain of L2 round trips (the whole kernel was latency-bound, 26 % issue-active)
             for (uint32_t sl0 = 0; sl0 < rows; sl0 += 8) {
                 uint32_t bits[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    bits[u] = sl0 + u < l ? __float_as_uint(__ldcg(src + (int64_t)(1 + sl0 + u) * slab)) : 0u;
+                for (int u = 0; u < 8; ++u) {
+                    const bool act = sl0 + u < l;
+                    const uint32_t bal = __ballot_sync(0xffffffffu, act);
+                    bits[u] = act ? __float_as_uint(__ldcg(stream + total + __popc(bal & lt))) : 0u;
+                    total += __popc(bal);
+                }
 #pragma unroll
                 for (int u = 0; u < 8; ++u)
                     if (sl0 + u < l) {
@@ -1016,6 +1125,46 @@ radix_hist_dev_kernel(const float* __restrict__ x, int64_t n, const uint32_t* __
     if (threadIdx.x == 0 && sh[256]) atomicAdd(hist + 256, sh[256]);
 }
 
+// The whole select in ONE launch when the scores live on one GPU: a single 1024-thread CTA runs the four
+// passes back to back (the array is read from L2 after the first pass), histogram and state in shared memory.
+__global__ void __launch_bounds__(1024)
+radix_select_block_kernel(const float* __restrict__ x, int64_t n, uint32_t k, float* __restrict__ out) {
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t sel[3];          // prefix, remaining rank, flags (1: NaN seen, 2: rank out of range)
+    const int t = threadIdx.x;
+    if (t < 3) sel[t] = t == 1 ? k : 0u;
+    uint32_t mask = 0u;
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        if (t < 256) hist[t] = 0u;
+        __syncthreads();
+        const uint32_t prefix = sel[0];
+        bool nan = false;
+        for (int64_t i = t; i < n; i += 1024) {
+            const uint32_t bits = __float_as_uint(__ldg(x + i));
+            nan |= (bits & 0x7fffffffu) > 0x7f800000u;
+            const uint32_t key = float_to_key(bits);
+            if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        }
+        if (pass == 0 && nan) sel[2] = 1u;
+        __syncthreads();
+        if (t == 0) {                    // 256 counters: a serial scan costs less than another barrier round
+            uint32_t kk = sel[1], acc = 0u;
+            int d = 0;
+            for (; d < 256; ++d) {
+                if (kk < acc + hist[d]) break;
+                acc += hist[d];
+            }
+            if (d == 256) { sel[2] |= 2u; d = 255; }
+            sel[0] = prefix | ((uint32_t)d << shift);
+            sel[1] = kk - acc;
+        }
+        mask |= 255u << shift;
+        __syncthreads();
+    }
+    if (t == 0) *out = sel[2] ? __uint_as_float(0x7fc00000u) : __uint_as_float(key_to_float_bits(sel[0]));
+}
+
 __global__ void __launch_bounds__(kThreads)
 radix_begin_kernel(uint32_t* __restrict__ state, uint32_t* __restrict__ hist, uint32_t k) {
     const int i = blockIdx.x * kThreads + threadIdx.x;
@@ -1125,17 +1274,7 @@ int cppre_cell_moments(const float* d_a, int64_t as, const float* d_b, int64_t b
     CPPRE_REQUIRE(n >= 0 && cells >= 0, CPPRE_ERR_BAD_ARG, "negative size");
     if (cells == 0) return CPPRE_OK;
     CPPRE_REQUIRE(d_mean && d_m2 && (d_a || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
-    if (vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0})) {
-        const int64_t blocks = (cells / 4 + kThreads - 1) / kThreads;
-        cell_moments_kernel<4, false><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
-            d_a, as, d_b, bs, n, cells, d_mean, d_m2, 0.0f, nullptr, nullptr);
-    } else {
-        const int64_t blocks = (cells + kThreads - 1) / kThreads;
-        cell_moments_kernel<1, false><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
-            d_a, as, d_b, bs, n, cells, d_mean, d_m2, 0.0f, nullptr, nullptr);
-    }
-    CPPRE_CHECK_LAUNCH();
-    return CPPRE_OK;
+    return launch_moments<false>(d_a, as, d_b, bs, n, cells, d_mean, d_m2, 0.0f, nullptr, nullptr, (cudaStream_t)stream);
 }
 
 int cppre_cell_modulation(const float* d_a, int64_t as, const float* d_b, int64_t bs, int64_t n, int64_t cells,
@@ -1143,17 +1282,7 @@ int cppre_cell_modulation(const float* d_a, int64_t as, const float* d_b, int64_
     CPPRE_REQUIRE(n >= 1 && cells >= 0, CPPRE_ERR_BAD_ARG, "bad size (n=%lld)", (long long)n);
     if (cells == 0) return CPPRE_OK;
     CPPRE_REQUIRE(d_a && d_std, CPPRE_ERR_BAD_ARG, "null pointer");
-    if (vec4_ok(cells, {d_a, d_b}, {as, d_b ? bs : 0})) {
-        const int64_t blocks = (cells / 4 + kThreads - 1) / kThreads;
-        cell_moments_kernel<4, true><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
-            d_a, as, d_b, bs, n, cells, nullptr, nullptr, add_eps, d_std, d_inv);
-    } else {
-        const int64_t blocks = (cells + kThreads - 1) / kThreads;
-        cell_moments_kernel<1, true><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
-            d_a, as, d_b, bs, n, cells, nullptr, nullptr, add_eps, d_std, d_inv);
-    }
-    CPPRE_CHECK_LAUNCH();
-    return CPPRE_OK;
+    return launch_moments<true>(d_a, as, d_b, bs, n, cells, nullptr, nullptr, add_eps, d_std, d_inv, (cudaStream_t)stream);
 }
 
 int cppre_cell_std(const double* d_m2, double count, float add_eps, int64_t cells, float* d_std,
@@ -1176,14 +1305,16 @@ int cppre_joint_score(const float* d_a, int64_t as, const float* d_b, int64_t bs
     cudaStream_t st = (cudaStream_t)stream;
     CPPRE_CHECK_CUDA(cudaMemsetAsync(d_scores, 0, sizeof(float) * (size_t)n, st));
     if (cells == 0) return CPPRE_OK;
-    const int chunks = chunks_for(n, cells);
-    CPPRE_REQUIRE(n * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
+    constexpr int S = 4;                                   // samples per block
+    const int64_t groups = (n + S - 1) / S;
+    const int chunks = chunks_for(groups, cells);
+    CPPRE_REQUIRE(groups * chunks < (int64_t(1) << 31), CPPRE_ERR_UNSUPPORTED, "grid too large");
     if (vec4_ok(cells, {d_a, d_b, d_mod}, {as, d_b ? bs : 0}))
-        joint_score_kernel<4><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
-                                                                          d_scores);
+        joint_score_kernel<4, S><<<(unsigned)(groups * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, n, cells,
+                                                                                  chunks, d_scores);
     else
-        joint_score_kernel<1><<<(unsigned)(n * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, cells, chunks,
-                                                                          d_scores);
+        joint_score_kernel<1, S><<<(unsigned)(groups * chunks), kThreads, 0, st>>>(d_a, as, d_b, bs, d_mod, n, cells,
+                                                                                  chunks, d_scores);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }
@@ -1331,6 +1462,8 @@ int cppre_window_exchange(const float* d_scores, int64_t row_stride, int64_t n, 
                   CPPRE_ERR_BAD_ARG, "bad size (n=%lld cells=%lld slots=%d slab=%lld)", (long long)n,
                   (long long)cells, slots, (long long)slab);
     CPPRE_REQUIRE((cells + slab - 1) / slab <= n_peers, CPPRE_ERR_BAD_ARG, "more cell slabs than peers");
+    CPPRE_REQUIRE(slab % 32 == 0, CPPRE_ERR_BAD_ARG, "slab must be a multiple of 32 cells (one owner tile per warp), got %lld",
+                  (long long)slab);
     CPPRE_REQUIRE(cells < (int64_t(1) << 31) && overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells),
                   CPPRE_ERR_BAD_ARG, "bad overflow list");
     CPPRE_REQUIRE(n < (int64_t(1) << 24), CPPRE_ERR_UNSUPPORTED, "n too large for the packed count");
@@ -1358,8 +1491,8 @@ int cppre_owner_select(const float* d_recv, int32_t n_ranks, int32_t slots, int6
     PeerPtrs qp;
     const int rc0 = fill_peers(&qp, h_peer_q, n_peers, 0);
     if (rc0 != CPPRE_OK) return rc0;
-    CPPRE_REQUIRE(n_ranks >= 1 && n_ranks <= 16 && slots >= 1 && slots <= 96 && slab >= 1 && cells <= slab,
-                  CPPRE_ERR_BAD_ARG, "bad size");
+    CPPRE_REQUIRE(n_ranks >= 1 && n_ranks <= 16 && slots >= 1 && slots <= 96 && slab >= 1 && cells <= slab &&
+                      slab % 32 == 0, CPPRE_ERR_BAD_ARG, "bad size (slab must be a multiple of 32)");
     CPPRE_REQUIRE(overflow_cap >= 0 && (overflow_cap == 0 || d_overflow_cells), CPPRE_ERR_BAD_ARG, "bad overflow list");
     if (cells <= 0) return CPPRE_OK;
     CPPRE_REQUIRE(d_recv && d_overflow, CPPRE_ERR_BAD_ARG, "null pointer");
@@ -1408,6 +1541,14 @@ int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask
     int64_t blocks = (n + kThreads - 1) / kThreads;
     if (blocks > 148 * 8) blocks = 148 * 8;
     radix_hist_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(d_x, n, prefix, mask, shift, d_hist);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_radix_select(const float* d_x, int64_t n, int64_t k, float* d_out, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && k >= 0 && k < (int64_t(1) << 32), CPPRE_ERR_BAD_ARG, "bad argument");
+    CPPRE_REQUIRE(d_out && (d_x || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
+    radix_select_block_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(d_x, n, (uint32_t)k, d_out);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

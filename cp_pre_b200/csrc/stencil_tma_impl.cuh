@@ -46,6 +46,7 @@ constexpr int kWarps = 8;           // thread rows per CTA
 constexpr int kThreads = kTPR * kWarps;
 constexpr int kTW = 4 * kTPR;       // tile width in cells (128)
 constexpr int kMaxStages = 8;
+constexpr int kDefaultL2Hints = 0;   // see StarParams::l2_hints; CPPRE_TMA_L2_HINTS overrides
 // Field element type of this translation unit: fp32, or bf16 (CPPRE_TMA_BF16: the bf16-input
 // mode -- tiles are staged as bf16, halving the field bytes read from HBM, and widened to fp32
 // on the way into registers; all arithmetic and every output stay fp32).
@@ -71,6 +72,7 @@ struct alignas(64) StarParams {
     int32_t col_tiles, row_tiles;
     int32_t stages;
     uint32_t buf_bytes;   // bytes of one (stage, field) tile, 128-aligned
+    int32_t l2_hints;     // bit 0: field tiles evict_first, bit 1: weight tile evict_last
 };
 
 template <int N, class F>
@@ -110,6 +112,34 @@ __device__ __forceinline__ void bar_arrive(uint32_t id, uint32_t threads) {
 }
 __device__ __forceinline__ void bar_sync(uint32_t id, uint32_t threads) {
     asm volatile("barrier.cta.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+// L2 eviction-priority hints for the TMA loads: the field tiles are streamed once (evict_first), the
+// per-cell weight tile (qhat / modulation, 13-26 MB) is re-read by every sample and should stay (evict_last)
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void tma_load_3d_hint(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                                 int c2, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(pol)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_hint(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                                 int c2, int c3, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(pol)
+        : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
     asm volatile(
@@ -295,18 +325,23 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
     __syncthreads();
 
     const int NPL = p.N2;
+    const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
+    const bool hint_f = (p.l2_hints & 1) != 0, hint_w = (p.l2_hints & 2) != 0;
     auto issue = [&](int plane, int stage) {
         const uint32_t bar = bars + 8u * stage;
         mbar_expect_tx(bar, BOX_BYTES * NF + WBUF_BYTES);
-        if constexpr (WTMA)
-            tma_load_3d(base + (uint32_t)stage * STAGE_BYTES + NF * BUF_BYTES, &p.wmap, bar, col0, row0, plane);
+        if constexpr (WTMA) {
+            const uint32_t wdst = base + (uint32_t)stage * STAGE_BYTES + NF * BUF_BYTES;
+            if (hint_w) tma_load_3d_hint(wdst, &p.wmap, bar, col0, row0, plane, pol_last);
+            else tma_load_3d(wdst, &p.wmap, bar, col0, row0, plane);
+        }
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
             const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * BUF_BYTES;
-            if constexpr (BATCH_ROWS)   // map dims (N0, N2, B, 1): tile rows are samples
-                tma_load_4d(dst, &p.map[f], bar, col0 - kHP, plane, row0, 0);
-            else                        // map dims (N0, N1, N2, B)
-                tma_load_4d(dst, &p.map[f], bar, col0 - kHP, row0 - HALO, plane, outer);
+            // map dims (N0, N2, B, 1) with samples as tile rows (batch-rows mode) or (N0, N1, N2, B)
+            const int c1 = BATCH_ROWS ? plane : row0 - HALO, c2 = BATCH_ROWS ? row0 : plane, c3 = BATCH_ROWS ? 0 : outer;
+            if (hint_f) tma_load_4d_hint(dst, &p.map[f], bar, col0 - kHP, c1, c2, c3, pol_first);
+            else tma_load_4d(dst, &p.map[f], bar, col0 - kHP, c1, c2, c3);
         }
     };
     if (tid == 0) {
@@ -714,11 +749,14 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     sp.buf_bytes = ((uint32_t)(SR * kTWP) * kES + 127u) & ~127u;
 
     // ring depth: as deep as fits while leaving room for >= 2 CTAs per SM
-    static int env_stages = -1;
+    static int env_stages = -1, env_hints = -1;
     if (env_stages < 0) {
         const char* s = getenv("CPPRE_TMA_STAGES");
         env_stages = s ? atoi(s) : 0;
+        const char* h = getenv("CPPRE_TMA_L2_HINTS");       // bit 0: fields evict_first, bit 1: weight evict_last
+        env_hints = h ? atoi(h) : kDefaultL2Hints;
     }
+    sp.l2_hints = env_hints;
     int stages = env_stages > 0 ? env_stages : 4;
     const size_t per_stage = (size_t)NF * sp.buf_bytes + (WTMA ? (size_t)TX * kTW * sizeof(float) : 0);
     while (stages > 2 && stages * per_stage + 256 > 112 * 1024) --stages;      // 2 x (112 KB + 1 KB) <= 228 KB per SM

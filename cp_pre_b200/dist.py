@@ -250,6 +250,12 @@ def pending_overflow() -> int:
     return total
 
 
+def fused_slab(cells: int, world: int) -> int:
+    """Cells owned by one rank in the fused exchange: ceil(cells / world) rounded up to whole 32-cell
+    tiles (a warp of the sender packs the candidate lists of exactly one owner tile)."""
+    return (-(-cells // world) + 31) // 32 * 32
+
+
 def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots: int, defer: bool = False):
     """K3x: `_window_quantile` with every exchange inside the kernels (include/cppre.h).  Per
     quantile: K3t local order statistic -> keys stored into every peer -> barrier -> window scan,
@@ -265,9 +271,10 @@ def _fused_window_quantile(scores: torch.Tensor, rank_k: int, group, kern, slots
     dev = scores.device
     kt = w * n - int(rank_k)
     J = -(-kt // w)
-    slab = (cells + w - 1) // w
+    slab = fused_slab(cells, w)
     cells_pad = (slab * w + 3) // 4 * 4
-    recv, recv_ptrs = _symm_buffer("recvx", (w, 1 + slots, slab), torch.float32, dev, group)
+    # every rank's receive buffer: per sender and 32-cell tile one block [header row | dense candidate rows]
+    recv, recv_ptrs = _symm_buffer("recvx", (w, slab // 32, 1 + slots, 32), torch.float32, dev, group)
     qbuf, q_ptrs = _symm_buffer("q", (cells_pad,), torch.float32, dev, group)
     flag = torch.zeros(1, dtype=torch.int32, device=dev)
     over = torch.zeros(1, dtype=torch.int32, device=dev)

@@ -415,7 +415,8 @@ def window_exchange(scores: torch.Tensor, keys: torch.Tensor, slots: int, slab: 
                     key_mode: int = 0):
     """K3x-2: scores [n, cells...]; keys = this rank's [world, cells_pad] key buffer (int32 storage of uint32
     keys; key_mode 0) or the MAX-all-reduced [2, cells_pad] pair [~min, max] of signed keys (key_mode 1).
-    Headers + candidates go straight into the owners' receive buffers [world, 1+slots, slab]."""
+    Headers + candidates go straight into the owners' receive buffers [world, slab/32, 1+slots, 32]
+    (slab a multiple of 32: dist.fused_slab)."""
     lib = L.load()
     fs, rs = _rows(scores)
     n, cells = fs.shape
@@ -428,10 +429,13 @@ def window_exchange(scores: torch.Tensor, keys: torch.Tensor, slots: int, slab: 
 
 def owner_select(recv: torch.Tensor, cells: int, kt: int, network: int, cell_offset: int, peer_q: Sequence[int],
                  overflow: torch.Tensor, overflow_cells: Optional[torch.Tensor] = None):
-    """K3x-3: recv = this rank's [world, 1+slots, slab] receive buffer; the answers of its `cells` live
-    cells are stored into every peer's q buffer at [cell_offset + c]."""
+    """K3x-3: recv = this rank's [world, slab/32, 1+slots, 32] receive buffer (per sender and 32-cell tile:
+    header row + dense candidate rows); the answers of its `cells` live cells are stored into every peer's
+    q buffer at [cell_offset + c]."""
     lib = L.load()
-    w, rows, slab = recv.shape
+    w, tiles, rows, lanes = recv.shape
+    assert lanes == 32
+    slab = tiles * 32
     cap = 0 if overflow_cells is None else overflow_cells.numel()
     with torch.cuda.device(recv.device):
         L.check(lib.cppre_owner_select(_ptr(recv), int(w), int(rows - 1), int(slab), int(cells), int(kt), int(network),
@@ -461,6 +465,10 @@ def radix_select(scores, k: int, allreduce=None) -> torch.Tensor:
     state = torch.empty(4, dtype=torch.int32, device=dev)
     hist = torch.empty(257, dtype=torch.int32, device=dev)
     out = torch.empty(1, dtype=torch.float32, device=dev)
+    if allreduce is None and len(parts) == 1 and parts[0].numel() <= (1 << 20):
+        with torch.cuda.device(dev):      # everything on this GPU: one launch, one CTA
+            L.check(lib.cppre_radix_select(_ptr(parts[0]), parts[0].numel(), int(k), _ptr(out), _stream(dev)))
+        return out
     with torch.cuda.device(dev):
         st = _stream(dev)
         L.check(lib.cppre_radix_select_begin(_ptr(state), _ptr(hist), int(k), st))

@@ -221,6 +221,9 @@ int cppre_radix_hist(const float* d_x, int64_t n, uint32_t prefix, uint32_t mask
  * cppre_epilogue_t::d_band_q.          replaces np.quantile inside calibrate() for 1-D scores
  *                                      Joint/MHD_Residuals_CP.py:399, Joint/NS_Residuals_CP.py:311 */
 int cppre_radix_select_begin(uint32_t* d_state, uint32_t* d_hist, int64_t k, void* stream);
+/* All four passes in ONE launch (one CTA; scores on one GPU, a few hundred thousand at most):
+ * *d_out = the k-th smallest (0-based) of d_x[0..n), NaN rules as above. */
+int cppre_radix_select(const float* d_x, int64_t n, int64_t k, float* d_out, void* stream);
 int cppre_radix_select_hist(const float* d_x, int64_t n, const uint32_t* d_state, int32_t pass,
                             uint32_t* d_hist, void* stream);
 int cppre_radix_select_pick(uint32_t* d_hist, uint32_t* d_state, int32_t pass, float* d_out, void* stream);

@@ -355,11 +355,11 @@ def test_fused_exchange_protocol_emulated_ranks_equals_global_quantile(world, n_
     k = O.calibrate_rank(N, N, alpha)
     kt, slots = N - k, 32
     J = -(-kt // world)
-    slab = -(-cells // world)
+    slab = D.fused_slab(cells, world)
     cells_pad = (slab * world + 3) // 4 * 4
     shards = [cuda(full[r * n_loc:(r + 1) * n_loc]) for r in range(world)]
     keys = [torch.zeros((world, cells_pad), dtype=torch.int32, device="cuda") for _ in range(world)]
-    recv = [torch.full((world, 1 + slots, slab), float("nan"), device="cuda") for _ in range(world)]   # stale garbage
+    recv = [torch.full((world, slab // 32, 1 + slots, 32), float("nan"), device="cuda") for _ in range(world)]   # stale garbage
     qbuf = [torch.full((cells_pad,), -7.0, device="cuda") for _ in range(world)]
     ov = torch.zeros(1, dtype=torch.int32, device="cuda")
     cells_ov = torch.full((256,), -1, dtype=torch.int32, device="cuda")
@@ -407,9 +407,11 @@ def test_device_radix_select_equals_sorted_order_statistic(n):
     want = np.sort(x)
     xc = cuda(x)
     for k in sorted({0, n // 3, n // 2, int(0.9 * (n - 1)), n - 1}):
-        got = ops.radix_select(xc, k)
+        got = ops.radix_select(xc, k)                                     # one launch (single-CTA form)
         assert got.shape == (1,) and got.is_cuda
         assert float(got) == float(want[k])         # == : +0.0 and -0.0 tie in np.sort's order too
+        multi = ops.radix_select(xc, k, allreduce=lambda h: None)         # four passes, state on the device
+        assert torch.equal(multi, got) or (float(multi) == 0.0 and float(got) == 0.0)
     assert np.isnan(float(ops.radix_select(xc, n)))                       # rank out of range
     if n >= 19:
         y = x.copy()

