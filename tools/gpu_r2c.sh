@@ -14,3 +14,4 @@ for w in burgers wave-joint; do
   timeout 600 python bench.py --workload $w --steps 20 --warmup 3 --no-e2e --no-cpu > $O/${TAG}_bench_$w.json 2> $O/${TAG}_bench_$w.err; echo "bench $w exit $?"
 done
 ls $O | grep ${TAG} | head -40
+timeout 300 python tools/dropin_script_bench.py 32 > $O/${TAG}_dropin.json 2> $O/${TAG}_dropin.err; cat $O/${TAG}_dropin.json
