@@ -28,7 +28,7 @@ PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS
 EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1
 FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16 = 1, 2, 4, 8, 16
-PATH_AUTO, PATH_GENERIC, PATH_TMA = 0, 1, 2
+PATH_AUTO, PATH_GENERIC, PATH_TMA, PATH_TIN = 0, 1, 2, 3
 
 BC_DIRICHLET, BC_NEUMANN, BC_PERIODIC, BC_SYMMETRIC, BC_NONE = range(5)
 SPEC_CONJ_FIRST, SPEC_INVERSE, SPEC_CONJ_LAST = 1, 2, 4
@@ -48,7 +48,7 @@ class Epilogue(C.Structure):
     _fields_ = [("mode", C.c_int32), ("flags", C.c_int32), ("reduce", C.c_int32),
                 ("band_q", C.c_float), ("d_ref", C.c_void_p), ("ref_stride", C.c_int64 * 4),
                 ("d_weight", C.c_void_p), ("d_out", C.c_void_p), ("out_stride", C.c_int64 * 4),
-                ("d_scores", C.c_void_p), ("d_band_q", C.c_void_p)]
+                ("d_scores", C.c_void_p), ("d_band_q", C.c_void_p), ("weight_stride", C.c_int64 * 3)]
 
 
 class BC(C.Structure):
@@ -65,6 +65,8 @@ SIGNATURES = {
     "cppre_last_path": (C.c_char_p, []),
     "cppre_residual": (C.c_int, [C.POINTER(Program), C.POINTER(_I64), C.POINTER(Field),
                                  C.POINTER(Epilogue), C.c_int, _P]),
+    "cppre_residual_tin_eligible": (C.c_int, [C.POINTER(Program), C.POINTER(_I64), C.POINTER(Field),
+                                              C.POINTER(Epilogue)]),
     "cppre_residual_tma_eligible": (C.c_int, [C.POINTER(Program), C.POINTER(_I64), C.POINTER(Field),
                                               C.POINTER(Epilogue)]),
     "cppre_cell_moments": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P, _P, _P]),

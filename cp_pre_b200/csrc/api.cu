@@ -105,6 +105,18 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
     P.epi.r1 = epi->ref_stride[2];
     P.epi.r0 = epi->ref_stride[3];
     P.epi.weight = epi->d_weight;
+    {
+        const int64_t* ws = epi->weight_stride;
+        const int64_t o2 = P.g.O2, o1 = P.g.O1, o0 = P.g.O0;
+        const bool unset = ws[0] == 0 && ws[1] == 0 && ws[2] == 0;
+        auto fits = [&](int64_t a2, int64_t a1, int64_t a0) {   // strides on extent-1 axes are free
+            return (o2 <= 1 || ws[0] == a2) && (o1 <= 1 || ws[1] == a1) && (o0 <= 1 || ws[2] == a0);
+        };
+        P.weight_contig = unset || fits(o1 * o0, o0, 1);
+        P.weight_tin = !unset && fits(1, o0 * o2, o2);
+        CPPRE_REQUIRE(!epi->d_weight || P.weight_contig || P.weight_tin, CPPRE_ERR_UNSUPPORTED,
+                      "d_weight must be contiguous [O2,O1,O0] or t-innermost (strides 1, O0*O2, O2)");
+    }
     P.epi.out = epi->d_out;
     P.epi.ob = epi->out_stride[0];
     P.epi.o2 = epi->out_stride[1];
@@ -141,6 +153,13 @@ const char* cppre_last_error(void) { return t_error; }
 uint64_t cppre_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 const char* cppre_last_path(void) { return t_path; }
 
+int cppre_residual_tin_eligible(const cppre_program_t* prog, const int64_t shape[4],
+                                const cppre_field_t* fields, const cppre_epilogue_t* epi) {
+    Prepared P;
+    if (prepare(prog, shape, fields, epi, &P) != CPPRE_OK) return 0;
+    return tin_eligible(prog, P);
+}
+
 int cppre_residual_tma_eligible(const cppre_program_t* prog, const int64_t shape[4],
                                 const cppre_field_t* fields, const cppre_epilogue_t* epi) {
     Prepared P;
@@ -162,8 +181,16 @@ int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
         set_path("empty");
         return CPPRE_OK;
     }
-    CPPRE_REQUIRE(path == CPPRE_PATH_AUTO || path == CPPRE_PATH_GENERIC || path == CPPRE_PATH_TMA,
-                  CPPRE_ERR_BAD_ARG, "unknown path %d", path);
+    CPPRE_REQUIRE(path == CPPRE_PATH_AUTO || path == CPPRE_PATH_GENERIC || path == CPPRE_PATH_TMA ||
+                      path == CPPRE_PATH_TIN, CPPRE_ERR_BAD_ARG, "unknown path %d", path);
+    if (path == CPPRE_PATH_TIN || (path == CPPRE_PATH_AUTO && tin_eligible(prog, P))) {
+        CPPRE_REQUIRE(tin_eligible(prog, P), CPPRE_ERR_UNSUPPORTED,
+                      "request does not qualify for the t-innermost star kernel");
+        set_path("tin");
+        return launch_tin(prog, P, st);
+    }
+    CPPRE_REQUIRE(!P.epi.weight || P.weight_contig, CPPRE_ERR_UNSUPPORTED,
+                  "a t-innermost weight is served by the t-innermost star kernel only");
     const int ok = tma_eligible(prog, P);
     if (path == CPPRE_PATH_TMA)
         CPPRE_REQUIRE(ok, CPPRE_ERR_UNSUPPORTED, "request does not qualify for the TMA star kernel");

@@ -129,6 +129,8 @@ struct Prepared {
     float scalars[CPPRE_MAX_SCALARS];
     int kind, n_fields, n_slots;
     int in_bf16;   // CPPRE_FLAG_IN_BF16: fields[].p point to bfloat16 elements
+    int weight_tin;      // the epilogue weight is laid out [N1][N0][N2] (t-innermost), not contiguous [N2][N1][N0]
+    int weight_contig;   // ... contiguous (both can hold for degenerate extents)
 };
 int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_field_t* fields,
             const cppre_epilogue_t* epi, Prepared* out);
@@ -148,6 +150,19 @@ CPPRE_TMA_TU(store_dyn_bf16) CPPRE_TMA_TU(store_plain_bf16)
 CPPRE_TMA_TU(score_dyn_bf16) CPPRE_TMA_TU(score_w_bf16)
 CPPRE_TMA_TU(cover_dyn_bf16) CPPRE_TMA_TU(cover_w_bf16)
 #undef CPPRE_TMA_TU
+#define CPPRE_TIN_TU(sfx)                                                   \
+    int tin_eligible_##sfx(const cppre_program_t* prog, const Prepared& P); \
+    int launch_tin_##sfx(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+CPPRE_TIN_TU(store) CPPRE_TIN_TU(score) CPPRE_TIN_TU(cover)
+#undef CPPRE_TIN_TU
+inline int tin_eligible(const cppre_program_t* prog, const Prepared& P) {
+    return P.epi.mode == CPPRE_EPI_STORE ? tin_eligible_store(prog, P)
+         : P.epi.mode == CPPRE_EPI_SCORE ? tin_eligible_score(prog, P) : tin_eligible_cover(prog, P);
+}
+inline int launch_tin(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
+    return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store(prog, P, stream)
+         : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score(prog, P, stream) : launch_tin_cover(prog, P, stream);
+}
 inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
     if (P.in_bf16)
         return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store_dyn_bf16(prog, P)

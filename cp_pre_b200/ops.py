@@ -110,6 +110,77 @@ def _to_logical_order(f: torch.Tensor, perm) -> torch.Tensor:
     return f.contiguous()
 
 
+def _is_tin(t: torch.Tensor) -> bool:
+    """A logical [B,Nt,Nx,Ny] view of [B,Nx,Ny,Nt] memory: what ``pred.permute(0,1,4,2,3)[:, j]`` of an FNO
+    output is."""
+    if t.dim() != 4 or t.numel() == 0:
+        return False
+    B, N2, N1, N0 = t.shape
+    return (N2 > 1 and t.stride(1) == 1 and (N0 == 1 or t.stride(3) == N2) and (N1 == 1 or t.stride(2) == N0 * N2)
+            and (B == 1 or t.stride(0) >= N1 * N0 * N2))
+
+
+def _as_tin(t: torch.Tensor) -> torch.Tensor:
+    """The same logical [B,Nt,Nx,Ny] values stored t-innermost (a copy unless it already is)."""
+    return t if _is_tin(t) else t.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+
+
+def _residual_call(kind, fields, kernels, pads, scalars, mode, flags, reduce, ref, weight, weight_stride, path, out,
+                   band_q, query_tin=False):
+    """Fills the C structs for one cppre_residual call and makes it (or, ``query_tin``, only asks whether the
+    t-innermost kernel would take it).  ``out`` is the STORE destination or None for the reducing modes."""
+    lib = L.load()
+    f0 = fields[0]
+    B, N2, N1, N0 = (int(v) for v in f0.shape)
+    prog = L.Program()
+    prog.kind, prog.n_fields, prog.n_slots = kind, len(fields), len(kernels)
+    for s, (k, p) in enumerate(zip(kernels, pads)):
+        for d in range(3):
+            prog.ksize[s][d] = k.shape[d]
+            prog.pad[s][d] = p[d]
+        prog.h_taps[s] = k.ctypes.data
+    for i, v in enumerate(scalars):
+        prog.scalars[i] = float(v)
+    fl = (L.Field * len(fields))()
+    for i, f in enumerate(fields):
+        fl[i].d_data = f.data_ptr() if f.numel() else 0
+        for d in range(4):
+            fl[i].stride[d] = f.stride(d)
+    epi = L.Epilogue()
+    epi.mode, epi.flags, epi.reduce = mode, flags, reduce
+    dev = f0.device
+    if isinstance(band_q, torch.Tensor):
+        if band_q.numel() != 1 or band_q.dtype != torch.float32 or band_q.device != dev:
+            raise ValueError(f"band_q must be a Python float or a one-element float32 tensor on {dev}")
+        epi.d_band_q = band_q.data_ptr()
+    else:
+        epi.band_q = float(band_q)
+    if ref is not None:
+        epi.d_ref = ref.data_ptr()
+        for d in range(4):
+            epi.ref_stride[d] = ref.stride(d)
+    if weight is not None:
+        epi.d_weight = weight.data_ptr()
+        if weight_stride is not None:
+            for d in range(3):
+                epi.weight_stride[d] = int(weight_stride[d])
+    res = None
+    with torch.cuda.device(dev):
+        if mode == L.EPI_STORE:
+            epi.d_out = out.data_ptr() if out.numel() else 0
+            for d in range(4):
+                epi.out_stride[d] = out.stride(d)
+            res = out
+        else:
+            res = torch.empty((B,), dtype=torch.float32 if mode == L.EPI_SCORE else torch.int32, device=dev)
+            epi.d_scores = res.data_ptr() if B else 0
+        shape = (C.c_int64 * 4)(B, N2, N1, N0)
+        if query_tin:
+            return bool(lib.cppre_residual_tin_eligible(C.byref(prog), shape, fl, C.byref(epi)))
+        L.check(lib.cppre_residual(C.byref(prog), shape, fl, C.byref(epi), int(path), _stream(dev)))
+    return res
+
+
 def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.ndarray],
                 pads: Sequence[Sequence[int]], scalars: Sequence[float] = (), *,
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
@@ -126,7 +197,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     ``band_q`` is a Python float or a one-element float32 CUDA tensor (e.g. the device scalar
     ``radix_select`` returns): the kernel then reads q itself and nothing crosses to the host.
     """
-    lib = L.load()
+    L.load()
     require_cuda()
     f0 = fields[0]
     if any(f.shape != f0.shape for f in fields):
@@ -136,6 +207,43 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         raise RuntimeError("expected scalar type Float (fields must all be float32, or all bfloat16)")
     kernels = [np.ascontiguousarray(k, dtype=np.float32) for k in kernels]
     pads = [tuple(int(v) for v in p) for p in pads]
+    for k in kernels:
+        if k.ndim != 3:
+            raise ValueError("slot kernels must be 3-D [k2,k1,k0]")
+    if f0.dim() != 4:
+        raise ValueError("fields must be [B, N2, N1, N0]")
+    B, N2, N1, N0 = (int(v) for v in f0.shape)
+    O = [n + 2 * p - k + 1 for n, p, k in zip((N2, N1, N0), pads[0], kernels[0].shape)]
+    if min(O) < 0:
+        raise RuntimeError(f"kernel size {tuple(kernels[0].shape)} can't be greater than the padded input {(N2, N1, N0)}")
+    if ref is not None and tuple(ref.shape) != (B, *O):
+        raise ValueError(f"reference residual has shape {tuple(ref.shape)}, expected {(B, *O)}")
+    if weight is not None and tuple(weight.shape) != tuple(O):
+        raise ValueError(f"weight has shape {tuple(weight.shape)}, expected {tuple(O)}")
+    if out is not None and mode == L.EPI_STORE and (tuple(out.shape) != (B, *O) or out.dtype != torch.float32
+                                                    or out.device != f0.device):
+        raise ValueError(f"out must be a float32 {(B, *O)} tensor on {f0.device}")
+    eflags = flags | (L.FLAG_IN_BF16 if bf16 else 0)
+
+    # t-innermost ingestion: [B,Nt,Nx,Ny] views of [B,Nx,Ny,Nt] memory -- FNO outputs
+    # handed on as pred.permute(0,1,4,2,3) -- are processed IN PLACE by the t-innermost star kernel.  The
+    # result, the reference residual and the per-cell weight use the same physical order; the caller sees
+    # logical shapes throughout.
+    if (canonicalise and path in (L.PATH_AUTO, L.PATH_TIN) and not bf16 and tuple(O) == (N2, N1, N0)
+            and all(_is_tin(f) for f in fields) and (out is None or mode != L.EPI_STORE or _is_tin(out))):
+        t_ref = None if ref is None else _as_tin(ref)
+        t_w, t_ws = None, None
+        if weight is not None:
+            t_w = weight.permute(1, 2, 0).contiguous()                    # physical [Nx][Ny][Nt]
+            t_ws = (1, N0 * N2, N2)
+        t_out = out
+        if mode == L.EPI_STORE and t_out is None:
+            t_out = torch.empty((B, N1, N0, N2), dtype=torch.float32, device=f0.device).permute(0, 3, 1, 2)
+        args = (kind, list(fields), kernels, pads, scalars, mode, eflags, reduce, t_ref, t_w, t_ws)
+        if _residual_call(*args, L.PATH_TIN, t_out, band_q, query_tin=True):
+            return _residual_call(*args, L.PATH_TIN, t_out, band_q)
+        if path == L.PATH_TIN:
+            raise NotImplementedError("request does not qualify for the t-innermost star kernel")
 
     # Physical-layout canonicalisation: a permuted view such
     # as pred.permute(0,1,4,2,3) is processed in its memory order -- fields, taps, padding,
@@ -145,10 +253,9 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     if canonicalise and f0.numel() > 0 and all(_axis_order(f) == _axis_order(f0) for f in fields):
         perm = _axis_order(f0)
     if perm != [0, 1, 2]:
-        # Memory order pays only when its innermost axis can fill the 128-column TMA tiles.  The
-        # t-innermost views FNO surrogates emit (Nt = 50..100 innermost) cannot: measured on B200
-        # (tools/perm_layout.py, NS momentum) 13-19 Gpoints/s in place against 67 Gpoints/s for one
-        # transposing copy + the contiguous kernel (416 Gpoints/s), so those are copied once.
+        # Memory order pays only when its innermost axis can fill the 128-column TMA tiles.  Views that the
+        # t-innermost kernel did not take (odd Nt, Taylor-4/6 taps, bf16) are copied once: the FNO layout
+        # through the library's tiled transpose, anything else through torch.
         n0_mem, n0_log = int(f0.shape[1 + perm[2]]), int(f0.shape[3])
         if (n0_mem % 4 != 0 or n0_mem < 128) and n0_log % 4 == 0 and n0_log >= n0_mem:
             fields = [_to_logical_order(f, perm) for f in fields]
@@ -164,82 +271,29 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         if weight is not None:
             weight = weight.permute(perm).contiguous()
         bit = {0: L.FLAG_INTERIOR_2, 1: L.FLAG_INTERIOR_1, 2: L.FLAG_INTERIOR_0}
-        nf = flags & L.FLAG_ABS
+        nf = eflags & (L.FLAG_ABS | L.FLAG_IN_BF16)
         for new_axis, old_axis in enumerate(perm):
-            if flags & bit[old_axis]:
+            if eflags & bit[old_axis]:
                 nf |= bit[new_axis]
-        flags = nf
+        eflags = nf
         f0 = fields[0]
+        if out is not None:
+            out = out.permute(tperm)
 
     B, N2, N1, N0 = (int(v) for v in f0.shape)
-    prog = L.Program()
-    prog.kind, prog.n_fields, prog.n_slots = kind, len(fields), len(kernels)
-    for s, (k, p) in enumerate(zip(kernels, pads)):
-        if k.ndim != 3:
-            raise ValueError("slot kernels must be 3-D [k2,k1,k0]")
-        for d in range(3):
-            prog.ksize[s][d] = k.shape[d]
-            prog.pad[s][d] = p[d]
-        prog.h_taps[s] = k.ctypes.data
-    for i, v in enumerate(scalars):
-        prog.scalars[i] = float(v)
-    k0, p0 = kernels[0], pads[0]
-    O = [n + 2 * p - k + 1 for n, p, k in zip((N2, N1, N0), p0, k0.shape)]
-    if min(O) < 0:
-        raise RuntimeError(f"kernel size {tuple(k0.shape)} can't be greater than the padded input {(N2, N1, N0)}")
-
-    fl = (L.Field * len(fields))()
-    for i, f in enumerate(fields):
-        fl[i].d_data = f.data_ptr() if f.numel() else 0
-        for d in range(4):
-            fl[i].stride[d] = f.stride(d)
-    epi = L.Epilogue()
-    epi.mode, epi.flags, epi.reduce = mode, flags | (L.FLAG_IN_BF16 if bf16 else 0), reduce
-    dev = f0.device
-    keep = []
-    if isinstance(band_q, torch.Tensor):
-        if band_q.numel() != 1 or band_q.dtype != torch.float32 or band_q.device != dev:
-            raise ValueError(f"band_q must be a Python float or a one-element float32 tensor on {dev}")
-        epi.d_band_q = band_q.data_ptr()
-        keep.append(band_q)
-    else:
-        epi.band_q = float(band_q)
-    if ref is not None:
-        if tuple(ref.shape) != (B, *O):
-            raise ValueError(f"reference residual has shape {tuple(ref.shape)}, expected {(B, *O)}")
-        epi.d_ref = ref.data_ptr()
-        for d in range(4):
-            epi.ref_stride[d] = ref.stride(d)
-        keep.append(ref)
+    O = [n + 2 * p - k + 1 for n, p, k in zip((N2, N1, N0), pads[0], kernels[0].shape)]
     if weight is not None:
-        if tuple(weight.shape) != tuple(O):
-            raise ValueError(f"weight has shape {tuple(weight.shape)}, expected {tuple(O)}")
         weight = weight.contiguous()
-        epi.d_weight = weight.data_ptr()
-        keep.append(weight)
-    with torch.cuda.device(dev):
-        if mode == L.EPI_STORE:
-            if out is None:
-                out = torch.empty((B, *O), dtype=torch.float32, device=dev)
-            else:      # caller-owned destination (e.g. a batch slice of a larger score tensor)
-                if perm != [0, 1, 2]:
-                    out = out.permute([0] + [1 + d for d in perm])
-                if tuple(out.shape) != (B, *O) or out.dtype != torch.float32 or out.device != dev:
-                    raise ValueError(f"out must be a float32 {(B, *O)} tensor on {dev}")
-            epi.d_out = out.data_ptr() if out.numel() else 0
-            for d in range(4):
-                epi.out_stride[d] = out.stride(d)
-        else:
-            out = torch.empty((B,), dtype=torch.float32 if mode == L.EPI_SCORE else torch.int32, device=dev)
-            epi.d_scores = out.data_ptr() if B else 0
-        shape = (C.c_int64 * 4)(B, N2, N1, N0)
-        L.check(lib.cppre_residual(C.byref(prog), shape, fl, C.byref(epi), int(path), _stream(dev)))
+    if mode == L.EPI_STORE and out is None:
+        out = torch.empty((B, *O), dtype=torch.float32, device=f0.device)
+    res = _residual_call(kind, list(fields), kernels, pads, scalars, mode, eflags, reduce, ref, weight, None, path,
+                         out, band_q)
     if mode == L.EPI_STORE and perm != [0, 1, 2]:
         inv = [0] * 3
         for new_axis, old_axis in enumerate(perm):
             inv[old_axis] = new_axis
-        out = out.permute([0] + [1 + d for d in inv])
-    return out
+        res = res.permute([0] + [1 + d for d in inv])
+    return res
 
 
 # --------------------------------------------------------------------------------------

@@ -132,8 +132,10 @@ enum {
     CPPRE_FLAG_IN_BF16 = 16
 };
 /* Which kernel executes the program.  AUTO picks the TMA star kernel when the request
- * qualifies (3-point star taps, 16-byte aligned rows) and the generic kernel otherwise. */
-enum { CPPRE_PATH_AUTO = 0, CPPRE_PATH_GENERIC = 1, CPPRE_PATH_TMA = 2 };
+ * qualifies (3-point star taps, 16-byte aligned rows), the t-innermost star kernel when every field
+ * (and the output / reference / weight) is a [B,Nt,Nx,Ny] view of [B,Nx,Ny,Nt] memory -- the layout FNO
+ * surrogates emit, pred.permute(0,1,4,2,3)  Joint/Wave_Residuals_CP.py:216 -- and the generic kernel otherwise. */
+enum { CPPRE_PATH_AUTO = 0, CPPRE_PATH_GENERIC = 1, CPPRE_PATH_TMA = 2, CPPRE_PATH_TIN = 3 };
 
 typedef struct cppre_epilogue {
     int32_t mode;   /* CPPRE_EPI_* */
@@ -150,6 +152,10 @@ typedef struct cppre_epilogue {
      * (cppre_radix_select / cppre_select_ranks) and hands the pointer straight to the coverage launch:
      * no host round trip between calibrate() and emp_cov_joint()  Joint/MHD_Residuals_CP.py:399-401 */
     const float* d_band_q;
+    /* Element strides of d_weight, order [O2, O1, O0]; all zero = contiguous.  The only other order the
+     * kernels take is the t-innermost one, (1, O0*O2, O2) -- the weight laid out like the [Nx][Ny][Nt]
+     * fields it goes with (CPPRE_PATH_TIN); anything else is CPPRE_ERR_UNSUPPORTED. */
+    int64_t weight_stride[3];
 } cppre_epilogue_t;
 
 /* ---- library state -------------------------------------------------------------------- */
@@ -157,7 +163,7 @@ int cppre_version(void);
 const char* cppre_last_error(void);
 /* Number of kernels this library has launched in the calling process (all threads). */
 uint64_t cppre_launch_count(void);
-/* Name of the kernel path the last cppre_residual call on this thread used: "tma" | "generic". */
+/* Name of the kernel path the last cppre_residual call on this thread used: "tma" | "tin" | "generic". */
 const char* cppre_last_path(void);
 
 /* ---- K1: fused residual program ------------------------------------------------------- */
@@ -165,6 +171,9 @@ const char* cppre_last_path(void);
 int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
                    const cppre_field_t* fields, const cppre_epilogue_t* epi,
                    int path, void* stream);
+/* Returns 1 if (prog, shape, fields, epi) qualifies for the t-innermost star kernel, else 0. */
+int cppre_residual_tin_eligible(const cppre_program_t* prog, const int64_t shape[4],
+                                const cppre_field_t* fields, const cppre_epilogue_t* epi);
 /* Returns 1 if (prog, shape, fields, epi) qualifies for the TMA star kernel, else 0. */
 int cppre_residual_tma_eligible(const cppre_program_t* prog, const int64_t shape[4],
                                 const cppre_field_t* fields, const cppre_epilogue_t* epi);

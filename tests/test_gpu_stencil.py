@@ -493,6 +493,86 @@ def test_fno_layout_views_are_transposed_by_the_library_and_match_the_contiguous
         assert got.shape == want.shape and torch.equal(got, want), (nx, ny, nt)
 
 
+def _tin(t):
+    """Same logical values, stored t-innermost: what pred.permute(0,1,4,2,3) of an FNO output looks like."""
+    nd = t.dim()
+    fwd = list(range(nd - 3)) + [nd - 2, nd - 1, nd - 3]
+    inv = list(range(nd - 3)) + [nd - 1, nd - 3, nd - 2]
+    return t.permute(fwd).contiguous().permute(inv)
+
+
+def test_t_innermost_kernel_takes_fno_views_in_place_and_is_bit_equal_to_the_contiguous_run():
+    """the t-innermost star kernel reads [BS,F,Nx,Ny,Nt] memory through its
+    [BS,F,Nt,Nx,Ny] view with no transpose pass; STORE / SCORE / COVER results equal the contiguous
+    run BIT FOR BIT (same arm accumulation order), for every shipped program family, ragged tiles,
+    short and long t lines, and sample strides that are not the dense ones (field slices of a 5-D tensor)."""
+    import bench
+    o, n = _programs_2d(), synth.NS
+    progs = {"ns": (programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"],
+                                         n["nu"]), 3),
+             "cont": (programs.ns_continuity(o["D_x"], o["D_y"], n["dx"], n["dy"]), 3),
+             "wave": (bench.make_program("wave"), 1)}
+    for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+        progs["mhd_" + eq] = (bench.make_program("mhd", eq), 6)
+    g = torch.Generator(device="cuda").manual_seed(21)
+    shapes = ((3, 50, 12, 20), (2, 4, 7, 9), (2, 100, 33, 17), (1, 80, 5, 130), (2, 20, 64, 64), (1, 512, 6, 10),
+              (2, 6, 3, 4), (1, 258, 9, 10))
+    for name, (prog, nf) in progs.items():
+        for (bs, nt, nx, ny) in shapes:
+            if name.startswith("mhd") and nt > 100:
+                continue
+            shape = (bs, nf, nt, nx, ny) if nf > 1 else (bs, nt, nx, ny)
+            v = torch.randn(shape, device="cuda", generator=g)
+            if name.startswith("mhd"):
+                v = v.abs() + 0.5                                        # density / pressure away from 0
+            vt = _tin(v)
+            assert not vt.is_contiguous()
+            want = prog.residual(v, boundary=True)
+            got = prog.residual(vt, boundary=True)
+            assert L.last_path() == "tin", (name, shape)
+            assert torch.equal(got, want), (name, shape)
+            assert got.stride(1) == 1                                   # result stays t-innermost
+            ref = torch.randn(want.shape, device="cuda", generator=g)
+            w = torch.rand(want.shape[1:], device="cuda", generator=g) + 0.1
+            for interior in (True, False):
+                for red in ("max", "sum"):
+                    a = prog.joint_scores(v, inv_modulation=w, ref=ref, interior=interior, reduce=red)
+                    b = prog.joint_scores(vt, inv_modulation=w, ref=_tin(ref), interior=interior, reduce=red)
+                    assert L.last_path() == "tin"
+                    if red == "max":
+                        assert torch.equal(a, b), (name, shape, interior)
+                    else:                                               # sums: different cell order
+                        assert torch.allclose(a, b, rtol=2e-5, atol=1e-6), (name, shape, interior)
+                a = prog.coverage_counts(v, 0.7, half=w, centre=ref, interior=interior)
+                b = prog.coverage_counts(vt, 0.7, half=_tin(w), centre=ref, interior=interior)   # ref copied once
+                assert L.last_path() == "tin"
+                assert torch.equal(a, b), (name, shape, interior)
+            sc = torch.empty_like(want)
+            a = prog.abs_scores(v, ref=ref, boundary=True)
+            outp = _tin(sc)
+            b = prog.abs_scores(vt, ref=_tin(ref), boundary=True, out=outp)
+            assert L.last_path() == "tin" and b.data_ptr() == outp.data_ptr() and torch.equal(a, b)
+
+
+def test_t_innermost_kernel_declines_what_it_cannot_take():
+    """Odd Nt (the y-neighbour is an 8-byte shared load), Taylor-4 taps and bf16 input fall back to the
+    transpose + contiguous kernels and still match; PATH_TIN then raises instead of running something else."""
+    o, n = _programs_2d(), synth.NS
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    v = torch.randn((2, 3, 33, 12, 20), device="cuda")
+    got = prog.residual(_tin(v), boundary=True)
+    assert L.last_path() != "tin" and torch.equal(got, prog.residual(v, boundary=True))
+    prog.path = L.PATH_TIN
+    with pytest.raises(NotImplementedError):
+        prog.residual(_tin(v), boundary=True)
+    with pytest.raises(NotImplementedError):
+        prog.residual(v, boundary=True)                                  # contiguous input is not t-innermost
+    prog.path = L.PATH_AUTO
+    vb = torch.randn((2, 3, 16, 12, 128), device="cuda").to(torch.bfloat16)
+    assert torch.equal(prog.residual(_tin(vb), boundary=True), prog.residual(vb, boundary=True))
+    assert L.last_path() != "tin"
+
+
 def test_ns_marginal_cp_at_full_config_size():
     """The HEADLINE configuration at its full size (BASELINE config 4: NS momentum PRE + marginal per-cell
     CP, [512,3,50,256,256], Marginal/NS_Residuals_CP.py:327-337), the exact pipeline bench.py times:
