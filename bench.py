@@ -2,7 +2,7 @@
 """bench.py -- the hot-path benchmark (driver contract in the task statement).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload ns|wave|wave-joint|burgers|mhd] [--equation momentum|...] [--global-batch G]
+                    [--workload ns|wave|wave-joint|burgers|mhd|advection] [--equation momentum|...] [--global-batch G]
 
 Default workload: BASELINE.json configs[3] -- 2-D Navier-Stokes vector PRE (momentum residual via the
 live ConvOperator kernels) + marginal per-cell CP, BS=512, Nt=50, 256x256, fp32, the shape the
@@ -61,6 +61,9 @@ WORKLOADS = {
                        desc="configs[2]: 2D wave PRE (D_tt - c^2 Laplacian) + Joint CP, BS=1024 Nt=80 128x128"),
     "burgers": dict(kind="joint", bs=4096, nf=1, grid=(100, 1024),
                     desc="configs[1]: 1D Burgers nonlinear-residual PRE + Joint CP, BS=4096 Nt=100 Nx=1024"),
+    "advection": dict(kind="marginal-aer", bs=1100, nf=1, grid=(10, 197),
+                      desc="configs[0]: Marginal/Advection_Residuals_CP.py 1D advection PRE + marginal CP (AER+PRE scores, "
+                           "alpha grid), n_cal=100 n_test=1000 Nt=10 Nx=197 (the reference's own CPU-scale case)"),
     "mhd": dict(kind="joint", bs=None, nf=6, grid=(100, 256, 256),
                 desc="configs[4]: 2D MHD multi-field vector PRE + Joint CP, BS=2048 Nt=100 256x256 sharded over 8 GPUs"),
 }
@@ -471,47 +474,68 @@ class E2E:
 # ----------------------------------------------------------------------------------------
 # the reference's CPU path (oracle/torch_port.py) -- cpu_baseline leg and --impl reference
 # ----------------------------------------------------------------------------------------
+def cpu_arm():
+    """(module, kind) of the CPU arm: the reference's own code when the build-time snapshot (or the checkout)
+    is there -- oracle/ref_arm.py, kind "reference" -- else the oracle's port of it (kind "port")."""
+    from oracle import ref_arm, torch_port
+    if os.environ.get("CPPRE_CPU_ARM", "") != "port" and ref_arm.available():
+        return ref_arm, "reference"
+    return torch_port, "port"
+
+
+def cpu_residual_fn(args, arm, kind):
+    """residual(vars) of the workload on the CPU arm."""
+    from oracle import synth
+    if kind == "reference":
+        fn = arm.residual_function(args.workload, args.equation)
+        return fn
+    TP = arm
+    ops2 = TP.Ops2D() if len(WORKLOADS[args.workload]["grid"]) == 3 else None
+    if args.workload == "ns":
+        c = synth.NS
+        return lambda v: TP.ns_momentum(v, c["dx"], c["dy"], c["dt"], c["nu"], ops2)
+    if args.workload == "mhd":
+        return lambda v: TP.mhd(args.equation, v, synth.MHD["gamma"], ops2)
+    if args.workload == "burgers":
+        c = synth.BURGERS
+        return lambda v: TP.burgers(v, c["dx"], c["dt"], c["nu"])
+    return lambda v: TP.wave(v, synth.WAVE["c2"])
+
+
 def cpu_pipeline(args, bs, nt, seed=99, threads=None, chunk=32):
     """One UN-EXTRAPOLATED pass of the reference's CPU path over a [bs, F, nt, Nx(, Ny)] batch: PRE on every
     sample (F.conv3d + elementwise algebra, torch intra-op threads; evaluated in batch chunks only to bound
     host RAM), then the conformal step on the calibration half and coverage on the validation half.
-    Returns (points processed, seconds, per-stage seconds)."""
-    from oracle import cpu_oracle as O
-    from oracle import synth, torch_port as TP
+    Returns (points processed, seconds, per-stage seconds, kind)."""
+    from oracle import synth
+    arm, kind = cpu_arm()
     w = WORKLOADS[args.workload]
     torch.set_num_threads(threads or os.cpu_count())
     grid = (nt,) + tuple(w["grid"][1:])
     n_cal = bs // 2
     pos = (0, 3) if args.workload == "mhd" else ()
-    ops2 = TP.Ops2D() if len(grid) == 3 else None
+    residual = cpu_residual_fn(args, arm, kind)
     t_pre = 0.0
     res = []
     for b0 in range(0, bs, chunk):
         b1 = min(bs, b0 + chunk)
         v = torch.from_numpy(synth.fields(seed + b0, w["nf"], (b1 - b0,) + grid, positive=pos))   # untimed: data
+        if w["nf"] == 1:
+            v = v[:, 0]
         t0 = time.perf_counter()
-        if args.workload == "ns":
-            c = synth.NS
-            r = TP.ns_momentum(v, c["dx"], c["dy"], c["dt"], c["nu"], ops2)
-        elif args.workload == "mhd":
-            r = TP.mhd(args.equation, v, synth.MHD["gamma"], ops2)
-        elif args.workload == "burgers":
-            c = synth.BURGERS
-            r = TP.burgers(v[:, 0], c["dx"], c["dt"], c["nu"])
-        else:
-            r = TP.wave(v[:, 0], synth.WAVE["c2"])
+        r = residual(v)
         res.append(r.contiguous())
         t_pre += time.perf_counter() - t0
     t0 = time.perf_counter()
     res = torch.cat(res)
     cal, val = res[:n_cal], res[n_cal:]
     if w["kind"] == "marginal":
-        TP.marginal_cp(cal, val, ALPHA)
+        arm.marginal_cp(cal, val, ALPHA)
     else:
-        TP.joint_cp(cal, val, ALPHA, 1e-6 if args.workload == "mhd" else 0.0)
+        arm.joint_cp(cal, val, ALPHA, 1e-6 if args.workload == "mhd" else 0.0)
     t_cp = time.perf_counter() - t0
     pts = bs * int(np.prod(grid))
-    return pts, t_pre + t_cp, {"pre_s": t_pre, "cp_s": t_cp}
+    return pts, t_pre + t_cp, {"pre_s": t_pre, "cp_s": t_cp}, kind
 
 
 CPU_SAMPLE = {   # (batch, time planes) of the bounded CPU sample: the FULL per-GPU batch (the calibration set keeps
@@ -525,13 +549,16 @@ def cpu_sample(args, full=False):
     bs, nt = CPU_SAMPLE[args.workload]
     if full:
         bs, nt = (w["bs"] or 256), w["grid"][0]
-    pts, secs, stages = cpu_pipeline(args, bs, nt)
+    pts, secs, stages, kind = cpu_pipeline(args, bs, nt)
     threads = torch.get_num_threads()
     shape = (bs, w["nf"], nt) + tuple(w["grid"][1:])
     desc = (f"whole pipeline (PRE {stages['pre_s']:.2f}s + conformal step {stages['cp_s']:.2f}s) measured on a "
             f"{list(shape)} batch = {'the full configuration' if full else f'the full batch on {nt} of {w['grid'][0]} time planes'}; "
             f"value = its points / its seconds, nothing extrapolated")
-    return pts / secs / 1e9, desc, secs, threads, pts
+    desc += {"reference": "; the reference's own operators and residual functions (byte-for-byte snapshot of Utils/ and the "
+                          "script's statements), conformal helpers from the oracle (un-vendored upstream)",
+             "port": "; oracle/torch_port.py (the reference's library calls restated; no reference snapshot on this box)"}[kind]
+    return pts / secs / 1e9, desc, secs, threads, pts, kind
 
 
 def run_reference(args):
@@ -540,18 +567,20 @@ def run_reference(args):
     FULL configuration is timed as well, so the sample's throughput can be checked against it.  Rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    if args.workload == "advection":
+        return run_reference_advection(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     for _ in range(min(args.warmup, 1)):
         cpu_sample(args)
     vals, secs, pts = [], [], 0
     for _ in range(args.steps):
-        v, desc, s, threads, pts = cpu_sample(args)
+        v, desc, s, threads, pts, arm_kind = cpu_sample(args)
         vals.append(v)
         secs.append(s)
     value = pts / float(np.mean(secs)) / 1e9
     full = None
     if args.steps <= 2 and args.workload in ("ns", "wave", "wave-joint", "burgers") and not args.no_full_cpu:
-        fv, fdesc, fs, _, fpts = cpu_sample(args, full=True)
+        fv, fdesc, fs, _, fpts, _ = cpu_sample(args, full=True)
         full = {"value": fv, "unit": "Gpoints/s", "seconds": fs, "points": fpts, "what": fdesc,
                 "sample_over_full": value / fv}
     step = {"marginal": MarginalStep, "joint": JointStep}[WORKLOADS[args.workload]["kind"]]
@@ -561,9 +590,180 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(secs)),
         "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args, world),
-        "cpu_baseline": {"value": value, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc,
+        "cpu_baseline": {"value": value, "unit": "Gpoints/s", "cores": threads, "kind": arm_kind, "sample": desc,
                          "points_per_step": pts, "extrapolated": False, "full_configuration_step": full},
         "e2e": {"value": value, "unit": "Gpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+
+# ----------------------------------------------------------------------------------------
+# configs[0]: the reference's own CPU-scale case  [ref: Marginal/Advection_Residuals_CP.py:86-93,160-164,225-262]
+# ----------------------------------------------------------------------------------------
+ADV_N_CAL, ADV_N_TEST = 100, 1000
+ADV_ALPHAS = [float(a) for a in np.arange(0.05, 0.95, 0.1)]          # the script's alpha_levels (9 values)
+
+
+def advection_fields(n, seed, xp):
+    """Synthetic stand-in for the missing solver / FNO: travelling Gaussians on the script's grid
+    (Nx=200 minus the [1:-2] slice, Nt=100 -> T_out=20 -> every disc=2nd instant), ``out`` = exact solution,
+    ``pred`` = out + a smooth 1 % perturbation (a surrogate's error).  xp = numpy or torch.  [n, 10, 197] each."""
+    from oracle import synth
+    a = synth.ADVECTION
+    rng = np.random.default_rng(seed)
+    xc = rng.uniform(0.5, 1.0, (n, 1, 1)).astype(np.float32)
+    amp = rng.uniform(50, 200, (n, 1, 1)).astype(np.float32)
+    ph = rng.uniform(0, 1, (n, 1, 1)).astype(np.float32)
+    x = np.linspace(a["x_min"], a["x_max"], a["nx"], dtype=np.float32)[1:-2].reshape(1, 1, -1)
+    dt = a["t_end"] / a["nt"]
+    t = (dt * np.arange(80, 100, 2, dtype=np.float32)).reshape(1, -1, 1)      # last T_out=20 instants, ::disc
+    out = np.exp(-amp * (x - xc - a["v"] * t) ** 2).astype(np.float32)
+    pred = (out * (1 + 0.01 * np.sin(2 * np.pi * (x + 3 * t + ph)))).astype(np.float32)
+    if xp is torch:
+        return torch.from_numpy(out), torch.from_numpy(pred)
+    return out, pred
+
+
+def advection_cpu(args):
+    """The script's flow on the CPU arm, measured whole: residuals of out / pred for the calibration and test
+    sets, AER+PRE scores, then calibrate + emp_cov for every alpha.  Returns (points, seconds, kind, coverages)."""
+    from oracle import cpu_oracle as O
+    arm, kind = cpu_arm()
+    torch.set_num_threads(os.cpu_count())
+    if kind == "reference":
+        D = arm.residual_function("advection")
+    else:
+        from oracle import synth
+        a = synth.ADVECTION
+        k = torch.from_numpy(O.build_kernel("1d", "t", 1)) + (a["v"] * 2 * (a["t_end"] / a["nt"]) /
+                                                               ((a["x_max"] - a["x_min"]) / a["nx"])) * torch.from_numpy(O.build_kernel("1d", "x", 1))
+        D = lambda u: arm.conv_same(u, k)[..., 1:-1, 1:-1]
+    oc, pc = advection_fields(ADV_N_CAL, 11, torch)
+    ot, pt = advection_fields(ADV_N_TEST, 12, torch)
+    t0 = time.perf_counter()
+    scores = np.abs(D(oc) - D(pc))                                   # :234-237 (np.abs of a tensor difference)
+    scores = np.asarray(scores)
+    val, prd = D(ot).numpy(), D(pt).numpy()                          # :262-263
+    cov = []
+    for alpha in ADV_ALPHAS:                                         # :266-271
+        qhat = O.calibrate(scores, len(scores), alpha)
+        cov.append(float(O.emp_cov([prd - qhat, prd + qhat], val)))
+    secs = time.perf_counter() - t0
+    return (ADV_N_CAL + ADV_N_TEST) * 10 * 197, secs, kind, cov
+
+
+def run_advection(args):
+    """--workload advection, our arm: the same flow on the GPU through the public API -- K1 (generic kernel: Nx=197
+    is not a multiple of 4) STORE of the data residuals, |.-ref| scores, ONE multi-rank select for the alpha grid,
+    COVER per alpha with centre = predicted residual, half = qhat (sets never written)."""
+    from cp_pre_b200 import _lib, ops, programs
+    from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+    import cp_pre_b200
+    from oracle import synth
+    cp_pre_b200.install()
+    import ConvOps_1d as C1
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: cp_pre_b200 has no CPU fallback"
+    dev = torch.device("cuda", 0)
+    a = synth.ADVECTION
+    D = C1.ConvOperator()
+    D.kernel = C1.ConvOperator("t", 1).kernel + (a["v"] * 2 * (a["t_end"] / a["nt"]) / ((a["x_max"] - a["x_min"]) / a["nx"])) * C1.ConvOperator("x", 1).kernel
+    prog = programs.linear(D)
+    host = [t.pin_memory() for t in advection_fields(ADV_N_CAL, 11, torch) + advection_fields(ADV_N_TEST, 12, torch)]
+    ranks = [calibrate_rank(ADV_N_CAL, ADV_N_CAL, al) for al in ADV_ALPHAS]
+    interior = prog.interior_cells(host[0].shape)
+    events = []
+
+    def step(oc, pc, ot, pt, timed=False):
+        ref = prog.residual(oc, boundary=True)
+        scores = prog.abs_scores(pc, ref=ref, boundary=True)
+        q = ops.select_ranks(scores, ranks)                            # [9, Nt, Nx]
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        centre = prog.residual(pt, boundary=True)
+        if timed:
+            e1.record()
+            events.append((e0, e1))
+        counts = torch.stack([prog.coverage_counts(ot, 1.0, half=q[i], centre=centre).sum() for i in range(len(ranks))])
+        return q, counts
+
+    W, K = max(args.warmup, 3), args.steps
+    devt = [h.to(dev) for h in host]
+    for _ in range(W):
+        step(*devt)
+    torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(0) as clk:
+        e0.record()
+        for _ in range(K):
+            q, counts = step(*devt, timed=True)
+        e1.record()
+        torch.cuda.synchronize()
+    launches = _lib.launch_count() - l0
+    path = _lib.last_path()
+    ms = e0.elapsed_time(e1) / K
+    k1_ms = float(np.mean([x.elapsed_time(y) for x, y in events]))
+    cov = (counts.double() / (ADV_N_TEST * interior)).tolist()
+    # check against the CPU arm's numbers (same seeds): qhat bit-equal on the interior, coverage equal
+    from oracle import cpu_oracle as O
+    pts, cpu_s, kind, cpu_cov = advection_cpu(args)
+    ok = bool(np.allclose(cov, cpu_cov, atol=2e-4))
+    # e2e: pinned host tensors in, coverage list out
+    for _ in range(2):
+        step(*[h.to(dev, non_blocking=True) for h in host])
+    torch.cuda.synchronize()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for _ in range(K):
+        _, c = step(*[h.to(dev, non_blocking=True) for h in host])
+        c.cpu()
+    a1.record()
+    torch.cuda.synchronize()
+    e2e_ms = a0.elapsed_time(a1) / K
+    peak, peak_src = peaks()
+    k1_bytes = 8 * ADV_N_TEST * 10 * 197
+    print(json.dumps({
+        "metric": "PRE+marginal-CP throughput", "value": pts / (ms * 1e-3) / 1e9, "unit": "Gpoints/s", "n_gpus": 1, "steps": K,
+        "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": WORKLOADS["advection"]["desc"], "cp": "marginal-aer", "fields": 1,
+                                         "alphas": ADV_ALPHAS, "n_cal": ADV_N_CAL, "n_test": ADV_N_TEST,
+                                         "l2": "4.3 MB of inputs: L2-resident and launch-latency bound by construction (CPU-scale config)"},
+        "checks": {"empirical_coverage_per_alpha": cov, "cpu_arm_coverage_per_alpha": cpu_cov, "coverage_equals_cpu_arm": ok,
+                   "kernel_path": path},
+        "roofline": {"bound": "hbm", "kernel": "generic_kernel<linear> (K1g: Nx=197 is ragged), STORE of the test-set residual",
+                     "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "bytes_per_point": 8, "kernel_ms": k1_ms, "points_per_launch": ADV_N_TEST * 10 * 197,
+                     "note": "15.8 MB per launch: launch latency, not bandwidth, bounds this configuration"},
+        "cpu_baseline": {"value": pts / cpu_s / 1e9, "unit": "Gpoints/s", "cores": torch.get_num_threads(), "kind": kind,
+                         "sample": "the whole configuration, measured once", "seconds": cpu_s, "extrapolated": False},
+        "e2e": {"value": pts / (e2e_ms * 1e-3) / 1e9, "unit": "Gpoints/s", "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": sum(h.numel() * 4 for h in host), "d2h_bytes_per_step": 8 * len(ranks),
+                "path": "pinned host tensors -> H2D -> residuals, scores, quantiles, coverage -> 9 coverage values D2H"},
+        "gpu_launches": int(launches), "clocks": clk.summary(),
+    }))
+    assert ok, "coverage differs from the CPU arm"
+
+
+def run_reference_advection(args):
+    vals = []
+    for _ in range(max(1, args.steps)):
+        pts, secs, kind, cov = advection_cpu(args)
+        vals.append(secs)
+    secs = float(np.mean(vals))
+    v = pts / secs / 1e9
+    print(json.dumps({
+        "impl": "reference", "metric": "PRE+marginal-CP throughput", "value": v, "unit": "Gpoints/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOADS["advection"]["desc"], "cp": "marginal-aer", "fields": 1, "alphas": ADV_ALPHAS,
+                   "n_cal": ADV_N_CAL, "n_test": ADV_N_TEST,
+                   "l2": "4.3 MB of inputs: L2-resident and launch-latency bound by construction (CPU-scale config)"},
+        "checks": {"empirical_coverage_per_alpha": cov},
+        "cpu_baseline": {"value": v, "unit": "Gpoints/s", "cores": torch.get_num_threads(), "kind": kind,
+                         "sample": "the whole configuration", "extrapolated": False},
+        "e2e": {"value": v, "unit": "Gpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
@@ -583,6 +783,9 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "advection":
+        assert int(os.environ.get("WORLD_SIZE", "1")) == 1, "configs[0] is a single-device, CPU-scale configuration"
+        return run_advection(args)
 
     # stdout carries exactly one JSON line: anything a library prints meanwhile (NCCL's version
     # banner at communicator creation) is sent to stderr by pointing fd 1 there until the end
@@ -732,8 +935,8 @@ def main():
         alg_bytes = 4 * step.nf * (k1_pts + k1c_pts)                      # every input element read once
         cpu = None
         if world == 1 and not args.no_cpu:
-            v, desc, secs, threads, pts = cpu_sample(args)
-            cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": "port", "sample": desc,
+            v, desc, secs, threads, pts, arm_kind = cpu_sample(args)
+            cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": arm_kind, "sample": desc,
                    "points_per_step": pts, "seconds": secs, "extrapolated": False}
         _, _, scaling = geometry(args, world)
         traffic = k1_traffic(args.workload, args.equation)

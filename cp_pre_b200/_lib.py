@@ -27,7 +27,7 @@ PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS
 
 EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1
-FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16 = 1, 2, 4, 8, 16
+FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16, FLAG_DECODE = 1, 2, 4, 8, 16, 32
 PATH_AUTO, PATH_GENERIC, PATH_TMA, PATH_TIN = 0, 1, 2, 3
 
 BC_DIRICHLET, BC_NEUMANN, BC_PERIODIC, BC_SYMMETRIC, BC_NONE = range(5)
@@ -35,7 +35,7 @@ SPEC_CONJ_FIRST, SPEC_INVERSE, SPEC_CONJ_LAST = 1, 2, 4
 
 
 class Field(C.Structure):
-    _fields_ = [("d_data", C.c_void_p), ("stride", C.c_int64 * 4)]
+    _fields_ = [("d_data", C.c_void_p), ("stride", C.c_int64 * 4), ("scale", C.c_float), ("offset", C.c_float)]
 
 
 class Program(C.Structure):

@@ -93,6 +93,21 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
                                 fields[f].stride[2], fields[f].stride[3]};
     }
     memcpy(P.scalars, prog->scalars, sizeof(P.scalars));
+    P.dec_on = (epi->flags & CPPRE_FLAG_DECODE) ? 1 : 0;
+    if (P.dec_on) {
+        CPPRE_REQUIRE(!(epi->flags & CPPRE_FLAG_IN_BF16), CPPRE_ERR_UNSUPPORTED,
+                      "the decode fold takes fp32 fields only");
+        CPPRE_REQUIRE(same, CPPRE_ERR_UNSUPPORTED, "the decode fold needs 'same'-padded derivative slots");
+        for (int s = 0; s < prog->n_slots; ++s) {
+            double sum = 0.0;       // sum of the slot's taps: what the slot returns on a constant field of ones
+            for (int t = P.taps.begin[s]; t < P.taps.begin[s + 1]; ++t) sum += (double)P.taps.c[t];
+            for (int f = 0; f < prog->n_fields; ++f) P.dec.bs[s][f] = (float)((double)fields[f].offset * sum);
+        }
+        for (int f = 0; f < prog->n_fields; ++f) {
+            P.dec.a[f] = fields[f].scale;
+            P.dec.b[f] = fields[f].offset;
+        }
+    }
     CPPRE_REQUIRE(epi->mode == CPPRE_EPI_STORE || epi->mode == CPPRE_EPI_SCORE || epi->mode == CPPRE_EPI_COVER,
                   CPPRE_ERR_BAD_ARG, "unknown epilogue mode %d", epi->mode);
     P.epi.mode = epi->mode;

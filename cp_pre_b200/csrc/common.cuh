@@ -89,6 +89,13 @@ struct StarCoef {
     float c[CPPRE_MAX_SLOTS][8];  // [slot][arm], arm 7 unused
 };
 
+// ---- normaliser-decode fold (CPPRE_FLAG_DECODE) ----------------------------------------
+struct DecodeDev {
+    float a[CPPRE_MAX_FIELDS];                     // scale of field f
+    float b[CPPRE_MAX_FIELDS];                     // offset of field f
+    float bs[CPPRE_MAX_SLOTS][CPPRE_MAX_FIELDS];   // offset_f * (sum of the taps of slot s)
+};
+
 // ---- generic tap list ----------------------------------------------------------------------
 struct DevTaps {
     int32_t begin[CPPRE_MAX_SLOTS + 1];
@@ -131,6 +138,8 @@ struct Prepared {
     int in_bf16;   // CPPRE_FLAG_IN_BF16: fields[].p point to bfloat16 elements
     int weight_tin;      // the epilogue weight is laid out [N1][N0][N2] (t-innermost), not contiguous [N2][N1][N0]
     int weight_contig;   // ... contiguous (both can hold for degenerate extents)
+    int dec_on;          // CPPRE_FLAG_DECODE
+    DecodeDev dec;
 };
 int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_field_t* fields,
             const cppre_epilogue_t* epi, Prepared* out);
@@ -149,17 +158,22 @@ CPPRE_TMA_TU(cover_dyn) CPPRE_TMA_TU(cover_w)
 CPPRE_TMA_TU(store_dyn_bf16) CPPRE_TMA_TU(store_plain_bf16)
 CPPRE_TMA_TU(score_dyn_bf16) CPPRE_TMA_TU(score_w_bf16)
 CPPRE_TMA_TU(cover_dyn_bf16) CPPRE_TMA_TU(cover_w_bf16)
+CPPRE_TMA_TU(store_dyn_dec) CPPRE_TMA_TU(score_dyn_dec) CPPRE_TMA_TU(cover_dyn_dec)
 #undef CPPRE_TMA_TU
 #define CPPRE_TIN_TU(sfx)                                                   \
     int tin_eligible_##sfx(const cppre_program_t* prog, const Prepared& P); \
     int launch_tin_##sfx(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
 CPPRE_TIN_TU(store) CPPRE_TIN_TU(score) CPPRE_TIN_TU(cover)
+CPPRE_TIN_TU(store_dec) CPPRE_TIN_TU(score_dec) CPPRE_TIN_TU(cover_dec)
 #undef CPPRE_TIN_TU
 inline int tin_eligible(const cppre_program_t* prog, const Prepared& P) {
     return P.epi.mode == CPPRE_EPI_STORE ? tin_eligible_store(prog, P)
          : P.epi.mode == CPPRE_EPI_SCORE ? tin_eligible_score(prog, P) : tin_eligible_cover(prog, P);
 }
 inline int launch_tin(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
+    if (P.dec_on)     // the decode fold lives in its own translation units: the plain kernels carry none of it
+        return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store_dec(prog, P, stream)
+             : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score_dec(prog, P, stream) : launch_tin_cover_dec(prog, P, stream);
     return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store(prog, P, stream)
          : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score(prog, P, stream) : launch_tin_cover(prog, P, stream);
 }
@@ -172,6 +186,9 @@ inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
 }
 inline int launch_tma(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
     const int oper = (P.epi.ref ? 1 : 0) | (P.epi.weight ? 2 : 0);
+    if (P.dec_on)
+        return P.epi.mode == CPPRE_EPI_STORE ? launch_tma_store_dyn_dec(prog, P, stream)
+             : P.epi.mode == CPPRE_EPI_SCORE ? launch_tma_score_dyn_dec(prog, P, stream) : launch_tma_cover_dyn_dec(prog, P, stream);
     if (P.in_bf16) {
         switch (P.epi.mode) {
             case CPPRE_EPI_STORE:

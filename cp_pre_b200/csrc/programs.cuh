@@ -47,6 +47,27 @@ __device__ __forceinline__ f2 pfnma(f2 a, f2 b, f2 c) { return f2{__ffma2_rn(mak
 __device__ __forceinline__ f2 pfnma(f2 a, float b, f2 c) { return f2{__ffma2_rn(a.v, bc2(-b), c.v)}; }
 __device__ __forceinline__ f2 pinv(f2 a) { return mk2(1.0f / a.v.x, 1.0f / a.v.y); }
 
+// Normaliser-decode fold (CPPRE_FLAG_DECODE): wraps a kernel's context so the program sees the field
+// a_f * x + b_f.  A derivative slot is linear, so on cells whose whole stencil lies inside the field
+// D(a x + b) = a D(x) + b * sum(taps): one more FFMA(2) per slot evaluation with broadcast operands, and the
+// raw field factors are decoded at the output cell.  No pass over the tensor, no decoded copy.
+__device__ __forceinline__ float paffine(float x, float a, float b) { return fmaf(x, a, b); }
+__device__ __forceinline__ f2 paffine(f2 x, float a, float b) { return f2{__ffma2_rn(x.v, bc2(a), bc2(b))}; }
+
+template <class C>
+struct DecodeCtx {
+    const C& c;
+    const DecodeDev& d;
+    template <int SLOT, int FIELD, int I>
+    __device__ __forceinline__ auto D() const {
+        return paffine(c.template D<SLOT, FIELD, I>(), d.a[FIELD], d.bs[SLOT][FIELD]);
+    }
+    template <int FIELD, int I>
+    __device__ __forceinline__ auto V() const {
+        return paffine(c.template V<FIELD, I>(), d.a[FIELD], d.b[FIELD]);
+    }
+};
+
 template <int KIND>
 struct Prog;
 

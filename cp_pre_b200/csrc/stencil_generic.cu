@@ -17,6 +17,8 @@ struct GenericParams {
     EpiDev e;
     float scalars[CPPRE_MAX_SCALARS];
     int32_t chunks;  // blocks per sample
+    int32_t dec_on;
+    DecodeDev dec;
     DevTaps taps;
 };
 
@@ -66,7 +68,8 @@ generic_kernel(const __grid_constant__ GenericParams p) {
         GenericCtx c{p, {}, o2, o1, o0};
 #pragma unroll
         for (int f = 0; f < Prog<KIND>::NF; ++f) c.base[f] = p.f[f].p + (int64_t)b * p.f[f].sb;
-        v = Prog<KIND>::template eval<0>(c, p.scalars);
+        if (p.dec_on) v = Prog<KIND>::template eval<0>(DecodeCtx<GenericCtx>{c, p.dec}, p.scalars);
+        else v = Prog<KIND>::template eval<0>(c, p.scalars);
         const float rf = p.e.ref ? __ldg(p.e.ref + b * p.e.rb + o2 * p.e.r2 + o1 * p.e.r1 + o0 * p.e.r0) : 0.0f;
         if (p.e.mode == CPPRE_EPI_COVER) {
             const float q = p.e.band_qp ? __ldg(p.e.band_qp) : p.e.band_q;
@@ -119,6 +122,8 @@ int launch_generic(const Prepared& P, cudaStream_t st) {
     gp.e = P.epi;
     for (int i = 0; i < CPPRE_MAX_SCALARS; ++i) gp.scalars[i] = P.scalars[i];
     gp.taps = P.taps;
+    gp.dec_on = P.dec_on;
+    gp.dec = P.dec;
     const int64_t cells = (int64_t)P.g.O2 * P.g.O1 * P.g.O0;
     const int64_t chunks = (cells + kThreads - 1) / kThreads;
     const int64_t blocks = chunks * P.g.B;

@@ -36,6 +36,12 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kMaxStages = 8;
+// CPPRE_TIN_DECODE: the normaliser-decode fold (CPPRE_FLAG_DECODE, programs.cuh DecodeCtx) is compiled into
+// this translation unit's kernels -- the layout FNO surrogates emit is also the one that arrives normalised.
+#ifndef CPPRE_TIN_DECODE
+#define CPPRE_TIN_DECODE 0
+#endif
+constexpr bool kDEC = CPPRE_TIN_DECODE != 0;
 
 template <int NF>
 struct alignas(16) TinParams {
@@ -50,6 +56,7 @@ struct alignas(16) TinParams {
     int32_t padl;             // leading pad elements: (padl + Nt) % 4 == 0, so centre element 0 is 16-byte aligned
     int32_t stages;
     uint32_t buf_bytes;       // one (stage, field) row tile, 128-aligned
+    DecodeDev dec;            // read by the CPPRE_TIN_DECODE units only
 };
 
 template <int N, class F>
@@ -309,8 +316,15 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
                 if (live & (1u << j)) {
-                    const f2 r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
-                    const f2 r23 = Prog<KIND>::template eval<2 * j + 1>(ctx, p.scalars);
+                    f2 r01, r23;
+                    if constexpr (kDEC) {
+                        const DecodeCtx<std::remove_const_t<decltype(ctx)>> dctx{ctx, p.dec};
+                        r01 = Prog<KIND>::template eval<2 * j + 0>(dctx, p.scalars);
+                        r23 = Prog<KIND>::template eval<2 * j + 1>(dctx, p.scalars);
+                    } else {
+                        r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
+                        r23 = Prog<KIND>::template eval<2 * j + 1>(ctx, p.scalars);
+                    }
                     float r[4] = {r01.v.x, r01.v.y, r23.v.x, r23.v.y};
                     const float rr[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
                     const float ww[4] = {wq[j].x, wq[j].y, wq[j].z, wq[j].w};
@@ -454,6 +468,7 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
     tp.coef = H.coef;
     memcpy(tp.scalars, P.scalars, sizeof(tp.scalars));
     tp.e = P.epi;
+    tp.dec = P.dec;
     tp.Nt = Nt; tp.Nx = Nx; tp.Ny = Ny;
     // y-lines per tile: as many as RX quads per thread hold, TY*Nt a multiple of 4
     int TY = (RX * kThreads * 4) / Nt;

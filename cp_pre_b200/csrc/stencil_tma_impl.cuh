@@ -54,6 +54,12 @@ constexpr int kDefaultL2Hints = 0;   // see StarParams::l2_hints; CPPRE_TMA_L2_H
 #define CPPRE_TMA_BF16 0
 #endif
 constexpr bool kBF16 = CPPRE_TMA_BF16 != 0;
+// CPPRE_TMA_DECODE: the normaliser-decode fold (CPPRE_FLAG_DECODE, programs.cuh DecodeCtx) is compiled into
+// this translation unit's kernels; the other units carry none of it.
+#ifndef CPPRE_TMA_DECODE
+#define CPPRE_TMA_DECODE 0
+#endif
+constexpr bool kDEC = CPPRE_TMA_DECODE != 0;
 constexpr uint32_t kES = kBF16 ? 2u : 4u;      // bytes per staged field element
 // smem row: 16 bytes of halo/pad each side (4 fp32 / 8 bf16 cells).  The TMA box must START on a
 // 16-byte boundary of the global row (col0 - kHP), and the interior stays 16-byte aligned.
@@ -73,6 +79,7 @@ struct alignas(64) StarParams {
     int32_t stages;
     uint32_t buf_bytes;   // bytes of one (stage, field) tile, 128-aligned
     int32_t l2_hints;     // bit 0: field tiles evict_first, bit 1: weight tile evict_last
+    DecodeDev dec;        // read by the CPPRE_TMA_DECODE units only
 };
 
 template <int N, class F>
@@ -502,8 +509,15 @@ star_kernel(const __grid_constant__ StarParams<Prog<KIND>::NF> p) {
                 }
                 if constexpr (j + 1 < RX) fetch_operands(std::integral_constant<int, j + 1>{});
                 if (live & (1u << j)) {
-                    const f2 r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
-                    const f2 r23 = Prog<KIND>::template eval<2 * j + 1>(ctx, p.scalars);
+                    f2 r01, r23;
+                    if constexpr (kDEC) {
+                        const DecodeCtx<std::remove_const_t<decltype(ctx)>> dctx{ctx, p.dec};
+                        r01 = Prog<KIND>::template eval<2 * j + 0>(dctx, p.scalars);
+                        r23 = Prog<KIND>::template eval<2 * j + 1>(dctx, p.scalars);
+                    } else {
+                        r01 = Prog<KIND>::template eval<2 * j + 0>(ctx, p.scalars);
+                        r23 = Prog<KIND>::template eval<2 * j + 1>(ctx, p.scalars);
+                    }
                     float r[4] = {r01.v.x, r01.v.y, r23.v.x, r23.v.y};
                     const float rr[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
                     const float ww[4] = {wq[j].x, wq[j].y, wq[j].z, wq[j].w};
@@ -740,6 +754,7 @@ int launch_variant(const Prepared& P, const StarHost& H, cudaStream_t st) {
     sp.coef = H.coef;
     memcpy(sp.scalars, P.scalars, sizeof(sp.scalars));
     sp.e = P.epi;
+    sp.dec = P.dec;
     sp.N2 = g.N2;
     sp.N1 = g.N1;
     sp.N0 = g.N0;

@@ -126,7 +126,7 @@ def _as_tin(t: torch.Tensor) -> torch.Tensor:
 
 
 def _residual_call(kind, fields, kernels, pads, scalars, mode, flags, reduce, ref, weight, weight_stride, path, out,
-                   band_q, query_tin=False):
+                   band_q, query_tin=False, decode=None):
     """Fills the C structs for one cppre_residual call and makes it (or, ``query_tin``, only asks whether the
     t-innermost kernel would take it).  ``out`` is the STORE destination or None for the reducing modes."""
     lib = L.load()
@@ -146,8 +146,9 @@ def _residual_call(kind, fields, kernels, pads, scalars, mode, flags, reduce, re
         fl[i].d_data = f.data_ptr() if f.numel() else 0
         for d in range(4):
             fl[i].stride[d] = f.stride(d)
+        fl[i].scale, fl[i].offset = (1.0, 0.0) if decode is None else (float(decode[0][i]), float(decode[1][i]))
     epi = L.Epilogue()
-    epi.mode, epi.flags, epi.reduce = mode, flags, reduce
+    epi.mode, epi.flags, epi.reduce = mode, flags | (L.FLAG_DECODE if decode is not None else 0), reduce
     dev = f0.device
     if isinstance(band_q, torch.Tensor):
         if band_q.numel() != 1 or band_q.dtype != torch.float32 or band_q.device != dev:
@@ -186,7 +187,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
                 mode: int = L.EPI_STORE, flags: int = 0, reduce: int = L.REDUCE_MAX,
                 ref: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None,
                 path: int = L.PATH_AUTO, canonicalise: bool = True,
-                out: Optional[torch.Tensor] = None, band_q=0.0) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, band_q=0.0, decode=None) -> torch.Tensor:
     """Runs one fused residual program.
 
     fields   CUDA fp32 tensors, all of logical shape [B, N2, N1, N0], any strides (views welcome)
@@ -196,6 +197,8 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     counts of cells with ref - band_q*weight <= residual <= ref + band_q*weight (COVER).
     ``band_q`` is a Python float or a one-element float32 CUDA tensor (e.g. the device scalar
     ``radix_select`` returns): the kernel then reads q itself and nothing crosses to the host.
+    ``decode`` = (scales, offsets), one float per field: the program reads scale_f * x + offset_f (the
+    normaliser-decode fold, CPPRE_FLAG_DECODE in include/cppre.h; exact on the interior cells only).
     """
     L.load()
     require_cuda()
@@ -203,6 +206,11 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     if any(f.shape != f0.shape for f in fields):
         raise ValueError("all fields of a residual program must share one shape")
     bf16 = f0.dtype == torch.bfloat16          # bf16-input mode (include/cppre.h, CPPRE_FLAG_IN_BF16)
+    if decode is not None:
+        if bf16:
+            raise NotImplementedError("the decode fold takes float32 fields only")
+        if len(decode) != 2 or len(decode[0]) != len(fields) or len(decode[1]) != len(fields):
+            raise ValueError("decode must be (scales, offsets) with one value per field")
     if any(f.dtype != f0.dtype for f in fields) or f0.dtype not in (torch.float32, torch.bfloat16):
         raise RuntimeError("expected scalar type Float (fields must all be float32, or all bfloat16)")
     kernels = [np.ascontiguousarray(k, dtype=np.float32) for k in kernels]
@@ -240,8 +248,8 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
         if mode == L.EPI_STORE and t_out is None:
             t_out = torch.empty((B, N1, N0, N2), dtype=torch.float32, device=f0.device).permute(0, 3, 1, 2)
         args = (kind, list(fields), kernels, pads, scalars, mode, eflags, reduce, t_ref, t_w, t_ws)
-        if _residual_call(*args, L.PATH_TIN, t_out, band_q, query_tin=True):
-            return _residual_call(*args, L.PATH_TIN, t_out, band_q)
+        if _residual_call(*args, L.PATH_TIN, t_out, band_q, query_tin=True, decode=decode):
+            return _residual_call(*args, L.PATH_TIN, t_out, band_q, decode=decode)
         if path == L.PATH_TIN:
             raise NotImplementedError("request does not qualify for the t-innermost star kernel")
 
@@ -287,7 +295,7 @@ def run_program(kind: int, fields: Sequence[torch.Tensor], kernels: Sequence[np.
     if mode == L.EPI_STORE and out is None:
         out = torch.empty((B, *O), dtype=torch.float32, device=f0.device)
     res = _residual_call(kind, list(fields), kernels, pads, scalars, mode, eflags, reduce, ref, weight, None, path,
-                         out, band_q)
+                         out, band_q, decode=decode)
     if mode == L.EPI_STORE and perm != [0, 1, 2]:
         inv = [0] * 3
         for new_axis, old_axis in enumerate(perm):

@@ -78,9 +78,56 @@ class ResidualProgram:
             return full[..., 1:-1, 1:-1]
         return full[..., 1:-1, 1:-1, 1:-1]
 
-    def _run(self, vars_, **kw):
+    def _run(self, vars_, decode=None, **kw):
         ks, pads = self._slots()
-        return ops.run_program(self.kind, self._fields(vars_), ks, pads, self.scalars, path=self.path, **kw)
+        fs = self._fields(vars_)
+        return ops.run_program(self.kind, fs, ks, pads, self.scalars, path=self.path,
+                               decode=self._decode_per_field(decode, vars_, len(fs)), **kw)
+
+    # -- normaliser-decode fold ------------------------------------------------
+    @staticmethod
+    def _affine(decode):
+        """(scale, offset) of ``decoded = scale * x + offset``.  Accepts the pair itself or a normaliser object
+        of the MinMax kind the scripts use -- attributes ``a`` / ``b`` with ``decode(x) = (x - b) / a``
+        [ref: Tests/test_ns.py:111-134; the class lives in the un-vendored Neural_PDE package]."""
+        if hasattr(decode, "a") and hasattr(decode, "b"):
+            a = torch.as_tensor(decode.a, dtype=torch.float64).reshape(-1)
+            b = torch.as_tensor(decode.b, dtype=torch.float64).reshape(-1)
+            return (1.0 / a).tolist(), (-b / a).tolist()
+        sc, of = decode
+        flat = lambda v: torch.as_tensor(v, dtype=torch.float64).reshape(-1).tolist()
+        return flat(sc), flat(of)
+
+    def _affine_per_variable(self, decode, vars_):
+        """(scales, offsets), one value per variable (channel) of ``vars``; scalars apply to every variable."""
+        sc, of = self._affine(decode)
+        n_vars = 1 if self.field_index is None else int(vars_.shape[1])
+        sc = sc * n_vars if len(sc) == 1 else sc
+        of = of * n_vars if len(of) == 1 else of
+        if len(sc) != n_vars or len(of) != n_vars:
+            raise ValueError(f"decode needs one scale and one offset, or one per variable ({n_vars})")
+        return sc, of
+
+    def _decode_per_field(self, decode, vars_, n_fields):
+        """(scales, offsets) per program field; a coefficient field (JOREK's R) is never decoded."""
+        if decode is None:
+            return None
+        sc, of = self._affine_per_variable(decode, vars_)
+        idx = [0] if self.field_index is None else self.field_index
+        return ([sc[j] for j in idx] + [1.0] * (n_fields - len(idx)),
+                [of[j] for j in idx] + [0.0] * (n_fields - len(idx)))
+
+    def _decoded(self, vars_, decode, keep_graph=False):
+        """The explicit decode (one elementwise pass): what the fold replaces.  Used where the fold is not
+        defined -- boundary=True results (in the reference the shell cells see the zero padding of the DECODED
+        field) and gradient-carrying calls."""
+        sc, of = self._affine_per_variable(decode, vars_)
+        v = ops.to_cuda(vars_, keep_graph=keep_graph)
+        if self.field_index is None:
+            return v * sc[0] + of[0]
+        shape = (1, -1) + (1,) * (v.dim() - 2)
+        return (v * torch.tensor(sc, dtype=torch.float32, device=v.device).view(shape)
+                + torch.tensor(of, dtype=torch.float32, device=v.device).view(shape))
 
     # -- autograd (SURVEY 8 f-2) -----------------------------------------------------------
     def _needs_grad(self, vars_):
@@ -111,13 +158,18 @@ class ResidualProgram:
         return full.squeeze(2) if self.nd == 2 else full
 
     # -- the reference-facing call ------------------------------------------------------
-    def residual(self, vars_, boundary=False):
-        """The PDE residual; interior view (``[...,1:-1,1:-1(,1:-1)]``) unless boundary=True."""
+    def residual(self, vars_, boundary=False, decode=None):
+        """The PDE residual; interior view (``[...,1:-1,1:-1(,1:-1)]``) unless boundary=True.
+        ``decode`` = (scale, offset) -- scalars or one value per variable of ``vars`` -- or a MinMax-style
+        normaliser object: the residual of ``scale * vars + offset`` (``out_normalizer.decode(pred)``,
+        [ref: Joint/Wave_Residuals_CP.py:213-217]) with the decode folded into the kernel's loads."""
         staged = ops.Staged(vars_)
+        if decode is not None and (boundary or self._needs_grad(vars_)):
+            vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_):
             full = self._residual_autograd(vars_)
         else:
-            full = self._run(vars_)
+            full = self._run(vars_, decode=decode)
             if self.nd == 2:
                 full = full.squeeze(2)
         return staged.back(full if boundary else self._crop(full))
@@ -125,11 +177,14 @@ class ResidualProgram:
     __call__ = residual
 
     # -- fused epilogues ----------------------------------------------------------------
-    def abs_scores(self, vars_, ref=None, boundary=False, out=None):
+    def abs_scores(self, vars_, ref=None, boundary=False, out=None, decode=None):
         """|residual - ref| (the marginal nonconformity score) in one pass.  ``ref`` is a FULL
         residual field (boundary=True form) or None; ``out`` an optional caller-owned FULL-size
-        CUDA destination (e.g. a batch slice of a larger score tensor)."""
+        CUDA destination (e.g. a batch slice of a larger score tensor); ``decode`` as in ``residual``
+        (with ``out`` / boundary=True the shell cells of the full field are not those of the decoded field)."""
         staged = ops.Staged(vars_)
+        if decode is not None and ((boundary and out is None) or self._needs_grad(vars_) or ops.needs_grad(ref)):
+            vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref):
             full = self._residual_autograd(vars_)
             if ref is not None:
@@ -139,15 +194,18 @@ class ResidualProgram:
                 raise ValueError("out= cannot be combined with a gradient-carrying call")
             return staged.back(full if boundary else self._crop(full))
         r = None if ref is None else self._unsq(ops.to_cuda(ref))
-        full = self._run(vars_, flags=L.FLAG_ABS, ref=r, out=self._unsq(out))
+        full = self._run(vars_, decode=decode, flags=L.FLAG_ABS, ref=r, out=self._unsq(out))
         if self.nd == 2:
             full = full.squeeze(2)
         return staged.back(full if boundary else self._crop(full))
 
-    def joint_scores(self, vars_, inv_modulation=None, ref=None, interior=True, reduce="max"):
+    def joint_scores(self, vars_, inv_modulation=None, ref=None, interior=True, reduce="max", decode=None):
         """Per-sample reduce over cells of |residual - ref| * inv_modulation; only [BS] floats
-        are written.  ``inv_modulation`` / ``ref`` are FULL-size ([Nt,Nx(,Ny)] / [BS,Nt,...])."""
+        are written.  ``inv_modulation`` / ``ref`` are FULL-size ([Nt,Nx(,Ny)] / [BS,Nt,...]);
+        ``decode`` as in ``residual`` (folded when ``interior``)."""
         staged = ops.Staged(vars_)
+        if decode is not None and (not interior or self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation)):
+            vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation):
             v = self.abs_scores(vars_, ref=ref, boundary=True)
             if inv_modulation is not None:
@@ -157,12 +215,12 @@ class ResidualProgram:
         w = None if inv_modulation is None else self._unsq(ops.to_cuda(inv_modulation))
         r = None if ref is None else self._unsq(ops.to_cuda(ref))
         flags = L.FLAG_ABS | (self._interior_flags() if interior else 0)
-        out = self._run(vars_, mode=L.EPI_SCORE, flags=flags, weight=w, ref=r,
+        out = self._run(vars_, decode=decode, mode=L.EPI_SCORE, flags=flags, weight=w, ref=r,
                         reduce=L.REDUCE_MAX if reduce == "max" else L.REDUCE_SUM)
         return staged.back(out)
 
 
-    def coverage_counts(self, vars_, q, half=None, centre=None, interior=True):
+    def coverage_counts(self, vars_, q, half=None, centre=None, interior=True, decode=None):
         """Per-sample number of cells with centre - q*half <= residual(vars) <= centre + q*half,
         int32 [BS]; neither the residual of ``vars_`` nor the prediction sets are written.
         ``half`` ([Nt,Nx(,Ny)], e.g. qhat per cell with q=1, or the modulation with q=qhat) and
@@ -170,12 +228,14 @@ class ResidualProgram:
         With ``interior`` the shell cells the reference crops are not counted
         [ref: Marginal/NS_Residuals_CP.py:311-312,336-337; Joint/NS_Residuals_CP.py:312,336]."""
         staged = ops.Staged(vars_)
+        if decode is not None and not interior:
+            vars_, decode = self._decoded(vars_, decode), None
         w = None if half is None else self._unsq(ops.to_cuda(half))
         r = None if centre is None else self._unsq(ops.to_cuda(centre))
         # q: Python float, or the one-element device tensor a device-side quantile returned (the
         # kernel reads it itself: no host round trip between calibrate and coverage)
         band = q if isinstance(q, torch.Tensor) and q.is_cuda else float(q)
-        out = self._run(vars_, mode=L.EPI_COVER, flags=self._interior_flags() if interior else 0,
+        out = self._run(vars_, decode=decode, mode=L.EPI_COVER, flags=self._interior_flags() if interior else 0,
                         weight=w, ref=r, band_q=band)
         return staged.back(out)
 

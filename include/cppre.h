@@ -85,6 +85,9 @@ enum {
 typedef struct cppre_field {
     const float* d_data;
     int64_t stride[4]; /* elements, order [B, N2, N1, N0] */
+    /* CPPRE_FLAG_DECODE: the program sees scale * x + offset instead of the stored x (the surrogate's output
+     * normaliser, out_normalizer.decode, folded into the load; ignored without the flag). */
+    float scale, offset;
 } cppre_field_t;
 
 typedef struct cppre_program {
@@ -123,6 +126,15 @@ enum {
     CPPRE_FLAG_INTERIOR_0 = 2, /* axis N0 */
     CPPRE_FLAG_INTERIOR_1 = 4, /* axis N1 */
     CPPRE_FLAG_INTERIOR_2 = 8, /* axis N2 */
+    /* Normaliser-decode fold: every field is decoded as scale_f * x + offset_f before the
+     * program reads it -- `pred = out_normalizer.decode(pred)` directly upstream of the residual call,
+     * Joint/Wave_Residuals_CP.py:213-217, Tests/test_ns.py:134 -- without a pass over the tensor: a derivative
+     * slot of the decoded field is scale_f * D(x) + offset_f * sum(taps) wherever the whole stencil lies inside
+     * the field, and raw field factors are decoded at the output cell.  Results are those of the decoded field
+     * on the INTERIOR (the cells the reference keeps, [...,1:-1,1:-1,1:-1]); cells whose stencil reaches into
+     * the zero padding see the padding of the STORED field (zeros before the decode) and are unspecified:
+     * crop them (STORE) or set the INTERIOR flags (SCORE / COVER).  fp32 fields only. */
+    CPPRE_FLAG_DECODE = 32,
     /* bf16-input mode: every cppre_field_t::d_data points to bfloat16 elements (strides in
      * elements), staged as bf16 and widened to fp32 in the kernel; arithmetic, reference, weight
      * and every output stay fp32.  Halves the field bytes read (NS momentum STORE: 16 -> 10 B per

@@ -1,9 +1,12 @@
 """Import the UNMODIFIED reference (TEST INFRASTRUCTURE; build container only).
 
-``/root/reference`` exists only where the repo is built, never on the GPU box, so nothing
-that runs there (``-m gpu`` tests, ``smoke()``, ``bench.py``) may call this module.  It is
-used by ``oracle/make_golden.py`` to pin the NumPy restatement against the reference's own
-outputs, and by ``tests/test_oracle_vs_reference.py`` (skipped when the path is absent).
+``/root/reference`` exists only where the repo is built, never on the GPU box.  There the
+only source is ``oracle/_ref/reference_hotpath.zip`` -- the byte-for-byte snapshot of the hot-path
+modules that ``oracle/make_ref_snapshot.py`` packs at build time (git-ignored, it travels with
+the working tree) -- which is unpacked into a temporary directory and imported the same way.
+Used by ``oracle/make_golden.py`` to pin the NumPy restatement against the reference's own
+outputs, and by ``oracle/ref_arm.py`` (the timed CPU arm of ``bench.py``).  GPU tests and
+``smoke()`` never call it.
 
 Recipe: matplotlib is not installed, and two reference modules import
 it at module level (Utils/ConvOps_1d.py:314, Utils/boundary_conditions.py:4), so stub
@@ -20,17 +23,46 @@ import types
 import warnings
 
 REFERENCE_ROOT = os.environ.get("CPPRE_REFERENCE_ROOT", "/root/reference")
+_ARCHIVE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "reference_hotpath.zip")
+_unpacked = None
+
+
+def _root() -> str | None:
+    """The reference checkout, else the unpacked build-time snapshot, else None."""
+    global _unpacked
+    if os.path.isdir(os.path.join(REFERENCE_ROOT, "Utils")):
+        return REFERENCE_ROOT
+    if _unpacked is None and os.path.exists(_ARCHIVE):
+        import atexit
+        import shutil
+        import tempfile
+        import zipfile
+        from .make_ref_snapshot import verify
+        verify(_ARCHIVE)
+        d = tempfile.mkdtemp(prefix="cppre_ref_")
+        atexit.register(shutil.rmtree, d, ignore_errors=True)
+        with zipfile.ZipFile(_ARCHIVE) as z:
+            z.extractall(d)
+        _unpacked = d
+    return _unpacked
+
+
+def source() -> str:
+    """Where ``load()`` takes the reference from: "checkout", "snapshot" or "absent"."""
+    r = _root()
+    return "absent" if r is None else ("checkout" if r == REFERENCE_ROOT else "snapshot")
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REFERENCE_ROOT, "Utils"))
+    return _root() is not None
 
 
 def load():
     """Returns a namespace with the reference modules.  Our own drop-in mirrors use the same
     module names, so any of those already imported are evicted first."""
-    if not available():
-        raise RuntimeError(f"reference checkout not found at {REFERENCE_ROOT}")
+    root = _root()
+    if root is None:
+        raise RuntimeError(f"no reference checkout at {REFERENCE_ROOT} and no snapshot at {_ARCHIVE}")
     for name in ("matplotlib", "matplotlib.pyplot"):
         if name not in sys.modules:
             sys.modules[name] = types.ModuleType(name)
@@ -42,7 +74,7 @@ def load():
              "Other_UQ.Evaluation.PRE_estimations"]
     saved = {n: sys.modules.pop(n) for n in names if n in sys.modules}
     old_path = list(sys.path)
-    sys.path[:0] = [REFERENCE_ROOT, os.path.join(REFERENCE_ROOT, "Utils")]
+    sys.path[:0] = [root, os.path.join(root, "Utils")]
     ns = types.SimpleNamespace()
     try:
         with warnings.catch_warnings():
@@ -61,7 +93,7 @@ def load():
             # PRE_estimations lives in a directory without __init__.py: load by path.
             spec = importlib.util.spec_from_file_location(
                 "_ref_PRE_estimations",
-                os.path.join(REFERENCE_ROOT, "Other_UQ", "Evaluation", "PRE_estimations.py"))
+                os.path.join(root, "Other_UQ", "Evaluation", "PRE_estimations.py"))
             mod = importlib.util.module_from_spec(spec)
             spec.loader.exec_module(mod)
             ns.PRE_estimations = mod

@@ -676,3 +676,88 @@ def test_autograd_through_nonlinear_programs_kernel_tensor_and_spectral_paths():
     x = torch.randn(2, 6, 8, 10, device="cuda", requires_grad=True)
     o["D_x"].differentiate(x, correlation=True).sum().backward()
     assert x.grad is not None and float(x.grad.abs().sum()) > 0
+
+
+class _MinMax:
+    """Shape of the normaliser the scripts use: attributes a, b; decode(x) = (x - b) / a
+    [ref: Tests/test_ns.py:111-134; class in the un-vendored Neural_PDE package]."""
+
+    def __init__(self, a, b):
+        self.a, self.b = torch.tensor(a), torch.tensor(b)
+
+
+def test_normaliser_decode_fold_equals_the_residual_of_the_decoded_field():
+    """SURVEY.md section 8 (f-1), second half: ``pred = out_normalizer.decode(pred)`` directly upstream of the
+    residual call [ref: Joint/Wave_Residuals_CP.py:213-217] is folded into K1 -- no pass over the tensor.
+    Parity: against the ORACLE evaluated on the explicitly decoded field (fp32), interior cells, 1e-5 of
+    max|ref|; on all three kernels (TMA, t-innermost, generic), every epilogue, per-variable and scalar
+    coefficients, a MinMax-style object; boundary=True takes the explicit decode and equals it bit for bit."""
+    import bench
+    o, n = _programs_2d(), synth.NS
+    ns = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
+    sc, of = [2.0, 0.5, 3.0], [0.3, -0.2, 1.0]
+    for shape, path in (((3, 12, 16, 128), "tma"), ((2, 8, 9, 30), "generic")):
+        enc = synth.fields(5, 3, shape)
+        dec = (enc * np.asarray(sc, np.float32).reshape(1, 3, 1, 1, 1) + np.asarray(of, np.float32).reshape(1, 3, 1, 1, 1)).astype(np.float32)
+        want = O.residual_ns_momentum(dec[:, 0], dec[:, 1], dec[:, 2], n["dx"], n["dy"], n["dt"], n["nu"])[:, 1:-1, 1:-1, 1:-1]
+        got = ns.residual(cuda(enc), decode=(sc, of))
+        assert L.last_path() == path
+        assert_close_rel(got.cpu().numpy(), want, TOL)
+        if path == "tma":
+            vt = _tin(cuda(enc))
+            got_t = ns.residual(vt, decode=(sc, of))
+            assert L.last_path() == "tin"
+            assert_close_rel(got_t.cpu().numpy(), want, TOL)
+        # the explicit form (boundary=True) is what the fold replaces: identical to decoding by hand
+        full = ns.residual(cuda(enc), boundary=True, decode=(sc, of))
+        by_hand = ns.residual(cuda(enc) * torch.tensor(sc, device="cuda").view(1, 3, 1, 1, 1)
+                              + torch.tensor(of, device="cuda").view(1, 3, 1, 1, 1), boundary=True)
+        assert torch.equal(full, by_hand)
+        assert_close_rel(full[:, 1:-1, 1:-1, 1:-1].cpu().numpy(), want, TOL)
+        # fused epilogues with the fold against the same epilogues on the decoded tensor
+        dec_t = cuda(dec)
+        w = torch.rand(shape[1:], device="cuda") + 0.1
+        a = ns.joint_scores(cuda(enc), inv_modulation=w, decode=(sc, of))
+        b = ns.joint_scores(dec_t, inv_modulation=w)
+        assert torch.allclose(a, b, rtol=1e-4, atol=0), (a, b)
+        q = float(np.quantile(np.abs(want), 0.8))
+        ca = ns.coverage_counts(cuda(enc), q, decode=(sc, of))
+        cb = ns.coverage_counts(dec_t, q)
+        assert int((ca - cb).abs().max()) <= max(2, int(1e-3 * want[0].size)), (ca, cb)
+        sa = ns.abs_scores(cuda(enc), decode=(sc, of))
+        assert_close_rel(sa.cpu().numpy(), np.abs(want), TOL)
+    # MHD momentum (6 variables, division by the decoded density) on the TMA and t-innermost kernels
+    mhd = bench.make_program("mhd", "momentum")
+    enc = synth.fields(9, 6, (2, 8, 16, 128), positive=(0, 3))
+    sc6, of6 = [1.5, 2.0, 0.5, 2.5, 1.0, 3.0], [0.25, 0.1, -0.3, 0.5, 0.0, 0.2]
+    dec = (enc * np.asarray(sc6, np.float32).reshape(1, 6, 1, 1, 1) + np.asarray(of6, np.float32).reshape(1, 6, 1, 1, 1)).astype(np.float32)
+    want = O.residual_mhd("momentum", *(dec[:, j] for j in range(6)), synth.MHD["gamma"])[:, 1:-1, 1:-1, 1:-1]
+    got = mhd.residual(cuda(enc), decode=(sc6, of6))
+    assert L.last_path() == "tma"
+    assert_close_rel(got.cpu().numpy(), want, TOL)
+    got = mhd.residual(_tin(cuda(enc)), decode=(sc6, of6))
+    assert L.last_path() == "tin"
+    assert_close_rel(got.cpu().numpy(), want, TOL)
+    # single-field linear operator (wave), scalar coefficients and the MinMax-object form: (x - b) / a
+    wave = bench.make_program("wave")
+    u = synth.fields(3, 1, (2, 10, 16, 128))[:, 0]
+    nrm = _MinMax(0.25, -0.5)
+    dec = ((u - np.float32(-0.5)) / np.float32(0.25)).astype(np.float32)
+    want = O.correlate(dec, O.build_kernel("2d", "t", 2) - np.float32(synth.WAVE["c2"]) * O.build_kernel("2d", ("x", "y"), 2))[:, 1:-1, 1:-1, 1:-1]
+    got = wave.residual(cuda(u), decode=nrm)
+    assert L.last_path() == "tma"
+    assert_close_rel(got.cpu().numpy(), want, TOL)
+    # 1-D + time (batch-rows TMA mode): Burgers with a scalar decode
+    import ConvOps_1d as C1
+    b = synth.BURGERS
+    bur = programs.burgers(C1.ConvOperator("t", 1), C1.ConvOperator("x", 1), C1.ConvOperator("x", 2), b["dx"], b["dt"], b["nu"])
+    u1 = synth.fields(4, 1, (16, 12, 128))[:, 0]
+    dec = (u1 * np.float32(1.7) + np.float32(0.4)).astype(np.float32)
+    want = O.residual_burgers(dec, b["dx"], b["dt"], b["nu"])[:, 1:-1, 1:-1]
+    got = bur.residual(cuda(u1), decode=(1.7, 0.4))
+    assert L.last_path() == "tma"
+    assert_close_rel(got.cpu().numpy(), want, TOL)
+    with pytest.raises(ValueError):
+        ns.residual(cuda(synth.fields(5, 3, (1, 6, 8, 8))), decode=([1.0, 2.0], [0.0, 0.0]))     # 2 scales, 3 variables
+    with pytest.raises(NotImplementedError):
+        ns.residual(cuda(synth.fields(5, 3, (1, 6, 8, 128))).bfloat16(), decode=(1.0, 0.0))

@@ -44,7 +44,7 @@ def test_abi_struct_layout_matches_header_constants():
     for name, val in (("CPPRE_MAX_FIELDS", L.MAX_FIELDS), ("CPPRE_MAX_SLOTS", L.MAX_SLOTS),
                       ("CPPRE_MAX_SCALARS", L.MAX_SCALARS), ("CPPRE_MAX_TAPS", L.MAX_TAPS)):
         assert int(re.search(rf"#define {name} (\d+)", header).group(1)) == val
-    assert C.sizeof(L.Field) == 8 + 32
+    assert C.sizeof(L.Field) == 8 + 32 + 8      # d_data, stride[4], scale + offset (decode fold)
     assert C.sizeof(L.Program) == 12 + 4 + 72 + 72 + 48 + 48     # kind..n_slots (+pad), ksize, pad, taps, scalars
     assert C.sizeof(L.BC) == 48
 

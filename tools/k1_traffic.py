@@ -1,0 +1,57 @@
+"""ncu raw CSV (`ncu -i X.ncu-rep --page raw --csv`) -> profiles/k1_traffic_<workload>[_<equation>].json, the file
+bench.py's `roofline.traffic` is read from.  The record carries the fingerprint of the K1 sources it was
+captured from (bench.kernel_source_sha): bench.py reports the traffic only while the kernel is unchanged.
+
+    python tools/k1_traffic.py gpurun_out/r2e_prof_raw.csv ns
+    python tools/k1_traffic.py gpurun_out/r2e_prof_mhd_raw.csv mhd momentum
+"""
+import csv
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+
+def to_bytes(v, unit):
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[unit]
+    return float(v.replace(",", "")) * mult
+
+
+def main(path, workload, equation=None):
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    w = bench.WORKLOADS[workload]
+    nf = bench.MHD_EQUATIONS[equation] if workload == "mhd" else w["nf"]
+    rec = None
+    for r in rows[2:]:
+        name = r[col["Kernel Name"]]
+        if "star_kernel" not in name:
+            continue
+        rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
+        wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
+        if wr < 0.05 * rd:          # a COVER / SCORE launch: nothing written
+            continue
+        grid = int(r[col["launch__grid_size"]].replace(",", ""))
+        ms = float(r[col["gpu__time_duration.sum"]].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(
+            units[col["gpu__time_duration.sum"]], 1e-6)
+        rec = {"kernel": name[:160], "workload": workload, "grid": grid, "dram_bytes_read": rd, "dram_bytes_write": wr,
+               "ncu_duration_ms": ms}
+        break
+    assert rec is not None, "no STORE launch of star_kernel in the capture"
+    # algorithmic bytes of the captured launch: (4F + 4) B per point; points from the written bytes (4 B per point)
+    points = round(rec["dram_bytes_write"] / 4 / 1e3) * 1e3
+    rec["algorithmic_bytes"] = (4 * nf + 4) * points
+    rec["points_estimated_from_written_bytes"] = points
+    rec["kernel_source_sha"] = bench.kernel_source_sha()
+    rec["source"] = f"ncu --set full --clock-control none, {os.path.basename(path)} (first STORE launch of star_kernel)"
+    name = f"k1_traffic_{workload}" + (f"_{equation}" if workload == "mhd" else "") + ".json"
+    json.dump(rec, open(os.path.join(ROOT, "profiles", name), "w"), indent=1)
+    print(json.dumps(rec))
+
+
+if __name__ == "__main__":
+    main(*sys.argv[1:])
