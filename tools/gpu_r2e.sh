@@ -28,6 +28,8 @@ timeout 900 ncu --set full --clock-control none --import-source on --profile-fro
 echo "ncu mhd exit $?"
 ncu -i $O/${TAG}_prof_mhd.ncu-rep --page raw --csv > $O/${TAG}_prof_mhd_raw.csv 2>/dev/null
 python tools/ncu_summary.py $O/${TAG}_prof_mhd_raw.csv > $O/${TAG}_prof_mhd_summary.txt 2>&1
+timeout 300 python tools/generic_bench.py > $O/${TAG}_generic_bench.json 2> $O/${TAG}_generic_bench.err; echo "generic bench exit $?"; cat $O/${TAG}_generic_bench.json | cut -c1-2500; tail -3 $O/${TAG}_generic_bench.err
+timeout 300 python tools/k3_sweep.py 256,512,2048,4096 > $O/${TAG}_k3_sweep.jsonl 2> $O/${TAG}_k3_sweep.err; echo "k3 sweep exit $?"; cat $O/${TAG}_k3_sweep.jsonl
 for w in burgers wave-joint; do
   timeout 600 python bench.py --workload $w --steps 20 --warmup 3 > $O/${TAG}_bench_$w.json 2> $O/${TAG}_bench_$w.err; echo "bench $w exit $?"
 done
