@@ -74,7 +74,13 @@ def load():
              "Other_UQ.Evaluation.PRE_estimations"]
     saved = {n: sys.modules.pop(n) for n in names if n in sys.modules}
     old_path = list(sys.path)
-    sys.path[:0] = [root, os.path.join(root, "Utils")]
+    # The drop-in mirror (cp_pre_b200.install()) uses the SAME module names and its ``Utils`` is a regular package,
+    # which would win over the reference's namespace package wherever it sits on sys.path: take the mirror's
+    # directories off the path while the reference is imported.
+    mirror = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cp_pre_b200")
+    sys.path[:] = [root, os.path.join(root, "Utils")] + [
+        p for p in old_path if not os.path.abspath(p or ".").startswith(mirror)]
+    importlib.invalidate_caches()
     ns = types.SimpleNamespace()
     try:
         with warnings.catch_warnings():
@@ -97,6 +103,9 @@ def load():
             mod = importlib.util.module_from_spec(spec)
             spec.loader.exec_module(mod)
             ns.PRE_estimations = mod
+        for m in (ns.ConvOps_2d, ns.ConvOps_1d, ns.ConvOps_0d, ns.ConvOps_Spatial, ns.boundary_conditions, ns.fft_conv):
+            if not os.path.abspath(m.__file__).startswith(os.path.abspath(root)):
+                raise RuntimeError(f"{m.__name__} resolved to {m.__file__}, not to the reference under {root}")
     finally:
         sys.path[:] = old_path
         for n in names:
