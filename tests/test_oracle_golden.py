@@ -1,12 +1,14 @@
 """The NumPy oracle against outputs of the unmodified reference (tests/golden, written by
 oracle/make_golden.py).  CPU only."""
 import ast
+import os
 
 import numpy as np
 import pytest
 
 from conftest import assert_close_rel, load_golden
 from oracle import cpu_oracle as O
+from oracle import synth
 
 
 def _parse_key(key):
@@ -299,3 +301,45 @@ def test_jorek_residuals_against_reference_golden():
     for eq, coef in (("continuity", 3.4), ("temperature", 2.25 * 1e-7)):
         got = O.residual_jorek(eq, v[:, 0], v[:, 1], v[:, 2], g["R"], coef, ops=o)
         assert_close_rel(got, g[eq], 1e-5, eq)
+
+
+def test_reference_arm_runs_the_reference_own_code_and_equals_the_port():
+    """bench.py's CPU arm (oracle/ref_arm.py): the operators come from the reference's own modules and the
+    residual functions are the scripts' own ``def residual*`` statements, lifted from the syntax tree -- from the
+    checkout in the build container, from the byte-for-byte snapshot (oracle/_ref/reference_hotpath.zip, packed by
+    oracle/make_ref_snapshot.py at build time) elsewhere.  They must (a) not resolve to the drop-in mirror even when
+    it is installed under the same module names, (b) equal oracle/torch_port.py bit for bit on every workload."""
+    import torch
+    from oracle import make_ref_snapshot, ref_arm, ref_shim, torch_port as TP
+    if not ref_arm.available():
+        pytest.skip("neither /root/reference nor oracle/_ref/reference_hotpath.zip is present")
+    if os.path.exists(make_ref_snapshot.ARCHIVE):
+        manifest = make_ref_snapshot.verify()
+        assert set(manifest["files"]) == set(make_ref_snapshot.FILES)
+    import cp_pre_b200
+    cp_pre_b200.install()
+    import Utils.ConvOps_2d as mirror
+    cases = [("ns", "momentum", 3, (2, 6, 16, 16)), ("wave-joint", "", 1, (2, 6, 16, 16)), ("burgers", "", 1, (3, 8, 32))]
+    cases += [("mhd", eq, 6, (2, 6, 16, 16)) for eq in ("continuity", "momentum", "energy", "induction", "gauss")]
+    for wl, eq, nf, shape in cases:
+        v = torch.from_numpy(synth.fields(3, nf, shape, positive=(0, 3) if wl == "mhd" else ()))
+        v = v[:, 0] if nf == 1 else v
+        got = ref_arm.residual_function(wl, eq)(v)
+        if wl == "ns":
+            want = TP.ns_momentum(v, synth.NS["dx"], synth.NS["dy"], synth.NS["dt"], synth.NS["nu"])
+        elif wl == "mhd":
+            want = TP.mhd(eq, v, synth.MHD["gamma"])
+        elif wl == "burgers":
+            want = TP.burgers(v, synth.BURGERS["dx"], synth.BURGERS["dt"], synth.BURGERS["nu"])
+        else:
+            want = TP.wave(v, synth.WAVE["c2"])
+        assert torch.equal(got, want), (wl, eq)
+    ns = ref_arm._ns
+    assert ns.ConvOps_2d.ConvOperator is not mirror.ConvOperator
+    assert ns.PRE_estimations.ConvOperator is ns.ConvOps_2d.ConvOperator
+    root = os.path.abspath(ref_shim._root())
+    assert os.path.abspath(ns.ConvOps_2d.__file__).startswith(root)
+    import Utils.ConvOps_2d as again            # the mirror is back in place afterwards
+    assert again is mirror
+    adv = ref_arm.residual_function("advection")
+    assert tuple(adv(torch.randn(4, 10, 197)).shape) == (4, 8, 195)
