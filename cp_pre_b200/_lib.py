@@ -30,6 +30,7 @@ REDUCE_MAX, REDUCE_SUM = 0, 1
 FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16, FLAG_DECODE = 1, 2, 4, 8, 16, 32
 PATH_AUTO, PATH_GENERIC, PATH_TMA, PATH_TIN = 0, 1, 2, 3
 
+WALL_TOP, WALL_BOTTOM, WALL_LEFT, WALL_RIGHT = range(4)
 BC_DIRICHLET, BC_NEUMANN, BC_PERIODIC, BC_SYMMETRIC, BC_NONE = range(5)
 SPEC_CONJ_FIRST, SPEC_INVERSE, SPEC_CONJ_LAST = 1, 2, 4
 
@@ -99,6 +100,7 @@ SIGNATURES = {
     "cppre_bc_pad": (C.c_int, [_P, _I64, _I64, _I64, C.POINTER(BC), _P, _P]),
     "cppre_bc_conv2d": (C.c_int, [_P, _I64, _I64, _I64, C.POINTER(BC), C.POINTER(C.c_float), C.c_int32,
                                   C.c_int32, _P, _P]),
+    "cppre_edge_difference": (C.c_int, [_P, _I64, _I64, _I64, _I64, _I64, _I64, C.c_int32, C.c_float, _P, _P]),
     "cppre_spectral_pointwise": (C.c_int, [_P, _P, _I64, _I64, C.c_int32, C.c_float, _P, _P]),
 }
 

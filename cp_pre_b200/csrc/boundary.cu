@@ -146,6 +146,19 @@ int grid_for(int64_t total) {
     return (int)(b < 1 ? 1 : b);
 }
 
+// Edge-value residual of a periodic boundary: out[img, j] = (u[img, wall line, j] - u[img, opposite line, j]) * scale,
+// subtraction and scaling rounded separately like the reference's `(u[...,-1] - u[...,0]) * dx`
+// [ref: Joint/NS_Residuals_CP.py:483-494].
+__global__ void __launch_bounds__(kThreads)
+edge_difference_kernel(const float* __restrict__ u, float* __restrict__ out, int64_t total, int64_t len, int64_t s_img,
+                       int64_t s_along, int64_t off_a, int64_t off_b, float scale) {
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kThreads) {
+        const int64_t img = i / len, j = i - img * len;
+        const float* base = u + img * s_img + j * s_along;
+        out[i] = __fmul_rn(__fsub_rn(__ldg(base + off_a), __ldg(base + off_b)), scale);
+    }
+}
+
 }  // namespace
 }  // namespace cppre
 
@@ -224,6 +237,27 @@ int cppre_bc_conv2d(const float* d_in, int64_t n_img, int64_t h, int64_t w, cons
     if (total == 0) return CPPRE_OK;
     CPPRE_REQUIRE(d_in && d_out, CPPRE_ERR_BAD_ARG, "null pointer");
     bc_conv2d_kernel<<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>(d_in, d_out, p);
+    CPPRE_CHECK_LAUNCH();
+    return CPPRE_OK;
+}
+
+int cppre_edge_difference(const float* d_u, int64_t n_img, int64_t h, int64_t w, int64_t s_img, int64_t s_row,
+                          int64_t s_col, int32_t wall, float scale, float* d_out, void* stream) {
+    CPPRE_REQUIRE(n_img >= 0 && h >= 0 && w >= 0, CPPRE_ERR_BAD_ARG, "bad argument");
+    CPPRE_REQUIRE(wall >= CPPRE_WALL_TOP && wall <= CPPRE_WALL_RIGHT, CPPRE_ERR_BAD_ARG, "unknown wall %d", wall);
+    const bool rows = wall == CPPRE_WALL_TOP || wall == CPPRE_WALL_BOTTOM;       // result runs along the columns
+    const int64_t len = rows ? w : h;
+    const int64_t total = n_img * len;
+    if (total == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(h >= 1 && w >= 1, CPPRE_ERR_BAD_ARG, "an edge difference needs at least one row and one column");
+    CPPRE_REQUIRE(d_u && d_out, CPPRE_ERR_BAD_ARG, "null pointer");
+    // first / last line of the axis the wall closes; minuend = the named wall's line, as the reference writes it
+    const int64_t first = 0, last = (rows ? h : w) - 1;
+    const int64_t line = rows ? s_row : s_col, along = rows ? s_col : s_row;
+    const bool named_is_first = wall == CPPRE_WALL_TOP || wall == CPPRE_WALL_LEFT;
+    const int64_t off_a = (named_is_first ? first : last) * line, off_b = (named_is_first ? last : first) * line;
+    edge_difference_kernel<<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>(d_u, d_out, total, len, s_img, along,
+                                                                                   off_a, off_b, scale);
     CPPRE_CHECK_LAUNCH();
     return CPPRE_OK;
 }

@@ -644,6 +644,25 @@ def bc_conv2d(x: torch.Tensor, bc: L.BC, kernel: np.ndarray) -> torch.Tensor:
     return out
 
 
+def edge_difference(u: torch.Tensor, wall: str, scale: float) -> torch.Tensor:
+    """(u[..., wall line] - u[..., opposite line]) * scale over the last two axes of a CUDA fp32 tensor (any view
+    whose leading axes flatten to one stride); [..., W] for 'top' / 'bottom', [..., H] for 'left' / 'right'."""
+    walls = {"top": L.WALL_TOP, "bottom": L.WALL_BOTTOM, "left": L.WALL_LEFT, "right": L.WALL_RIGHT}
+    if wall not in walls:
+        raise ValueError(f"unknown wall {wall!r}")
+    if u.dim() < 2:
+        raise IndexError("too many indices for tensor of dimension %d" % u.dim())
+    h, w = (int(v) for v in u.shape[-2:])
+    lead = tuple(u.shape[:-2])
+    n_img = int(np.prod(lead)) if lead else 1
+    flat = u.reshape(n_img, h, w)                      # a view whenever the leading axes flatten to one stride
+    out = torch.empty(lead + ((w,) if wall in ("top", "bottom") else (h,)), dtype=torch.float32, device=u.device)
+    with torch.cuda.device(u.device):
+        L.check(L.load().cppre_edge_difference(_ptr(flat), n_img, h, w, flat.stride(0), flat.stride(1), flat.stride(2),
+                                               walls[wall], float(scale), _ptr(out), _stream(u.device)))
+    return out
+
+
 def spectral_pointwise(sig_hat: torch.Tensor, ker_hat: torch.Tensor, flags: int, eps: float = 1e-6):
     """sig_hat complex64 [B, ...], ker_hat complex64 [...]; returns sig_hat * g(ker_hat)."""
     lib = L.load()

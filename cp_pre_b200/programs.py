@@ -366,6 +366,17 @@ def jorek(equation, D_t, D_R, D_Z, D_RR, D_ZZ, R, coef, gamma=5 / 3):
     return prog
 
 
+def periodic_bc_residual(u, wall="right", dx=1.0):
+    """PRE over a periodic boundary: the edge-value difference ``(u[wall] - u[opposite wall]) * dx`` of a
+    [..., Nx, Ny] field (e.g. the vorticity ``w`` as [BS, Nt, Nx, Ny]) -> [..., Ny] ('top' / 'bottom') or
+    [..., Nx] ('left' / 'right'); the result goes through the same Joint CP helpers as any residual
+    [ref: Joint/NS_Residuals_CP.py:483-512].  An unknown wall raises like the reference (its ``res`` is unbound)."""
+    if wall not in ("top", "bottom", "left", "right"):
+        raise UnboundLocalError("cannot access local variable 'res' where it is not associated with a value")
+    staged = ops.Staged(u)
+    return staged.back(ops.edge_difference(ops.to_cuda(u), wall, _f(dx)))
+
+
 # ---------------------------------------------------------------------------------------
 # calibration pipelines
 # ---------------------------------------------------------------------------------------

@@ -386,6 +386,15 @@ int cppre_bc_pad(const float* d_in, int64_t n_img, int64_t h, int64_t w, const c
 int cppre_bc_conv2d(const float* d_in, int64_t n_img, int64_t h, int64_t w, const cppre_bc_t* bc,
                     const float* h_taps, int32_t kh, int32_t kw, float* d_out, void* stream);
 
+/* Edge-value residual of a periodic boundary: for every image u[img] (h rows x w columns, element strides s_img /
+ * s_row / s_col -- any view), out[img, :] = (u[named wall's line] - u[opposite line]) * scale, contiguous
+ * [n_img, w] for CPPRE_WALL_TOP / BOTTOM (rows 0 / h-1) and [n_img, h] for LEFT / RIGHT (columns 0 / w-1); the
+ * subtraction and the scaling are rounded separately, like the reference's tensor expression.
+ * replaces periodic_bc_residual(u, wall)   Joint/NS_Residuals_CP.py:483-494 (result fed to the Joint CP helpers) */
+enum { CPPRE_WALL_TOP = 0, CPPRE_WALL_BOTTOM = 1, CPPRE_WALL_LEFT = 2, CPPRE_WALL_RIGHT = 3 };
+int cppre_edge_difference(const float* d_u, int64_t n_img, int64_t h, int64_t w, int64_t s_img, int64_t s_row,
+                          int64_t s_col, int32_t wall, float scale, float* d_out, void* stream);
+
 /* ---- spectral path -------------------------------------------------------------------- */
 enum {
     CPPRE_SPEC_CONJ_FIRST = 1, /* K <- conj(K) before anything else (correlation) */

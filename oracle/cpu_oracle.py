@@ -434,6 +434,22 @@ def residual_jorek(equation, rho, phi, T, R, coef, gamma=5.0 / 3.0, ops=None):
     raise ValueError(equation)
 
 
+def periodic_bc_residual(u, wall="right", dx=1.0):
+    """[ref: Joint/NS_Residuals_CP.py:483-494] edge-value residual of a periodic boundary."""
+    u = np.asarray(u, dtype=F32)
+    if wall == "top":
+        res = u[..., 0, :] - u[..., -1, :]
+    elif wall == "bottom":
+        res = u[..., -1, :] - u[..., 0, :]
+    elif wall == "left":
+        res = u[..., :, 0] - u[..., :, -1]
+    elif wall == "right":
+        res = u[..., :, -1] - u[..., :, 0]
+    else:
+        raise UnboundLocalError(wall)
+    return (res * F32(dx)).astype(F32)
+
+
 def interior(res, nd):
     """[ref: Joint/Wave_Residuals_CP.py:184] strip one cell on each of the last nd axes."""
     return res[(Ellipsis,) + (slice(1, -1),) * nd]

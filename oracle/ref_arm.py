@@ -49,17 +49,17 @@ def source() -> str:
     return ref_shim.source()
 
 
-def _lift(script: str, namespace: dict, functions: set) -> dict:
+def _lift(script: str, namespace: dict, functions: set, operators: bool = True) -> dict:
     """Executes, in ``namespace``, the module-level statements of ``script`` that build the operators
     (assignments to the names in _OPERATOR_NAMES, incl. ``D.kernel = ...``) and the listed function
-    definitions -- in source order, untouched."""
+    definitions -- in source order, untouched.  ``operators=False`` lifts the functions only."""
     path = os.path.join(ref_shim._root(), script)
     tree = ast.parse(open(path).read(), filename=path)
     keep = []
     for node in tree.body:
         if isinstance(node, ast.FunctionDef) and node.name in functions:
             keep.append(node)
-        elif isinstance(node, ast.Assign) and len(node.targets) == 1:
+        elif operators and isinstance(node, ast.Assign) and len(node.targets) == 1:
             t = node.targets[0]
             name = t.id if isinstance(t, ast.Name) else (t.value.id if isinstance(t, ast.Attribute) and isinstance(t.value, ast.Name) else None)
             if name in _OPERATOR_NAMES:

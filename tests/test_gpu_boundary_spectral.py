@@ -135,3 +135,31 @@ def test_spectral_paths_against_reference_golden():
     sig, ker, bias = (torch.from_numpy(g[k]) for k in ("fc|sig", "fc|ker", "fc|bias"))
     assert_close_rel(fft_conv(sig, ker, bias=bias, padding="same").numpy(), g["fc|same"], tol)
     assert_close_rel(fft_conv(sig, ker, padding=2, stride=2).numpy(), g["fc|stride"], tol)
+
+
+def test_periodic_boundary_residual_is_bit_exact_on_views():
+    """[ref: Joint/NS_Residuals_CP.py:483-512] periodic_bc_residual: edge-value differences of the vorticity,
+    taken by the scripts on the t-innermost view ``pred[:, -1].permute(0, 3, 1, 2)``; bit-equal to the oracle on
+    contiguous tensors, permuted views and NumPy input, every wall; an unknown wall raises like the reference."""
+    from cp_pre_b200 import programs
+    rng = np.random.default_rng(5)
+    raw = rng.standard_normal((3, 4, 9, 11, 6)).astype(np.float32)            # [BS, var, Nx, Ny, Nt]
+    w_np = np.ascontiguousarray(raw[:, -1].transpose(0, 3, 1, 2))            # logical [BS, Nt, Nx, Ny]
+    w_view = torch.from_numpy(raw).cuda()[:, -1].permute(0, 3, 1, 2)
+    assert not w_view.is_contiguous()
+    for wall in ("top", "bottom", "left", "right"):
+        want = O.periodic_bc_residual(w_np, wall, 0.01)
+        got = programs.periodic_bc_residual(w_view, wall, 0.01)
+        assert got.is_cuda and np.array_equal(got.cpu().numpy(), want), wall
+        got = programs.periodic_bc_residual(torch.from_numpy(w_np).cuda(), wall, torch.tensor(0.01))
+        assert np.array_equal(got.cpu().numpy(), want), wall
+        got = programs.periodic_bc_residual(w_np, wall, np.asarray(0.01))
+        assert isinstance(got, np.ndarray) and np.array_equal(got, want), wall
+    with pytest.raises(UnboundLocalError):
+        programs.periodic_bc_residual(w_view, "front")
+    # the result goes through the Joint CP helpers like any residual (:505-512)
+    from Neural_PDE.UQ.inductive_cp import modulation_func, ncf_metric_joint
+    res = programs.periodic_bc_residual(w_np, "right", 0.01)
+    mod = modulation_func(res, np.zeros(res.shape))
+    sc = ncf_metric_joint(res, np.zeros(res.shape), mod)
+    np.testing.assert_allclose(sc, O.ncf_metric_joint(res, np.zeros(res.shape), O.modulation_func(res, np.zeros(res.shape))), rtol=2e-6)

@@ -343,3 +343,19 @@ def test_reference_arm_runs_the_reference_own_code_and_equals_the_port():
     assert again is mirror
     adv = ref_arm.residual_function("advection")
     assert tuple(adv(torch.randn(4, 10, 197)).shape) == (4, 8, 195)
+
+
+def test_periodic_boundary_residual_against_the_script_function():
+    """[ref: Joint/NS_Residuals_CP.py:483-494] -- the oracle's restatement against the script's own function
+    (lifted from its syntax tree like the residual functions of the CPU arm), all four walls, bit for bit."""
+    import torch
+    from oracle import ref_arm, ref_shim
+    if not ref_arm.available():
+        pytest.skip("no reference checkout / snapshot")
+    env = {"torch": torch, "np": np, "dx": 0.01}
+    ref_arm._lift("Joint/NS_Residuals_CP.py", env, {"periodic_bc_residual"}, operators=False)
+    u = np.random.default_rng(3).standard_normal((3, 5, 6, 7)).astype(np.float32)
+    for wall in ("top", "bottom", "left", "right"):
+        want = env["periodic_bc_residual"](torch.from_numpy(u), wall).numpy()
+        got = O.periodic_bc_residual(u, wall, 0.01)
+        assert got.dtype == np.float32 and np.array_equal(got, want), wall
