@@ -28,7 +28,7 @@ PROGRAM_SLOTS = {PROG_LINEAR: 1, PROG_BURGERS: 3, PROG_NS_CONTINUITY: 2, PROG_NS
 EPI_STORE, EPI_SCORE, EPI_COVER = 0, 1, 2
 REDUCE_MAX, REDUCE_SUM = 0, 1
 FLAG_ABS, FLAG_INTERIOR_0, FLAG_INTERIOR_1, FLAG_INTERIOR_2, FLAG_IN_BF16, FLAG_DECODE = 1, 2, 4, 8, 16, 32
-PATH_AUTO, PATH_GENERIC, PATH_TMA, PATH_TIN = 0, 1, 2, 3
+PATH_AUTO, PATH_GENERIC, PATH_TMA, PATH_TIN, PATH_FLAT = 0, 1, 2, 3, 4
 
 WALL_TOP, WALL_BOTTOM, WALL_LEFT, WALL_RIGHT = range(4)
 BC_DIRICHLET, BC_NEUMANN, BC_PERIODIC, BC_SYMMETRIC, BC_NONE = range(5)

@@ -197,7 +197,7 @@ int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
         return CPPRE_OK;
     }
     CPPRE_REQUIRE(path == CPPRE_PATH_AUTO || path == CPPRE_PATH_GENERIC || path == CPPRE_PATH_TMA ||
-                      path == CPPRE_PATH_TIN, CPPRE_ERR_BAD_ARG, "unknown path %d", path);
+                      path == CPPRE_PATH_TIN || path == CPPRE_PATH_FLAT, CPPRE_ERR_BAD_ARG, "unknown path %d", path);
     if (path == CPPRE_PATH_TIN || (path == CPPRE_PATH_AUTO && tin_eligible(prog, P))) {
         CPPRE_REQUIRE(tin_eligible(prog, P), CPPRE_ERR_UNSUPPORTED,
                       "request does not qualify for the t-innermost star kernel");
@@ -209,12 +209,20 @@ int cppre_residual(const cppre_program_t* prog, const int64_t shape[4],
     const int ok = tma_eligible(prog, P);
     if (path == CPPRE_PATH_TMA)
         CPPRE_REQUIRE(ok, CPPRE_ERR_UNSUPPORTED, "request does not qualify for the TMA star kernel");
-    if (ok && path != CPPRE_PATH_GENERIC) {
+    if (ok && path != CPPRE_PATH_GENERIC && path != CPPRE_PATH_FLAT) {
         set_path("tma");
         rc = launch_tma(prog, P, st);
         // the driver may still refuse an exotic stride pattern when encoding the tensor map;
         // nothing has been launched in that case, so AUTO takes the generic kernel instead
         if (rc != CPPRE_ERR_UNSUPPORTED || path == CPPRE_PATH_TMA) return rc;
+    }
+    // contiguous star requests the TMA unit cannot stage (rows that are not a multiple of 16 bytes, unaligned
+    // bases): the flat-line star kernel, before the one-thread-per-cell generic kernel
+    if (path == CPPRE_PATH_FLAT || (path == CPPRE_PATH_AUTO && flat_eligible(prog, P))) {
+        CPPRE_REQUIRE(flat_eligible(prog, P), CPPRE_ERR_UNSUPPORTED,
+                      "request does not qualify for the flat-line star kernel (contiguous 3x3x3 star programs)");
+        set_path("flat");
+        return launch_flat(prog, P, st);
     }
     CPPRE_REQUIRE(!P.in_bf16, CPPRE_ERR_UNSUPPORTED,
                   "bf16 fields are served by the TMA star kernel only (star stencils, 'same' padding, N0 %% 8 == 0, "

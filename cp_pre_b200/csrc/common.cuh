@@ -177,6 +177,19 @@ inline int launch_tin(const cppre_program_t* prog, const Prepared& P, cudaStream
     return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store(prog, P, stream)
          : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score(prog, P, stream) : launch_tin_cover(prog, P, stream);
 }
+#define CPPRE_FLAT_TU(sfx)                                                   \
+    int flat_eligible_##sfx(const cppre_program_t* prog, const Prepared& P); \
+    int launch_flat_##sfx(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
+CPPRE_FLAT_TU(store) CPPRE_FLAT_TU(score) CPPRE_FLAT_TU(cover)
+#undef CPPRE_FLAT_TU
+inline int flat_eligible(const cppre_program_t* prog, const Prepared& P) {
+    return P.epi.mode == CPPRE_EPI_STORE ? flat_eligible_store(prog, P)
+         : P.epi.mode == CPPRE_EPI_SCORE ? flat_eligible_score(prog, P) : flat_eligible_cover(prog, P);
+}
+inline int launch_flat(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
+    return P.epi.mode == CPPRE_EPI_STORE ? launch_flat_store(prog, P, stream)
+         : P.epi.mode == CPPRE_EPI_SCORE ? launch_flat_score(prog, P, stream) : launch_flat_cover(prog, P, stream);
+}
 inline int tma_eligible(const cppre_program_t* prog, const Prepared& P) {
     if (P.in_bf16)
         return P.epi.mode == CPPRE_EPI_STORE ? tma_eligible_store_dyn_bf16(prog, P)

@@ -1,0 +1,5 @@
+// K1f flat-line star kernel on contiguous rows the TMA kernel cannot stage, COVER epilogue (see stencil_tin_impl.cuh, role 1).
+#define CPPRE_TIN_MODE CPPRE_EPI_COVER
+#define CPPRE_TIN_ROLE 1
+#define CPPRE_TIN_SUFFIX cover
+#include "stencil_tin_impl.cuh"

@@ -20,6 +20,12 @@
 //
 // This file is the body of one translation unit per epilogue mode (stencil_tin_<mode>.cu), each defining
 // CPPRE_TIN_MODE and CPPRE_TIN_SUFFIX.  Optional operands (ref, weight) are decided at run time.
+//
+// Role 1 (stencil_flat_<mode>.cu, CPPRE_TIN_ROLE 1) applies the same flat-neighbour scheme to CONTIGUOUS
+// [BS, Nt, Nx, Ny] data the TMA kernel cannot stage -- rows that are not a multiple of 16 bytes (N0 % 4 != 0,
+// e.g. 254 x 254, 33 x 33, config 1's Nx = 197), unaligned bases or sample strides: march = t, lines = x, within
+// a line = y.  Before it these requests fell to the one-thread-per-cell generic kernel at ~5 % of the star
+// kernels' rate (ns momentum 20 vs 420 Gpoints/s).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -42,6 +48,23 @@ constexpr int kMaxStages = 8;
 #define CPPRE_TIN_DECODE 0
 #endif
 constexpr bool kDEC = CPPRE_TIN_DECODE != 0;
+// CPPRE_TIN_ROLE: which logical axis plays which physical part.
+//   0  t-innermost memory [B][Nx][Ny][Nt] (FNO layout): march = x, lines = y, within a line = t   (the default)
+//   1  CONTIGUOUS memory [B][Nt][Nx][Ny] whose rows the TMA kernel cannot take (N0 % 4 != 0, unaligned base or
+//      strides): march = t, lines = x, within a line = y.  Same flat-neighbour scheme; in addition this role copes
+//      with rows that are not 16-byte aligned (the refilling warp stages them with 4-byte cp.async instead of one
+//      bulk copy), odd line lengths, partially live quads and scalar epilogue accesses -- all decided at run time,
+//      so aligned ragged shapes (e.g. 254 x 254) keep the bulk copies and the 128-bit epilogue.
+#ifndef CPPRE_TIN_ROLE
+#define CPPRE_TIN_ROLE 0
+#endif
+constexpr int kROLE = CPPRE_TIN_ROLE;
+constexpr bool kFLEX = kROLE == 1;
+// logical arm served by each physical neighbour: I = within the line (flat -+1), M = march axis (register
+// pipeline), L = neighbouring line (flat -+line length)
+constexpr int A_IM = kROLE == 0 ? ARM_TM : ARM_YM, A_IP = kROLE == 0 ? ARM_TP : ARM_YP;
+constexpr int A_MM = kROLE == 0 ? ARM_XM : ARM_TM, A_MP = kROLE == 0 ? ARM_XP : ARM_TP;
+constexpr int A_LM = kROLE == 0 ? ARM_YM : ARM_XM, A_LP = kROLE == 0 ? ARM_YP : ARM_XP;
 
 template <int NF>
 struct alignas(16) TinParams {
@@ -56,6 +79,8 @@ struct alignas(16) TinParams {
     int32_t padl;             // leading pad elements: (padl + Nt) % 4 == 0, so centre element 0 is 16-byte aligned
     int32_t stages;
     uint32_t buf_bytes;       // one (stage, field) row tile, 128-aligned
+    int32_t bulk;             // rows are 16-byte aligned: one bulk copy per (row, field); else 4-byte cp.async (kFLEX)
+    int32_t vec;              // out / ref / weight quads are 16-byte aligned: 128-bit epilogue accesses (kFLEX)
     DecodeDev dec;            // read by the CPPRE_TIN_DECODE units only
 };
 
@@ -98,6 +123,14 @@ __device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// 4-byte asynchronous copy (no alignment rule beyond the element), and "arrive on the mbarrier once all my prior
+// cp.async have landed" (.noinc: the arrival is one of those the barrier was initialised to expect)
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ float4 lds128(uint32_t a) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
@@ -124,36 +157,55 @@ struct TinCtx {
     float (&next)[NF][RX][4];      // x+1
     uint32_t cur_a;                // shared address of this thread's quad 0, field 0, in the slot of row x
     uint32_t buf;                  // bytes between the tiles of consecutive fields
-    uint32_t nt_bytes;             // Nt * 4
-    uint32_t tmask[RX];            // bits 0..3: element i has a t-1 neighbour; bits 4..7: a t+1 neighbour
+    uint32_t nt_bytes;             // line length * 4
+    uint32_t tmask[RX];            // bits 0..3: element i has a flat-1 neighbour in its line; bits 4..7: a flat+1 one
+    bool odd;                      // kFLEX: odd line length (the line arms are then two 32-bit loads)
 
-    template <int SLOT, int FD, int IP>
-    __device__ __forceinline__ f2 D() const {
+    // operand pair (elements i0, i1 of quad j, field FD) seen through the LOGICAL arm ARM
+    template <int ARM, int FD, int IP>
+    __device__ __forceinline__ f2 operand() const {
         constexpr int j = IP / 2, h = IP % 2, i0 = 2 * h, i1 = 2 * h + 1;
-        constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
-        const float* c = k.c[SLOT];
         const uint32_t fa = cur_a + FD * buf + j * QUAD_STRIDE + i0 * 4u;    // element i0 of quad j, field FD
         const uint32_t tm = tmask[j];
-        f2 acc = mk2(0.0f, 0.0f);
-        if constexpr ((m >> ARM_TM) & 1) {
+        if constexpr (ARM == ARM_C) {
+            return mk2(cur[FD][j][i0], cur[FD][j][i1]);
+        } else if constexpr (ARM == A_IM) {          // flat - 1, switched off at the first element of a line
             float a;
             if constexpr (h == 0) a = lds32(fa - 4u);
             else a = cur[FD][j][1];
             const float b = cur[FD][j][i0];
-            acc = pfma(mk2((tm >> i0) & 1u ? a : 0.0f, (tm >> i1) & 1u ? b : 0.0f), c[ARM_TM], acc);
-        }
-        if constexpr ((m >> ARM_XM) & 1) acc = pfma(mk2(prev[FD][j][i0], prev[FD][j][i1]), c[ARM_XM], acc);
-        if constexpr ((m >> ARM_YM) & 1) acc = pfma(lds64(fa - nt_bytes), c[ARM_YM], acc);
-        if constexpr ((m >> ARM_C) & 1) acc = pfma(mk2(cur[FD][j][i0], cur[FD][j][i1]), c[ARM_C], acc);
-        if constexpr ((m >> ARM_YP) & 1) acc = pfma(lds64(fa + nt_bytes), c[ARM_YP], acc);
-        if constexpr ((m >> ARM_XP) & 1) acc = pfma(mk2(next[FD][j][i0], next[FD][j][i1]), c[ARM_XP], acc);
-        if constexpr ((m >> ARM_TP) & 1) {
+            return mk2((tm >> i0) & 1u ? a : 0.0f, (tm >> i1) & 1u ? b : 0.0f);
+        } else if constexpr (ARM == A_IP) {          // flat + 1, switched off at the last element of a line
             const float a = cur[FD][j][i1];
             float b;
             if constexpr (h == 1) b = lds32(fa + 8u);
             else b = cur[FD][j][2];
-            acc = pfma(mk2((tm >> (4 + i0)) & 1u ? a : 0.0f, (tm >> (4 + i1)) & 1u ? b : 0.0f), c[ARM_TP], acc);
+            return mk2((tm >> (4 + i0)) & 1u ? a : 0.0f, (tm >> (4 + i1)) & 1u ? b : 0.0f);
+        } else if constexpr (ARM == A_MM) {
+            return mk2(prev[FD][j][i0], prev[FD][j][i1]);
+        } else if constexpr (ARM == A_MP) {
+            return mk2(next[FD][j][i0], next[FD][j][i1]);
+        } else if constexpr (ARM == A_LM) {          // previous line: flat - line length (8-byte aligned when it is even)
+            if (kFLEX && odd) return mk2(lds32(fa - nt_bytes), lds32(fa - nt_bytes + 4u));
+            return lds64(fa - nt_bytes);
+        } else {                                     // A_LP
+            if (kFLEX && odd) return mk2(lds32(fa + nt_bytes), lds32(fa + nt_bytes + 4u));
+            return lds64(fa + nt_bytes);
         }
+    }
+    template <int SLOT, int FD, int IP>
+    __device__ __forceinline__ f2 D() const {
+        constexpr uint32_t m = (uint32_t)((MASKS >> (7 * SLOT)) & 0x7f);
+        const float* c = k.c[SLOT];
+        // accumulation in the logical row-major tap order (t-, x-, y-, centre, y+, x+, t+), like every other kernel
+        f2 acc = mk2(0.0f, 0.0f);
+        if constexpr ((m >> ARM_TM) & 1) acc = pfma(operand<ARM_TM, FD, IP>(), c[ARM_TM], acc);
+        if constexpr ((m >> ARM_XM) & 1) acc = pfma(operand<ARM_XM, FD, IP>(), c[ARM_XM], acc);
+        if constexpr ((m >> ARM_YM) & 1) acc = pfma(operand<ARM_YM, FD, IP>(), c[ARM_YM], acc);
+        if constexpr ((m >> ARM_C) & 1) acc = pfma(operand<ARM_C, FD, IP>(), c[ARM_C], acc);
+        if constexpr ((m >> ARM_YP) & 1) acc = pfma(operand<ARM_YP, FD, IP>(), c[ARM_YP], acc);
+        if constexpr ((m >> ARM_XP) & 1) acc = pfma(operand<ARM_XP, FD, IP>(), c[ARM_XP], acc);
+        if constexpr ((m >> ARM_TP) & 1) acc = pfma(operand<ARM_TP, FD, IP>(), c[ARM_TP], acc);
         return acc;
     }
     template <int FD, int IP>
@@ -196,8 +248,11 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
     const int s_hi = (int)min((int64_t)L4, Q - g_first);
     const uint32_t copy_bytes = (uint32_t)(s_hi - s_lo) * 4u;
 
+    // rows that are not 16-byte aligned (kFLEX) are staged by the 32 lanes of the refilling warp with 4-byte
+    // cp.async, each lane arriving on the slot's mbarrier when its copies have landed
+    const bool coop = kFLEX && !p.bulk;
     if (tid == 0) {
-        for (int s = 0; s < p.stages; ++s) mbar_init(bars + 8u * s, 1);
+        for (int s = 0; s < p.stages; ++s) mbar_init(bars + 8u * s, coop ? 32u : 1u);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -217,9 +272,24 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
             bulk_load(base + (uint32_t)stage * STAGE_BYTES + f * p.buf_bytes + 4u * s_lo,
                       p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * Q + g_first + s_lo, copy_bytes, bar);
     };
-    if (tid == 0) {
+    auto issue_coop = [&](int x, int stage) {      // all 32 lanes of one warp
+        const uint32_t bar = bars + 8u * stage;
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const float* src = p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * Q + g_first;
+            const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * p.buf_bytes;
+            for (int s = s_lo + (tid & 31); s < s_hi; s += 32) cp_async4(dst + 4u * s, src + s);
+        }
+        cp_async_arrive(bar);
+    };
+    {
         const int pre = NPL < p.stages ? NPL : p.stages;
-        for (int q = 0; q < pre; ++q) issue(q, q);
+        if (coop) {
+            if (tr == 0)
+                for (int q = 0; q < pre; ++q) issue_coop(q, q);
+        } else if (tid == 0) {
+            for (int q = 0; q < pre; ++q) issue(q, q);
+        }
     }
 
     float prev[NF][RX][4], cur[NF][RX][4], next[NF][RX][4];
@@ -231,27 +301,35 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
             for (int i = 0; i < 4; ++i) prev[f][j][i] = 0.0f;
 
     // per-quad constants: which elements exist, have t-neighbours, count in a reduction
-    const bool in0 = (p.e.flags & CPPRE_FLAG_INTERIOR_0) != 0;   // logical y shell
-    const bool in1 = (p.e.flags & CPPRE_FLAG_INTERIOR_1) != 0;   // logical x shell
-    const bool in2 = (p.e.flags & CPPRE_FLAG_INTERIOR_2) != 0;   // logical t shell
-    uint32_t live = 0u, tmask[RX], cmask[RX];
+    // shell flags by PHYSICAL axis: within the line / across lines / along the march (role 0: t / y / x; role 1: y / x / t)
+    const bool in_i = (p.e.flags & (kROLE == 0 ? CPPRE_FLAG_INTERIOR_2 : CPPRE_FLAG_INTERIOR_0)) != 0;
+    const bool in_l = (p.e.flags & (kROLE == 0 ? CPPRE_FLAG_INTERIOR_0 : CPPRE_FLAG_INTERIOR_1)) != 0;
+    const bool in_m = (p.e.flags & (kROLE == 0 ? CPPRE_FLAG_INTERIOR_1 : CPPRE_FLAG_INTERIOR_2)) != 0;
+    // live: quads with at least one element of the tile; emask (kFLEX): which of their elements exist (W need not be
+    // a multiple of 4 when rows are unaligned); cmask: which of them count in a reduction
+    uint32_t live = 0u, tmask[RX], cmask[RX], emask[RX];
 #pragma unroll
     for (int j = 0; j < RX; ++j) {
         const int e = 4 * (j * kThreads + tid);
         tmask[j] = 0u;
         cmask[j] = 0u;
+        emask[j] = 0u;
         if (e < W) {
             live |= 1u << j;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
+                if (kFLEX && e + i >= W) continue;
+                emask[j] |= 1u << i;
                 const int t = (e + i) % Nt, y = y0 + (e + i) / Nt;
                 if (t != 0) tmask[j] |= 1u << i;
                 if (t != Nt - 1) tmask[j] |= 1u << (4 + i);
-                const bool shell = (in2 && (t == 0 || t == Nt - 1)) || (in0 && (y == 0 || y == p.Ny - 1));
+                const bool shell = (in_i && (t == 0 || t == Nt - 1)) || (in_l && (y == 0 || y == p.Ny - 1));
                 if (!shell) cmask[j] |= 1u << i;
             }
         }
     }
+    (void)emask;
+    const bool vec = !kFLEX || p.vec;             // 128-bit epilogue accesses
     const uint32_t cell0 = base + (uint32_t)(lead + 4 * tid) * 4u;   // quad 0, field 0, ring slot 0
     auto load_centres = [&](float (&dst)[NF][RX][4], uint32_t a) {
 #pragma unroll
@@ -292,8 +370,19 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
             rq[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             wq[j] = make_float4(1.f, 1.f, 1.f, 1.f);
             if (live & (1u << j)) {
-                if (has_ref) rq[j] = __ldg(reinterpret_cast<const float4*>(refp + j * (kThreads * 4)));
-                if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * (kThreads * 4)));
+                if (vec) {
+                    if (has_ref) rq[j] = __ldg(reinterpret_cast<const float4*>(refp + j * (kThreads * 4)));
+                    if (has_w) wq[j] = __ldg(reinterpret_cast<const float4*>(wp + j * (kThreads * 4)));
+                } else {
+                    float* r4 = reinterpret_cast<float*>(&rq[j]);
+                    float* w4 = reinterpret_cast<float*>(&wq[j]);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if ((emask[j] >> i) & 1u) {
+                            if (has_ref) r4[i] = __ldg(refp + j * (kThreads * 4) + i);
+                            if (has_w) w4[i] = __ldg(wp + j * (kThreads * 4) + i);
+                        }
+                }
             }
         }
         if (x + 1 < NPL) {
@@ -307,11 +396,11 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) N[f][j][i] = 0.0f;
         }
-        TinCtx<NF, RX, MASKS, QUAD_STRIDE> ctx{p.coef, P, C, N, cur_a, p.buf_bytes, (uint32_t)Nt * 4u, {}};
+        TinCtx<NF, RX, MASKS, QUAD_STRIDE> ctx{p.coef, P, C, N, cur_a, p.buf_bytes, (uint32_t)Nt * 4u, {}, (Nt & 1) != 0};
 #pragma unroll
         for (int j = 0; j < RX; ++j) ctx.tmask[j] = tmask[j];
         const bool refiller = tr == wturn;
-        const bool plane_live = STORE || !(in1 && (x == 0 || x == NPL - 1));
+        const bool plane_live = STORE || !(in_m && (x == 0 || x == NPL - 1));
         if (plane_live) {
             static_for<RX>([&](auto J) {
                 constexpr int j = decltype(J)::value;
@@ -345,7 +434,13 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
                             r[i] = has_w ? __fmul_rn(v, ww[i]) : v;
                         }
                         if constexpr (STORE) {
-                            *reinterpret_cast<float4*>(outp + j * (kThreads * 4)) = make_float4(r[0], r[1], r[2], r[3]);
+                            if (vec) {
+                                *reinterpret_cast<float4*>(outp + j * (kThreads * 4)) = make_float4(r[0], r[1], r[2], r[3]);
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    if ((emask[j] >> i) & 1u) outp[j * (kThreads * 4) + i] = r[i];
+                            }
                         } else {
 #pragma unroll
                             for (int i = 0; i < 4; ++i)
@@ -365,7 +460,10 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
         if (has_w) wp += Q;
         if (refiller) {
             bar_sync(stage + 1, kThreads);
-            if ((tid & 31) == 0 && x + p.stages < NPL) issue(x + p.stages, stage);
+            if (x + p.stages < NPL) {
+                if (coop) issue_coop(x + p.stages, stage);
+                else if ((tid & 31) == 0) issue(x + p.stages, stage);
+            }
         }
         wturn = (wturn + 1) & (kWarps - 1);
         stage = nstage;
@@ -414,7 +512,10 @@ bool classify(const cppre_program_t* prog, const Prepared& P, TinHost* H) {
     for (int s = 0; s < P.n_slots; ++s) {
         const int* k = prog->ksize[s];
         const int* pd = prog->pad[s];
-        if (!(k[0] == 3 && k[1] == 3 && k[2] == 3 && pd[0] == 1 && pd[1] == 1 && pd[2] == 1)) return false;
+        const bool k333 = k[0] == 3 && k[1] == 3 && k[2] == 3 && pd[0] == 1 && pd[1] == 1 && pd[2] == 1;
+        // 1-D + time data [B, Nt, 1, Nx] (ConvOps_1d): no x arm at all, one line per plane (role 1 only)
+        const bool k313 = kFLEX && g.N1 == 1 && k[0] == 3 && k[1] == 1 && k[2] == 3 && pd[0] == 1 && pd[1] == 0 && pd[2] == 1;
+        if (!(k333 || k313)) return false;
         for (int t = P.taps.begin[s]; t < P.taps.begin[s + 1]; ++t) {
             const int a = P.taps.o2[t], b = P.taps.o1[t], c = P.taps.o0[t];
             int arm = -1;
@@ -432,25 +533,46 @@ bool classify(const cppre_program_t* prog, const Prepared& P, TinHost* H) {
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// logical [B, N2 = Nt, N1 = Nx, N0 = Ny] stored as [B][Nx][Ny][Nt]: strides (sb, 1, Ny*Nt, Nt)
-bool tin_strides(const Geometry& g, int64_t sb, int64_t s2, int64_t s1, int64_t s0) {
-    const int64_t Nt = g.N2, Ny = g.N0;
-    return s2 == 1 && s0 == Nt && s1 == Ny * Nt && (g.B == 1 || (sb % 4 == 0 && sb >= (int64_t)g.N1 * Ny * Nt));
+// Physical extents by role: (inner = line length, lines, march).
+//   role 0: logical [B, N2 = Nt, N1 = Nx, N0 = Ny] stored as [B][Nx][Ny][Nt]: strides (sb, 1, Ny*Nt, Nt)
+//   role 1: the same logical array stored contiguously [B][Nt][Nx][Ny]:    strides (sb, Nx*Ny, Ny, 1)
+struct Phys {
+    int inner, lines, march;
+};
+Phys phys(const Geometry& g) {
+    return kROLE == 0 ? Phys{g.N2, g.N0, g.N1} : Phys{g.N0, g.N1, g.N2};
+}
+bool role_strides(const Geometry& g, int64_t sb, int64_t s2, int64_t s1, int64_t s0) {
+    const Phys ph = phys(g);
+    const int64_t plane = (int64_t)ph.lines * ph.inner;
+    // strides on extent-1 axes are never used for addressing
+    const int64_t si = kROLE == 0 ? s2 : s0, sl = kROLE == 0 ? s0 : s1, sm = kROLE == 0 ? s1 : s2;
+    if ((ph.inner > 1 && si != 1) || (ph.lines > 1 && sl != ph.inner) || (ph.march > 1 && sm != plane)) return false;
+    if (g.B > 1 && sb < plane * ph.march) return false;
+    return kFLEX || g.B == 1 || sb % 4 == 0;
 }
 
 bool layout_ok(const Prepared& P) {
     const Geometry& g = P.g;
+    const Phys ph = phys(g);
     if (P.in_bf16) return false;
-    if (g.N2 < 4 || g.N2 % 2 != 0 || g.N2 > 512) return false;          // Nt even: the y arms are 64-bit shared loads
-    if (((int64_t)g.N0 * g.N2) % 4 != 0 || g.N0 < 1 || g.N1 < 1) return false;
+    if (!kFLEX) {
+        if (ph.inner < 4 || ph.inner % 2 != 0 || ph.inner > 512) return false;   // even lines: the line arms are 64-bit shared loads
+        if (((int64_t)ph.lines * ph.inner) % 4 != 0 || ph.lines < 1 || ph.march < 1) return false;
+    } else {
+        // a tile is a whole number of lines covering a multiple of 4 elements: 1 / 2 / 4 lines at least
+        const int q = ph.inner % 4 == 0 ? 1 : (ph.inner % 2 == 0 ? 2 : 4);
+        if (ph.inner < 2 || (int64_t)q * ph.inner > kThreads * 4 || ph.lines < 1 || ph.march < 1) return false;
+    }
     for (int f = 0; f < P.n_fields; ++f) {
         const FieldView& v = P.fields[f];
-        if (!aligned16(v.p) || !tin_strides(g, v.sb, v.s2, v.s1, v.s0)) return false;
+        if ((!kFLEX && !aligned16(v.p)) || (reinterpret_cast<uintptr_t>(v.p) & 3u) || !role_strides(g, v.sb, v.s2, v.s1, v.s0))
+            return false;
     }
     const EpiDev& e = P.epi;
-    if (CPPRE_TIN_MODE == CPPRE_EPI_STORE && (!aligned16(e.out) || !tin_strides(g, e.ob, e.o2, e.o1, e.o0))) return false;
-    if (e.ref && (!aligned16(e.ref) || !tin_strides(g, e.rb, e.r2, e.r1, e.r0))) return false;
-    if (e.weight && (!aligned16(e.weight) || !P.weight_tin)) return false;
+    if (CPPRE_TIN_MODE == CPPRE_EPI_STORE && ((!kFLEX && !aligned16(e.out)) || !role_strides(g, e.ob, e.o2, e.o1, e.o0))) return false;
+    if (e.ref && ((!kFLEX && !aligned16(e.ref)) || !role_strides(g, e.rb, e.r2, e.r1, e.r0))) return false;
+    if (e.weight && ((!kFLEX && !aligned16(e.weight)) || !(kROLE == 0 ? P.weight_tin : P.weight_contig))) return false;
     return true;
 }
 
@@ -460,7 +582,8 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
     TinParams<NF> tp;
     memset(&tp, 0, sizeof(tp));
     const Geometry& g = P.g;
-    const int Nt = g.N2, Nx = g.N1, Ny = g.N0;
+    const Phys ph = phys(g);
+    const int Nt = ph.inner, Nx = ph.march, Ny = ph.lines;      // physical roles, named after role 0
     for (int f = 0; f < NF; ++f) {
         tp.f[f] = P.fields[f].p;
         tp.fsb[f] = g.B > 1 ? P.fields[f].sb : 0;
@@ -470,13 +593,24 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
     tp.e = P.epi;
     tp.dec = P.dec;
     tp.Nt = Nt; tp.Nx = Nx; tp.Ny = Ny;
-    // y-lines per tile: as many as RX quads per thread hold, TY*Nt a multiple of 4
-    int TY = (RX * kThreads * 4) / Nt;
-    if (Nt % 4 != 0) TY &= ~1;
-    if (TY > Ny) TY = (Nt % 4 != 0) ? ((Ny + 1) & ~1) : Ny;
-    CPPRE_REQUIRE(TY >= 1, CPPRE_ERR_UNSUPPORTED, "time axis of %d instants does not fit a row tile", Nt);
+    // lines per tile: as many as RX quads per thread hold, TY*Nt a multiple of 4
+    const int lq = Nt % 4 == 0 ? 1 : (Nt % 2 == 0 ? 2 : 4);     // lines per 4-element-aligned group
+    int TY = (RX * kThreads * 4) / Nt / lq * lq;
+    if (TY > Ny) TY = (Ny + lq - 1) / lq * lq;
+    CPPRE_REQUIRE(TY >= 1, CPPRE_ERR_UNSUPPORTED, "lines of %d elements do not fit a row tile", Nt);
     tp.TY = TY;
     tp.tiles = (Ny + TY - 1) / TY;
+    {
+        // bulk copies need 16-byte aligned rows of every field; the 128-bit epilogue needs the same of out / ref / weight
+        const int64_t Q = (int64_t)Ny * Nt;
+        bool bulk = Q % 4 == 0, vec = Q % 4 == 0;
+        for (int f = 0; f < NF; ++f) bulk = bulk && aligned16(P.fields[f].p) && (g.B == 1 || P.fields[f].sb % 4 == 0);
+        if (CPPRE_TIN_MODE == CPPRE_EPI_STORE) vec = vec && aligned16(P.epi.out) && (g.B == 1 || P.epi.ob % 4 == 0);
+        if (P.epi.ref) vec = vec && aligned16(P.epi.ref) && (g.B == 1 || P.epi.rb % 4 == 0);
+        if (P.epi.weight) vec = vec && aligned16(P.epi.weight);
+        tp.bulk = bulk ? 1 : 0;
+        tp.vec = vec ? 1 : 0;
+    }
     tp.padl = (4 - Nt % 4) % 4;
     const int lead = Nt + tp.padl;
     int elems = (tp.padl + (TY + 2) * Nt + 3) & ~3;
@@ -519,6 +653,9 @@ constexpr uint64_t M_NSM_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL, ARMS_ALL);
 constexpr uint64_t M_MHD = pack(ARMS_T, ARMS_X, ARMS_T), M_MHD_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL);
 const Variant kVariants[] = {
     V(CPPRE_PROG_LINEAR, M_LIN),
+#if CPPRE_TIN_ROLE == 1
+    V(CPPRE_PROG_BURGERS, pack(ARMS_T, ARMS_Y, ARMS_C | ARMS_Y)), V(CPPRE_PROG_BURGERS, pack(ARMS_ALL, ARMS_ALL, ARMS_ALL)),
+#endif
     V(CPPRE_PROG_NS_CONTINUITY, M_NSC), V(CPPRE_PROG_NS_CONTINUITY, M_NSC_FULL),
     V(CPPRE_PROG_NS_MOMENTUM, M_NSM), V(CPPRE_PROG_NS_MOMENTUM, M_NSM_FULL),
     V(CPPRE_PROG_MHD_CONTINUITY, M_MHD), V(CPPRE_PROG_MHD_CONTINUITY, M_MHD_FULL),
@@ -540,18 +677,27 @@ const Variant* pick(int kind, const TinHost& H) {
 #define CPPRE_CAT_(a, b) a##b
 #define CPPRE_CAT(a, b) CPPRE_CAT_(a, b)
 
-int CPPRE_CAT(tin_eligible_, CPPRE_TIN_SUFFIX)(const cppre_program_t* prog, const Prepared& P) {
+#if CPPRE_TIN_ROLE == 1
+#define CPPRE_TIN_ELIGIBLE flat_eligible_
+#define CPPRE_TIN_LAUNCH launch_flat_
+#else
+#define CPPRE_TIN_ELIGIBLE tin_eligible_
+#define CPPRE_TIN_LAUNCH launch_tin_
+#endif
+
+int CPPRE_CAT(CPPRE_TIN_ELIGIBLE, CPPRE_TIN_SUFFIX)(const cppre_program_t* prog, const Prepared& P) {
     TinHost H;
+    if (kFLEX && P.dec_on) return 0;        // the decode fold of unaligned data is served by the generic kernel
     if (!classify(prog, P, &H) || !layout_ok(P)) return 0;
     return pick(P.kind, H) != nullptr;
 }
 
-int CPPRE_CAT(launch_tin_, CPPRE_TIN_SUFFIX)(const cppre_program_t* prog, const Prepared& P, cudaStream_t st) {
+int CPPRE_CAT(CPPRE_TIN_LAUNCH, CPPRE_TIN_SUFFIX)(const cppre_program_t* prog, const Prepared& P, cudaStream_t st) {
     TinHost H;
     CPPRE_REQUIRE(classify(prog, P, &H) && layout_ok(P), CPPRE_ERR_UNSUPPORTED,
-                  "request does not qualify for the t-innermost star kernel");
+                  "request does not qualify for the flat-line star kernel of this layout");
     const Variant* v = pick(P.kind, H);
-    CPPRE_REQUIRE(v != nullptr, CPPRE_ERR_UNSUPPORTED, "no t-innermost variant for program %d", P.kind);
+    CPPRE_REQUIRE(v != nullptr, CPPRE_ERR_UNSUPPORTED, "no flat-line variant for program %d", P.kind);
     return v->fn(P, H, st);
 }
 

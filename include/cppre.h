@@ -146,8 +146,11 @@ enum {
 /* Which kernel executes the program.  AUTO picks the TMA star kernel when the request
  * qualifies (3-point star taps, 16-byte aligned rows), the t-innermost star kernel when every field
  * (and the output / reference / weight) is a [B,Nt,Nx,Ny] view of [B,Nx,Ny,Nt] memory -- the layout FNO
- * surrogates emit, pred.permute(0,1,4,2,3)  Joint/Wave_Residuals_CP.py:216 -- and the generic kernel otherwise. */
-enum { CPPRE_PATH_AUTO = 0, CPPRE_PATH_GENERIC = 1, CPPRE_PATH_TMA = 2, CPPRE_PATH_TIN = 3 };
+ * surrogates emit, pred.permute(0,1,4,2,3)  Joint/Wave_Residuals_CP.py:216 --, the flat-line star kernel for
+ * contiguous star requests whose rows the TMA unit cannot stage (N0 % 4 != 0 such as Nx = 197 of
+ * Marginal/Advection_Residuals_CP.py:87,108, odd grids, unaligned bases; N0 <= 1024 / 512 / 256 for N0 % 4 == 0 /
+ * even / odd) and the generic kernel otherwise (Taylor-4/6 taps, valid convolution, arbitrary strides). */
+enum { CPPRE_PATH_AUTO = 0, CPPRE_PATH_GENERIC = 1, CPPRE_PATH_TMA = 2, CPPRE_PATH_TIN = 3, CPPRE_PATH_FLAT = 4 };
 
 typedef struct cppre_epilogue {
     int32_t mode;   /* CPPRE_EPI_* */
@@ -175,7 +178,7 @@ int cppre_version(void);
 const char* cppre_last_error(void);
 /* Number of kernels this library has launched in the calling process (all threads). */
 uint64_t cppre_launch_count(void);
-/* Name of the kernel path the last cppre_residual call on this thread used: "tma" | "tin" | "generic". */
+/* Name of the kernel path the last cppre_residual call on this thread used: "tma" | "tin" | "flat" | "generic" | "empty". */
 const char* cppre_last_path(void);
 
 /* ---- K1: fused residual program ------------------------------------------------------- */

@@ -170,11 +170,16 @@ def test_ragged_and_empty_inputs_take_the_generic_kernel():
     m = _mods()
     W = _wave_op()
     rng = np.random.default_rng(3)
-    for shape in [(2, 5, 7, 197), (1, 1, 1, 1), (3, 2, 1, 5), (2, 80, 3, 2)]:
+    for shape, path in [((2, 5, 7, 197), "flat"), ((1, 1, 1, 1), "generic"), ((3, 2, 1, 5), "flat"), ((2, 80, 3, 2), "flat")]:
         u = rng.standard_normal(shape, dtype=np.float32)
         got = W(cuda(u))
-        assert L.last_path() == "generic"
+        assert L.last_path() == path        # ragged rows: the flat-line star kernel; degenerate rows: the generic one
         assert_close_rel(got.cpu().numpy(), O.correlate(u, W.kernel.numpy()), TOL, str(shape))
+    W5 = m["2d"].ConvOperator(("x", "y"), 2, taylor_order=4)            # 5x5x5 taps: generic kernel on any shape
+    u = rng.standard_normal((2, 5, 7, 197), dtype=np.float32)
+    got = W5(cuda(u))
+    assert L.last_path() == "generic"
+    assert_close_rel(got.cpu().numpy(), O.correlate(u, W5.kernel.numpy()), TOL)
     e = W(torch.zeros(0, 4, 4, 4, device="cuda"))
     assert e.shape == (0, 4, 4, 4)
     A = m["1d"].ConvOperator()                              # config 1: Nx = 197 (not a multiple of 4)
@@ -761,3 +766,90 @@ def test_normaliser_decode_fold_equals_the_residual_of_the_decoded_field():
         ns.residual(cuda(synth.fields(5, 3, (1, 6, 8, 8))), decode=([1.0, 2.0], [0.0, 0.0]))     # 2 scales, 3 variables
     with pytest.raises(NotImplementedError):
         ns.residual(cuda(synth.fields(5, 3, (1, 6, 8, 128))).bfloat16(), decode=(1.0, 0.0))
+
+
+def test_flat_line_kernel_takes_ragged_contiguous_data_and_is_bit_equal_to_the_generic_kernel():
+    """Contiguous star requests the TMA unit cannot stage -- N0 % 4 != 0 (254 x 254, 33 x 33, config 1's Nx = 197),
+    unaligned bases -- run on the flat-line star kernel (stencil_tin_impl.cuh role 1: march = t, lines = x) instead
+    of the one-thread-per-cell generic kernel.  Same arm order, same algebra: STORE fields, max-scores and coverage
+    counts are BIT-EQUAL to the generic kernel's, for every program family, aligned (bulk copies, 128-bit epilogue)
+    and unaligned rows (4-byte cp.async, scalar epilogue), odd and even lines, partial tiles, 1-D + time data."""
+    import bench
+    o, n = _programs_2d(), synth.NS
+    progs = {"ns": (programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"]), 3),
+             "cont": (programs.ns_continuity(o["D_x"], o["D_y"], n["dx"], n["dy"]), 3),
+             "wave": (bench.make_program("wave"), 1)}
+    for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+        progs["mhd_" + eq] = (bench.make_program("mhd", eq), 6)
+    g = torch.Generator(device="cuda").manual_seed(33)
+    shapes = ((2, 5, 7, 197), (2, 4, 8, 254), (3, 6, 9, 254), (2, 3, 4, 6), (1, 7, 5, 33), (2, 5, 33, 33), (2, 4, 2, 2),
+              (1, 3, 40, 510), (2, 6, 3, 255), (1, 2, 300, 10))
+    for name, (prog, nf) in progs.items():
+        for (bs, nt, nx, ny) in shapes:
+            shape = (bs, nf, nt, nx, ny) if nf > 1 else (bs, nt, nx, ny)
+            v = torch.randn(shape, device="cuda", generator=g)
+            if name.startswith("mhd"):
+                v = v.abs() + 0.5
+            for misalign in (False, True):
+                if misalign:                                            # base 4 bytes off a 16-byte boundary
+                    buf = torch.empty(v.numel() + 1, device="cuda")
+                    vv = buf[1:].view(v.shape)
+                    vv.copy_(v)
+                else:
+                    vv = v
+                prog.path = L.PATH_GENERIC
+                want = prog.residual(vv, boundary=True)
+                assert L.last_path() == "generic"
+                prog.path = L.PATH_AUTO
+                got = prog.residual(vv, boundary=True)
+                assert L.last_path() == "flat", (name, shape, misalign)
+                assert torch.equal(got, want), (name, shape, misalign, float((got - want).abs().max()))
+                ref = torch.randn(want.shape, device="cuda", generator=g)
+                w = torch.rand(want.shape[1:], device="cuda", generator=g) + 0.1
+                for interior in (True, False):
+                    for red in ("max", "sum"):
+                        prog.path = L.PATH_GENERIC
+                        a = prog.joint_scores(vv, inv_modulation=w, ref=ref, interior=interior, reduce=red)
+                        prog.path = L.PATH_AUTO
+                        b = prog.joint_scores(vv, inv_modulation=w, ref=ref, interior=interior, reduce=red)
+                        assert L.last_path() == "flat"
+                        if red == "max":
+                            assert torch.equal(a, b), (name, shape, interior)
+                        else:
+                            assert torch.allclose(a, b, rtol=2e-5, atol=1e-6), (name, shape, interior)
+                    prog.path = L.PATH_GENERIC
+                    a = prog.coverage_counts(vv, 0.7, half=w, centre=ref, interior=interior)
+                    prog.path = L.PATH_AUTO
+                    b = prog.coverage_counts(vv, 0.7, half=w, centre=ref, interior=interior)
+                    assert L.last_path() == "flat" and torch.equal(a, b), (name, shape, interior)
+                prog.path = L.PATH_GENERIC
+                a = prog.abs_scores(vv, ref=ref, boundary=True)
+                prog.path = L.PATH_AUTO
+                sc = torch.empty_like(want)
+                b = prog.abs_scores(vv, ref=ref, boundary=True, out=sc)
+                assert L.last_path() == "flat" and b.data_ptr() == sc.data_ptr() and torch.equal(a, b)
+    # 1-D + time (ConvOps_1d): config 1's [n, 10, 197] advection operator and Burgers on ragged rows
+    import ConvOps_1d as C1
+    A = C1.ConvOperator()
+    A.kernel = C1.ConvOperator("t", 1).kernel + 0.5 * C1.ConvOperator("x", 1).kernel
+    bq = synth.BURGERS
+    bur = programs.burgers(C1.ConvOperator("t", 1), C1.ConvOperator("x", 1), C1.ConvOperator("x", 2), bq["dx"], bq["dt"], bq["nu"])
+    for prog in (programs.linear(A), bur):
+        for shape in ((100, 10, 197), (7, 33, 50), (3, 5, 255), (3, 5, 510)):
+            u = torch.randn(shape, device="cuda", generator=g)
+            prog.path = L.PATH_GENERIC
+            want = prog.residual(u, boundary=True)
+            prog.path = L.PATH_AUTO
+            got = prog.residual(u, boundary=True)
+            assert L.last_path() == "flat", (prog.name, shape)
+            assert torch.equal(got, want), (prog.name, shape)
+            assert_close_rel(got.cpu().numpy(), (O.correlate(u.cpu().numpy(), A.kernel.numpy()) if prog.name == "linear"
+                                                 else O.residual_burgers(u.cpu().numpy(), bq["dx"], bq["dt"], bq["nu"])), TOL)
+    # what it declines still runs (generic) and PATH_FLAT then fails loudly
+    W = bench.make_program("wave")
+    u = torch.randn((2, 4, 6, 2050), device="cuda", generator=g)       # rows longer than a tile holds
+    W.residual(u, boundary=True)
+    assert L.last_path() == "generic"
+    W.path = L.PATH_FLAT
+    with pytest.raises(NotImplementedError):
+        W.residual(u, boundary=True)
