@@ -27,9 +27,11 @@ struct f2 {
 __device__ __forceinline__ f2 mk2(float x, float y) { return f2{make_float2(x, y)}; }
 __device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
 
-__device__ __forceinline__ float pmul(float a, float b) { return a * b; }
-__device__ __forceinline__ float padd(float a, float b) { return a + b; }
-__device__ __forceinline__ float psub(float a, float b) { return a - b; }
+// the scalar forms use the _rn intrinsics so that the compiler cannot contract a product into a following sum:
+// the packed forms below never are, and the generic kernel must return what the star kernels return, bit for bit
+__device__ __forceinline__ float pmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float padd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float psub(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float pfma(float a, float b, float c) { return fmaf(a, b, c); }    // a*b + c
 __device__ __forceinline__ float pfnma(float a, float b, float c) { return fmaf(-a, b, c); }  // c - a*b
 __device__ __forceinline__ float pinv(float a) { return 1.0f / a; }   // IEEE division (no fast-math)

@@ -5,6 +5,7 @@ import torch
 
 import cp_pre_b200
 from conftest import assert_close_rel, load_golden
+from oracle import cpu_oracle as O
 
 cp_pre_b200.install()
 pytestmark = pytest.mark.gpu

@@ -47,13 +47,13 @@ def main():
     W = C2.ConvOperator()
     W.kernel = C2.ConvOperator("t", 2).kernel - 0.25 * C2.ConvOperator(("x", "y"), 2).kernel
     record("wave_k3_aligned", programs.linear(W), u, 1, "the star kernel's case")
-    record("wave_k3_ragged_N0_254", programs.linear(W), u[..., :254].contiguous(), 1, "N0 % 4 != 0 -> generic kernel")
+    record("wave_k3_ragged_N0_254", programs.linear(W), u[..., :254].contiguous(), 1, "N0 % 4 != 0 -> flat-line star kernel (generic kernel before it existed)")
     c = synth.NS
     D = [C2.ConvOperator("t", 1), C2.ConvOperator("x", 1), C2.ConvOperator("y", 1), C2.ConvOperator(("x", "y"), 2)]
     ns = programs.ns_momentum(*D, c["dx"], c["dy"], c["dt"], c["nu"])
     v3 = torch.randn((32, 3, 50, 256, 256), device=dev, generator=g)
     record("ns_momentum_aligned", ns, v3, 3, "the star kernel's case")
-    record("ns_momentum_ragged_N0_254", ns, v3[..., :254].contiguous(), 3, "N0 % 4 != 0 -> generic kernel")
+    record("ns_momentum_ragged_N0_254", ns, v3[..., :254].contiguous(), 3, "N0 % 4 != 0 -> flat-line star kernel (generic kernel before it existed)")
     ns.path = L.PATH_GENERIC
     record("ns_momentum_aligned_forced_generic", ns, v3, 3, "same request, generic kernel forced")
     # config 1's shape: [1000, 10, 197] advection (1-D + time, ragged)
