@@ -86,7 +86,7 @@ def kernel_source_sha():
     return h.hexdigest()[:16]
 
 
-def k1_traffic(workload, equation=None):
+def k1_traffic(workload, equation=None, points=None):
     """DRAM bytes per K1 STORE launch from the committed `ncu --set full` capture (dram__bytes_read.sum +
     dram__bytes_write.sum) of THIS workload and THIS kernel source; None when there is no such capture or
     the kernel has changed since (a stale capture is never reported)."""
@@ -95,8 +95,13 @@ def k1_traffic(workload, equation=None):
         d = json.load(open(os.path.join(ROOT, "profiles", name)))
         if d.get("kernel_source_sha") != kernel_source_sha():
             return None
-        return {"bytes": d["dram_bytes_read"] + d["dram_bytes_write"], "read": d["dram_bytes_read"],
-                "write": d["dram_bytes_write"], "algorithmic": d["algorithmic_bytes"], "source": d["source"]}
+        # the capture may hold fewer samples per launch than this run (K1 traffic is linear in the samples: one CTA
+        # column per sample): scale to the points of this run's launch
+        k = float(points) / d["points_per_launch"] if points and d.get("points_per_launch") else 1.0
+        return {"bytes": k * (d["dram_bytes_read"] + d["dram_bytes_write"]), "read": k * d["dram_bytes_read"],
+                "write": k * d["dram_bytes_write"], "algorithmic": k * d["algorithmic_bytes"],
+                "over_algorithmic": (d["dram_bytes_read"] + d["dram_bytes_write"]) / d["algorithmic_bytes"],
+                "scaled_from_points": d.get("points_per_launch"), "source": d["source"]}
     except (OSError, ValueError, KeyError):
         return None
 
@@ -939,7 +944,7 @@ def main():
             cpu = {"value": v, "unit": "Gpoints/s", "cores": threads, "kind": arm_kind, "sample": desc,
                    "points_per_step": pts, "seconds": secs, "extrapolated": False}
         _, _, scaling = geometry(args, world)
-        traffic = k1_traffic(args.workload, args.equation)
+        traffic = k1_traffic(args.workload, args.equation, k1_pts)
         print(json.dumps({
             "metric": step.metric, "value": value, "unit": "Gpoints/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,

@@ -70,6 +70,8 @@ template <int NF>
 struct alignas(16) TinParams {
     const float* f[NF];       // field base pointers (sample 0, x-row 0, flat index 0)
     int64_t fsb[NF];          // sample stride of each field, elements
+    int64_t frow[NF];         // stride between consecutive rows of the march: lines * line length, or 0 for a field that
+                              // is the same plane for every row and sample (role 1: JOREK's R(x, y) coefficient plane)
     StarCoef coef;
     float scalars[CPPRE_MAX_SCALARS];
     EpiDev e;                 // out / ref: sample strides ob / rb; x-row stride Q, flat stride 1 (checked by the host)
@@ -270,13 +272,13 @@ tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
 #pragma unroll
         for (int f = 0; f < NF; ++f)
             bulk_load(base + (uint32_t)stage * STAGE_BYTES + f * p.buf_bytes + 4u * s_lo,
-                      p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * Q + g_first + s_lo, copy_bytes, bar);
+                      p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * p.frow[f] + g_first + s_lo, copy_bytes, bar);
     };
     auto issue_coop = [&](int x, int stage) {      // all 32 lanes of one warp
         const uint32_t bar = bars + 8u * stage;
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
-            const float* src = p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * Q + g_first;
+            const float* src = p.f[f] + (int64_t)b * p.fsb[f] + (int64_t)x * p.frow[f] + g_first;
             const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES + f * p.buf_bytes;
             for (int s = s_lo + (tid & 31); s < s_hi; s += 32) cp_async4(dst + 4u * s, src + s);
         }
@@ -542,9 +544,17 @@ struct Phys {
 Phys phys(const Geometry& g) {
     return kROLE == 0 ? Phys{g.N2, g.N0, g.N1} : Phys{g.N0, g.N1, g.N2};
 }
-bool role_strides(const Geometry& g, int64_t sb, int64_t s2, int64_t s1, int64_t s0) {
+// a FIELD may also be stationary (role 1): one contiguous plane read for every row of the march and every sample
+// (march and sample strides 0) -- a coefficient plane such as JOREK's R broadcast over time and batch
+bool stationary(const Geometry& g, int64_t sb, int64_t s2, int64_t s1, int64_t s0) {
+    const Phys ph = phys(g);
+    const int64_t si = kROLE == 0 ? s2 : s0, sl = kROLE == 0 ? s0 : s1, sm = kROLE == 0 ? s1 : s2;
+    return kFLEX && sm == 0 && sb == 0 && (ph.inner == 1 || si == 1) && (ph.lines == 1 || sl == ph.inner);
+}
+bool role_strides(const Geometry& g, int64_t sb, int64_t s2, int64_t s1, int64_t s0, bool field = false) {
     const Phys ph = phys(g);
     const int64_t plane = (int64_t)ph.lines * ph.inner;
+    if (field && stationary(g, sb, s2, s1, s0)) return true;
     // strides on extent-1 axes are never used for addressing
     const int64_t si = kROLE == 0 ? s2 : s0, sl = kROLE == 0 ? s0 : s1, sm = kROLE == 0 ? s1 : s2;
     if ((ph.inner > 1 && si != 1) || (ph.lines > 1 && sl != ph.inner) || (ph.march > 1 && sm != plane)) return false;
@@ -566,7 +576,7 @@ bool layout_ok(const Prepared& P) {
     }
     for (int f = 0; f < P.n_fields; ++f) {
         const FieldView& v = P.fields[f];
-        if ((!kFLEX && !aligned16(v.p)) || (reinterpret_cast<uintptr_t>(v.p) & 3u) || !role_strides(g, v.sb, v.s2, v.s1, v.s0))
+        if ((!kFLEX && !aligned16(v.p)) || (reinterpret_cast<uintptr_t>(v.p) & 3u) || !role_strides(g, v.sb, v.s2, v.s1, v.s0, true))
             return false;
     }
     const EpiDev& e = P.epi;
@@ -585,8 +595,11 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
     const Phys ph = phys(g);
     const int Nt = ph.inner, Nx = ph.march, Ny = ph.lines;      // physical roles, named after role 0
     for (int f = 0; f < NF; ++f) {
-        tp.f[f] = P.fields[f].p;
-        tp.fsb[f] = g.B > 1 ? P.fields[f].sb : 0;
+        const FieldView& v = P.fields[f];
+        const bool still = stationary(g, v.sb, v.s2, v.s1, v.s0) && !(g.B == 1 && Nx == 1);
+        tp.f[f] = v.p;
+        tp.fsb[f] = (g.B > 1 && !still) ? v.sb : 0;
+        tp.frow[f] = still ? 0 : (int64_t)Ny * Nt;
     }
     tp.coef = H.coef;
     memcpy(tp.scalars, P.scalars, sizeof(tp.scalars));
@@ -604,7 +617,7 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
         // bulk copies need 16-byte aligned rows of every field; the 128-bit epilogue needs the same of out / ref / weight
         const int64_t Q = (int64_t)Ny * Nt;
         bool bulk = Q % 4 == 0, vec = Q % 4 == 0;
-        for (int f = 0; f < NF; ++f) bulk = bulk && aligned16(P.fields[f].p) && (g.B == 1 || P.fields[f].sb % 4 == 0);
+        for (int f = 0; f < NF; ++f) bulk = bulk && aligned16(P.fields[f].p) && (tp.fsb[f] % 4 == 0);
         if (CPPRE_TIN_MODE == CPPRE_EPI_STORE) vec = vec && aligned16(P.epi.out) && (g.B == 1 || P.epi.ob % 4 == 0);
         if (P.epi.ref) vec = vec && aligned16(P.epi.ref) && (g.B == 1 || P.epi.rb % 4 == 0);
         if (P.epi.weight) vec = vec && aligned16(P.epi.weight);
@@ -635,8 +648,8 @@ int launch_variant(const Prepared& P, const TinHost& H, cudaStream_t st) {
     return CPPRE_OK;
 }
 
-constexpr uint64_t pack(uint32_t a, uint32_t b = 0, uint32_t c = 0, uint32_t d = 0) {
-    return (uint64_t)a | ((uint64_t)b << 7) | ((uint64_t)c << 14) | ((uint64_t)d << 21);
+constexpr uint64_t pack(uint32_t a, uint32_t b = 0, uint32_t c = 0, uint32_t d = 0, uint32_t e = 0) {
+    return (uint64_t)a | ((uint64_t)b << 7) | ((uint64_t)c << 14) | ((uint64_t)d << 21) | ((uint64_t)e << 28);
 }
 typedef int (*LaunchFn)(const Prepared&, const TinHost&, cudaStream_t);
 struct Variant {
@@ -655,6 +668,12 @@ const Variant kVariants[] = {
     V(CPPRE_PROG_LINEAR, M_LIN),
 #if CPPRE_TIN_ROLE == 1
     V(CPPRE_PROG_BURGERS, pack(ARMS_T, ARMS_Y, ARMS_C | ARMS_Y)), V(CPPRE_PROG_BURGERS, pack(ARMS_ALL, ARMS_ALL, ARMS_ALL)),
+    // JOREK reduced MHD {D_t, D_R, D_Z, D_RR, D_ZZ} [ref: Marginal/JOREK_residuals_CP.py:203-209]: as the reference's
+    // constructors build them (domain 'y' == 't'), then with D_Z / D_ZZ along y
+    V(CPPRE_PROG_JOREK_CONTINUITY, pack(ARMS_T, ARMS_X, ARMS_T, ARMS_C | ARMS_X, ARMS_C | ARMS_T)),
+    V(CPPRE_PROG_JOREK_CONTINUITY, pack(ARMS_T, ARMS_X, ARMS_Y, ARMS_C | ARMS_X, ARMS_C | ARMS_Y)),
+    V(CPPRE_PROG_JOREK_TEMPERATURE, pack(ARMS_T, ARMS_X, ARMS_T, ARMS_C | ARMS_X, ARMS_C | ARMS_T)),
+    V(CPPRE_PROG_JOREK_TEMPERATURE, pack(ARMS_T, ARMS_X, ARMS_Y, ARMS_C | ARMS_X, ARMS_C | ARMS_Y)),
 #endif
     V(CPPRE_PROG_NS_CONTINUITY, M_NSC), V(CPPRE_PROG_NS_CONTINUITY, M_NSC_FULL),
     V(CPPRE_PROG_NS_MOMENTUM, M_NSM), V(CPPRE_PROG_NS_MOMENTUM, M_NSM_FULL),

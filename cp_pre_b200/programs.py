@@ -61,7 +61,10 @@ class ResidualProgram:
             if fs[0].dim() == 4 and cf.numel() != fs[0].shape[-1]:
                 raise RuntimeError(f"The size of tensor a ({fs[0].shape[-1]}) must match the size of tensor b "
                                    f"({cf.numel()}) at non-singleton dimension {fs[0].dim() - 1}")
-            fs.append(cf.view(1, 1, 1, -1).expand(fs[0].shape))
+            # one [Nx, Ny] plane (Nx*Ny floats), viewed as the same plane for every instant and sample: the
+            # flat-line star kernel stages it like a field; no [BS,Nt,Nx,Ny] copy is ever made
+            plane = cf.view(1, -1).expand(fs[0].shape[2], -1).contiguous()
+            fs.append(plane.view((1, 1) + tuple(plane.shape)).expand(fs[0].shape))
         if fs[0].dim() != 4:
             raise RuntimeError(f"{self.name}: expected {'[BS,F,Nt,Nx,Ny]' if self.field_index else '[BS,Nt,...]'} input")
         return fs

@@ -2,8 +2,8 @@
 bench.py's `roofline.traffic` is read from.  The record carries the fingerprint of the K1 sources it was
 captured from (bench.kernel_source_sha): bench.py reports the traffic only while the kernel is unchanged.
 
-    python tools/k1_traffic.py gpurun_out/r2e_prof_raw.csv ns
-    python tools/k1_traffic.py gpurun_out/r2e_prof_mhd_raw.csv mhd momentum
+    python tools/k1_traffic.py gpurun_out/r2g_prof_raw.csv ns "" 256
+    python tools/k1_traffic.py gpurun_out/r2g_prof_mhd_raw.csv mhd momentum 64
 """
 import csv
 import json
@@ -20,7 +20,7 @@ def to_bytes(v, unit):
     return float(v.replace(",", "")) * mult
 
 
-def main(path, workload, equation=None):
+def main(path, workload, equation=None, samples=None):
     rows = list(csv.reader(open(path)))
     hdr, units = rows[0], rows[1]
     col = {h: i for i, h in enumerate(hdr)}
@@ -43,9 +43,16 @@ def main(path, workload, equation=None):
         break
     assert rec is not None, "no STORE launch of star_kernel in the capture"
     # algorithmic bytes of the captured launch: (4F + 4) B per point; points from the written bytes (4 B per point)
-    points = round(rec["dram_bytes_write"] / 4 / 1e3) * 1e3
+    import numpy as np
+    cells = int(np.prod(w["grid"]))
+    # samples per launch: given, or whole samples from the written bytes (4 B per point; ncu sees a little less than
+    # the algorithmic write volume because the last lines are still in L2 when the kernel ends)
+    samples = int(samples) if samples else round(rec["dram_bytes_write"] / 4 / cells)
+    points = samples * cells
     rec["algorithmic_bytes"] = (4 * nf + 4) * points
-    rec["points_estimated_from_written_bytes"] = points
+    rec["points_per_launch"] = points
+    rec["samples_per_launch"] = samples
+    rec["traffic_over_algorithmic"] = (rec["dram_bytes_read"] + rec["dram_bytes_write"]) / rec["algorithmic_bytes"]
     rec["kernel_source_sha"] = bench.kernel_source_sha()
     rec["source"] = f"ncu --set full --clock-control none, {os.path.basename(path)} (first STORE launch of star_kernel)"
     name = f"k1_traffic_{workload}" + (f"_{equation}" if workload == "mhd" else "") + ".json"
@@ -54,4 +61,5 @@ def main(path, workload, equation=None):
 
 
 if __name__ == "__main__":
-    main(*sys.argv[1:])
+    a = sys.argv[1:]
+    main(a[0], a[1], (a[2] or None) if len(a) > 2 else None, a[3] if len(a) > 3 else None)
