@@ -216,8 +216,10 @@ struct TinCtx {
     }
 };
 
+// Single-field programs run three CTAs per SM (80 registers, no spill: wave on 256 x 254 rows 443 -> 507 Gpoints/s);
+// with more fields the cap costs a spill frame that outweighs the extra warps (NS momentum 342 -> 244), so they stay at two.
 template <int KIND, int RX, uint64_t MASKS, int MODE>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, (Prog<KIND>::NF == 1 ? 3 : 2))
 tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
     constexpr int NF = Prog<KIND>::NF;
     constexpr bool STORE = MODE == CPPRE_EPI_STORE;
