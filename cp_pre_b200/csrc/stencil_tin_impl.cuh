@@ -219,7 +219,7 @@ struct TinCtx {
 // Single-field programs run three CTAs per SM (80 registers, no spill: wave on 256 x 254 rows 443 -> 507 Gpoints/s);
 // with more fields the cap costs a spill frame that outweighs the extra warps (NS momentum 342 -> 244), so they stay at two.
 template <int KIND, int RX, uint64_t MASKS, int MODE>
-__global__ void __launch_bounds__(kThreads, (Prog<KIND>::NF == 1 && RX == 1 ? 3 : 2))
+__global__ void __launch_bounds__(kThreads, (Prog<KIND>::NF == 1 ? 3 : 2))
 tin_kernel(const __grid_constant__ TinParams<Prog<KIND>::NF> p) {
     constexpr int NF = Prog<KIND>::NF;
     constexpr bool STORE = MODE == CPPRE_EPI_STORE;
@@ -658,10 +658,10 @@ struct Variant {
     int kind;
     uint64_t masks;
     LaunchFn fn;
-    LaunchFn fn2;     // two quads per thread (tiles of 2048 elements): shipped operator sets of programs with <= 3 fields
 };
-#define V(K, M) Variant{K, M, &launch_variant<K, 1, M>, nullptr}
-#define V2(K, M) Variant{K, M, &launch_variant<K, 1, M>, &launch_variant<K, 2, M>}
+// one quad per thread: two (tiles of 2048 elements) were measured and lose -- NS momentum 342 -> 260 Gpoints/s on
+// the FNO layout, 180 -> 136 on ragged rows (spill frame at the 128-register cap), wave +4 %
+#define V(K, M) Variant{K, M, &launch_variant<K, 1, M>}
 // "shipped" = the kernels the reference constructors produce (D_y == D_t); then any star
 constexpr uint64_t M_LIN = pack(ARMS_ALL);
 constexpr uint64_t M_NSC = pack(ARMS_X, ARMS_T), M_NSC_FULL = pack(ARMS_ALL, ARMS_ALL);
@@ -669,7 +669,7 @@ constexpr uint64_t M_NSM = pack(ARMS_T, ARMS_X, ARMS_T, ARMS_C | ARMS_X | ARMS_Y
 constexpr uint64_t M_NSM_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL, ARMS_ALL);
 constexpr uint64_t M_MHD = pack(ARMS_T, ARMS_X, ARMS_T), M_MHD_FULL = pack(ARMS_ALL, ARMS_ALL, ARMS_ALL);
 const Variant kVariants[] = {
-    V2(CPPRE_PROG_LINEAR, M_LIN),
+    V(CPPRE_PROG_LINEAR, M_LIN),
 #if CPPRE_TIN_ROLE == 1
     V(CPPRE_PROG_BURGERS, pack(ARMS_T, ARMS_Y, ARMS_C | ARMS_Y)), V(CPPRE_PROG_BURGERS, pack(ARMS_ALL, ARMS_ALL, ARMS_ALL)),
     // JOREK reduced MHD {D_t, D_R, D_Z, D_RR, D_ZZ} [ref: Marginal/JOREK_residuals_CP.py:203-209]: as the reference's
@@ -679,8 +679,8 @@ const Variant kVariants[] = {
     V(CPPRE_PROG_JOREK_TEMPERATURE, pack(ARMS_T, ARMS_X, ARMS_T, ARMS_C | ARMS_X, ARMS_C | ARMS_T)),
     V(CPPRE_PROG_JOREK_TEMPERATURE, pack(ARMS_T, ARMS_X, ARMS_Y, ARMS_C | ARMS_X, ARMS_C | ARMS_Y)),
 #endif
-    V2(CPPRE_PROG_NS_CONTINUITY, M_NSC), V(CPPRE_PROG_NS_CONTINUITY, M_NSC_FULL),
-    V2(CPPRE_PROG_NS_MOMENTUM, M_NSM), V(CPPRE_PROG_NS_MOMENTUM, M_NSM_FULL),
+    V(CPPRE_PROG_NS_CONTINUITY, M_NSC), V(CPPRE_PROG_NS_CONTINUITY, M_NSC_FULL),
+    V(CPPRE_PROG_NS_MOMENTUM, M_NSM), V(CPPRE_PROG_NS_MOMENTUM, M_NSM_FULL),
     V(CPPRE_PROG_MHD_CONTINUITY, M_MHD), V(CPPRE_PROG_MHD_CONTINUITY, M_MHD_FULL),
     V(CPPRE_PROG_MHD_MOMENTUM, M_MHD), V(CPPRE_PROG_MHD_MOMENTUM, M_MHD_FULL),
     V(CPPRE_PROG_MHD_ENERGY, M_MHD), V(CPPRE_PROG_MHD_ENERGY, M_MHD_FULL),
@@ -688,7 +688,6 @@ const Variant kVariants[] = {
     V(CPPRE_PROG_MHD_GAUSS, M_MHD), V(CPPRE_PROG_MHD_GAUSS, M_MHD_FULL),
 };
 #undef V
-#undef V2
 
 const Variant* pick(int kind, const TinHost& H) {
     for (const Variant& v : kVariants)
@@ -722,15 +721,6 @@ int CPPRE_CAT(CPPRE_TIN_LAUNCH, CPPRE_TIN_SUFFIX)(const cppre_program_t* prog, c
                   "request does not qualify for the flat-line star kernel of this layout");
     const Variant* v = pick(P.kind, H);
     CPPRE_REQUIRE(v != nullptr, CPPRE_ERR_UNSUPPORTED, "no flat-line variant for program %d", P.kind);
-    // two quads per thread when a plane holds at least two of the larger tiles and whole lines still fit
-    static int env_rx = -1;
-    if (env_rx < 0) {
-        const char* e = getenv("CPPRE_TIN_RX");
-        env_rx = e ? atoi(e) : 0;
-    }
-    const Phys ph = phys(P.g);
-    const bool big = (int64_t)ph.lines * ph.inner >= 2 * 2 * kThreads * 4;
-    if (v->fn2 != nullptr && (env_rx == 2 || (env_rx == 0 && big))) return v->fn2(P, H, st);
     return v->fn(P, H, st);
 }
 
