@@ -282,3 +282,33 @@ def test_integration_guide_covers_every_exported_entry_point():
     names = set(re.findall(r"\b(cppre_[a-z0-9_]+)\s*\(", header))
     assert len(names) >= 25
     assert not [n for n in sorted(names) if n not in guide]
+
+
+def test_decode_fold_host_mapping():
+    """Normaliser-decode fold, host side: (scale, offset) forms, the MinMax-object form (decode(x) = (x - b) / a),
+    per-variable entries routed to the program's fields by their index in ``vars`` (MHD induction reads variables
+    1, 2, 4, 5), the coefficient field of the JOREK programs never decoded, malformed input refused."""
+    import torch
+    from cp_pre_b200 import programs
+    mods = _mods()
+    D = [mods["2d"].ConvOperator("t", 1), mods["2d"].ConvOperator("x", 1), mods["2d"].ConvOperator("y", 1)]
+
+    class MinMax:
+        a, b = torch.tensor([2.0, 4.0]), torch.tensor([1.0, -2.0])
+
+    sc, of = programs.ResidualProgram._affine(MinMax())
+    assert sc == [0.5, 0.25] and of == [-0.5, 0.5]
+    assert programs.ResidualProgram._affine((3.0, -1.0)) == ([3.0], [-1.0])
+    ind = programs.mhd("induction", *D)
+    v = torch.zeros(2, 6, 4, 4, 4)
+    sc6, of6 = [1.0, 2.0, 3.0, 4.0, 5.0, 6.0], [0.1, 0.2, 0.3, 0.4, 0.5, 0.6]
+    assert ind._decode_per_field((sc6, of6), v, 4) == ([2.0, 3.0, 5.0, 6.0], [0.2, 0.3, 0.5, 0.6])
+    assert ind._decode_per_field((2.0, 0.5), v, 4) == ([2.0] * 4, [0.5] * 4)          # scalars: every variable
+    assert ind._decode_per_field(None, v, 4) is None
+    with pytest.raises(ValueError):
+        ind._decode_per_field(([1.0, 2.0], [0.0, 0.0]), v, 4)                          # 2 entries, 6 variables
+    jor = programs.jorek("continuity", *D, D[1], D[2], torch.linspace(1, 2, 4), 3.4)
+    s, o = jor._decode_per_field(([2.0, 3.0, 4.0], [0.0, 1.0, 2.0]), torch.zeros(2, 3, 4, 4, 4), 4)
+    assert s == [2.0, 3.0, 4.0, 1.0] and o == [0.0, 1.0, 2.0, 0.0]                     # R is not decoded
+    wave = programs.linear(D[0])
+    assert wave._decode_per_field((0.25, 2.0), torch.zeros(2, 4, 4, 4), 1) == ([0.25], [2.0])
