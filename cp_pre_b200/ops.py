@@ -9,6 +9,7 @@ host without CUDA raises -- there is no CPU path.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence
 
 import numpy as np
@@ -375,8 +376,64 @@ def joint_score(a: torch.Tensor, b: Optional[torch.Tensor], mod: torch.Tensor) -
     return out
 
 
+SEGMENT_SLOTS = 60          # candidate slots per segment and cell of the segmented select (as in the multi-GPU exchange)
+
+
+def _segmented_select(fs: torch.Tensor, rank: int):
+    """One order statistic near the TOP of columns longer than the register networks hold (n > 2048), on one
+    GPU, with the kernels of the multi-GPU candidate-window exchange (dist._window_quantile) and the row
+    segments of the column in the role of the ranks: the J-th largest of every segment (K3t, J = ceil(kt/S) <= 64)
+    brackets the kt-th largest of the whole column; one more pass collects the few samples inside the bracket
+    (K3w) and the answer is picked among them (select_from_top).  Two passes over the scores instead of the nine
+    of the radix select.  Returns None when the request does not fit (the caller then takes the radix kernel);
+    cells whose bracket overflowed the candidate slots are redone exactly with the radix kernel."""
+    n, cells = fs.shape
+    kt = n - int(rank)                           # the kt-th largest
+    if kt < 1 or kt > 1024:
+        return None
+    S = max(2, -(-kt // 64))                     # segments: J = ceil(kt / S) <= 64
+    if S > 16 or n // S <= 256:                  # owner network 64 * S <= 1024; segments long enough for the top-K kernel
+        return None
+    J = -(-kt // S)
+    bounds = [(i * n) // S for i in range(S + 1)]
+    segs = [fs[bounds[i]:bounds[i + 1]] for i in range(S)]
+    keys = torch.stack([ordered_keys(select_ranks(seg, [seg.shape[0] - J])[0]) for seg in segs])
+    lo, hi = keys.min(0).values, keys.max(0).values
+    dev = fs.device
+    over = torch.zeros(1, dtype=torch.int32, device=dev)
+    over_cells = torch.full((8192,), -1, dtype=torch.int32, device=dev)
+    wins, cnt = [], None
+    for seg in segs:
+        w, c = window_compact(seg, lo, hi, SEGMENT_SLOTS, cells, over, over_cells)      # one block: slab = all cells
+        wins.append(w[0])
+        cnt = c if cnt is None else cnt + c
+    net = 32
+    while net < 64 * S and net < S * SEGMENT_SLOTS:
+        net *= 2
+    q = select_from_top(torch.cat(wins), cnt.to(torch.int32), kt, over, over_cells, 0, min(net, 1024))
+    n_over = int(over.item())
+    if n_over:
+        if n_over > over_cells.numel():
+            return None
+        ids = torch.unique(over_cells[over_cells >= 0]).to(torch.int64)
+        q[ids] = _select_ranks_native(fs[:, ids].contiguous(), [int(rank)])[0]
+    return q
+
+
 def select_ranks(scores: torch.Tensor, ranks: Sequence[int]) -> torch.Tensor:
     """[len(ranks), *scores.shape[1:]]: the ranks[r]-th smallest along axis 0 (NaN-aware)."""
+    fs, rs = _rows(scores)
+    n, cells = fs.shape
+    ranks = [int(r) for r in ranks]
+    if n > 2048 and cells > 0 and len(ranks) <= 4 and os.environ.get("CPPRE_SEGMENTED_SELECT", "1") != "0":
+        parts = [_segmented_select(fs, r) for r in ranks]
+        if all(p is not None for p in parts):
+            return torch.stack(parts).reshape((len(ranks),) + tuple(scores.shape[1:]))
+    return _select_ranks_native(scores, ranks)
+
+
+def _select_ranks_native(scores: torch.Tensor, ranks: Sequence[int]) -> torch.Tensor:
+    """cppre_select_ranks: top-K streaming / register sort / radix select, chosen by the library."""
     lib = L.load()
     fs, rs = _rows(scores)
     n, cells = fs.shape

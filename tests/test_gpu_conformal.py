@@ -516,3 +516,31 @@ def test_mhd_joint_cp_flow_against_the_oracle(equation):
     np.testing.assert_array_equal(got, want)
     cells = prog.interior_cells(vc.shape)
     assert O.emp_cov_joint([-(q * m)[inner[1:]], (q * m)[inner[1:]]], mine[inner]) == float((got == cells).mean())
+
+
+@pytest.mark.parametrize("n,alpha", [(4096, 0.1), (3000, 0.1), (2500, 0.05), (8192, 0.02)])
+def test_segmented_select_for_long_columns_equals_numpy(n, alpha, monkeypatch):
+    """n > 2048 (beyond the register networks): the top-end order statistic through the candidate-window kernels
+    with row segments in the role of ranks (ops._segmented_select) -- bit-equal to np.quantile(method='higher')
+    and to the radix kernel it replaces, incl. NaN cells, ties, a constant column and +-inf."""
+    rng = np.random.default_rng(n)
+    cells = 1500
+    s = np.abs(rng.standard_normal((n, cells))).astype(np.float32)
+    s[rng.integers(0, n, 50), 3] = 0.75                  # ties
+    s[:, 4] = 1.25                                       # constant column
+    s[7, 5] = np.nan                                     # NaN cell -> NaN
+    s[rng.integers(0, n, 5), 6] = np.inf
+    s[rng.integers(0, n, 5), 8] = -np.inf
+    k = O.calibrate_rank(n, n, alpha)
+    want = O.calibrate(s, n, alpha)
+    t = cuda(s)
+    assert ops._segmented_select(t, k) is not None       # the request fits the segmented path
+    got = ops.select_ranks(t, [k])[0].cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+    monkeypatch.setenv("CPPRE_SEGMENTED_SELECT", "0")
+    np.testing.assert_array_equal(ops.select_ranks(t, [k])[0].cpu().numpy(), want)
+    monkeypatch.delenv("CPPRE_SEGMENTED_SELECT")
+    # a mid-column rank does not fit (the bracket would hold hundreds of samples): radix kernel, same answer
+    assert ops._segmented_select(t, n // 2) is None
+    np.testing.assert_array_equal(ops.select_ranks(t, [n // 2])[0].cpu().numpy(), np.sort(s, axis=0)[n // 2] if not np.isnan(s).any() else
+                                  np.where(np.isnan(s).any(axis=0), np.nan, np.sort(s, axis=0)[n // 2]))
