@@ -518,9 +518,9 @@ def test_mhd_joint_cp_flow_against_the_oracle(equation):
     assert O.emp_cov_joint([-(q * m)[inner[1:]], (q * m)[inner[1:]]], mine[inner]) == float((got == cells).mean())
 
 
-@pytest.mark.parametrize("n,alpha", [(4096, 0.1), (3000, 0.1), (2500, 0.05), (8192, 0.02)])
+@pytest.mark.parametrize("n,alpha", [(4096, 0.1), (3000, 0.1), (2500, 0.05), (8192, 0.02), (2048, 0.1), (1536, 0.1), (1100, 0.08)])
 def test_segmented_select_for_long_columns_equals_numpy(n, alpha, monkeypatch):
-    """n > 2048 (beyond the register networks): the top-end order statistic through the candidate-window kernels
+    """n > 1024 (where the register sort is slow, and beyond 2048 where only the radix select is left): the top-end order statistic through the candidate-window kernels
     with row segments in the role of ranks (ops._segmented_select) -- bit-equal to np.quantile(method='higher')
     and to the radix kernel it replaces, incl. NaN cells, ties, a constant column and +-inf."""
     rng = np.random.default_rng(n)
