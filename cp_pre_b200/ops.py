@@ -427,7 +427,7 @@ def select_ranks(scores: torch.Tensor, ranks: Sequence[int]) -> torch.Tensor:
     ranks = [int(r) for r in ranks]
     # long columns: above 1024 samples the register sort runs at < 200 Gscores/s and above 2048 only the radix
     # select is left; a calibration rank (near the top) is served by the segmented window select instead
-    if n > 1024 and cells > 0 and len(ranks) <= 4 and os.environ.get("CPPRE_SEGMENTED_SELECT", "1") != "0":
+    if n > 1024 and cells >= 32 and len(ranks) <= 4 and os.environ.get("CPPRE_SEGMENTED_SELECT", "1") != "0":
         parts = [_segmented_select(fs, r) for r in ranks]
         if all(p is not None for p in parts):
             return torch.stack(parts).reshape((len(ranks),) + tuple(scores.shape[1:]))

@@ -544,3 +544,16 @@ def test_segmented_select_for_long_columns_equals_numpy(n, alpha, monkeypatch):
     assert ops._segmented_select(t, n // 2) is None
     np.testing.assert_array_equal(ops.select_ranks(t, [n // 2])[0].cpu().numpy(), np.sort(s, axis=0)[n // 2] if not np.isnan(s).any() else
                                   np.where(np.isnan(s).any(axis=0), np.nan, np.sort(s, axis=0)[n // 2]))
+
+
+def test_calibrate_long_one_dimensional_scores_and_narrow_arrays():
+    """The Joint form on long score vectors (configs[1]: 2 048 calibration scores; here 4 096) and per-cell arrays
+    with only a few cells: too narrow for the segmented path, served by the library's own dispatch; bit-equal to
+    NumPy either way."""
+    rng = np.random.default_rng(12)
+    for n, cells in ((4096, 1), (2048, 1), (3000, 7), (1500, 31), (1500, 33)):
+        s = np.abs(rng.standard_normal((n, cells))).astype(np.float32)
+        arr = s[:, 0] if cells == 1 else s
+        for alpha in (0.1, 0.5):
+            got = calibrate(arr, n, alpha)
+            np.testing.assert_array_equal(np.asarray(got), O.calibrate(arr, n, alpha), err_msg=f"{n} {cells} {alpha}")
