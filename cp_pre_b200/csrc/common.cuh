@@ -165,12 +165,23 @@ CPPRE_TMA_TU(store_dyn_dec) CPPRE_TMA_TU(score_dyn_dec) CPPRE_TMA_TU(cover_dyn_d
     int launch_tin_##sfx(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream);
 CPPRE_TIN_TU(store) CPPRE_TIN_TU(score) CPPRE_TIN_TU(cover)
 CPPRE_TIN_TU(store_dec) CPPRE_TIN_TU(score_dec) CPPRE_TIN_TU(cover_dec)
+CPPRE_TIN_TU(store_x) CPPRE_TIN_TU(score_x) CPPRE_TIN_TU(cover_x)
 #undef CPPRE_TIN_TU
-inline int tin_eligible(const cppre_program_t* prog, const Prepared& P) {
+inline int tin_eligible_plain(const cppre_program_t* prog, const Prepared& P) {
     return P.epi.mode == CPPRE_EPI_STORE ? tin_eligible_store(prog, P)
          : P.epi.mode == CPPRE_EPI_SCORE ? tin_eligible_score(prog, P) : tin_eligible_cover(prog, P);
 }
+inline int tin_eligible_flex(const cppre_program_t* prog, const Prepared& P) {     // odd Nt, unaligned views
+    return P.epi.mode == CPPRE_EPI_STORE ? tin_eligible_store_x(prog, P)
+         : P.epi.mode == CPPRE_EPI_SCORE ? tin_eligible_score_x(prog, P) : tin_eligible_cover_x(prog, P);
+}
+inline int tin_eligible(const cppre_program_t* prog, const Prepared& P) {
+    return tin_eligible_plain(prog, P) || tin_eligible_flex(prog, P);
+}
 inline int launch_tin(const cppre_program_t* prog, const Prepared& P, cudaStream_t stream) {
+    if (!tin_eligible_plain(prog, P))
+        return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store_x(prog, P, stream)
+             : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score_x(prog, P, stream) : launch_tin_cover_x(prog, P, stream);
     if (P.dec_on)     // the decode fold lives in its own translation units: the plain kernels carry none of it
         return P.epi.mode == CPPRE_EPI_STORE ? launch_tin_store_dec(prog, P, stream)
              : P.epi.mode == CPPRE_EPI_SCORE ? launch_tin_score_dec(prog, P, stream) : launch_tin_cover_dec(prog, P, stream);

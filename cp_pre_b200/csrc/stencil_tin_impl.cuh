@@ -59,7 +59,13 @@ constexpr bool kDEC = CPPRE_TIN_DECODE != 0;
 #define CPPRE_TIN_ROLE 0
 #endif
 constexpr int kROLE = CPPRE_TIN_ROLE;
-constexpr bool kFLEX = kROLE == 1;
+// CPPRE_TIN_FLEX: the unaligned / odd-line-length machinery (always on in role 1).  Role 0 has it in separate
+// translation units (stencil_tinx_<mode>.cu) that take the FNO views the plain ones decline: odd Nt, bases or
+// sample strides that are not 16-byte aligned.
+#ifndef CPPRE_TIN_FLEX
+#define CPPRE_TIN_FLEX (CPPRE_TIN_ROLE == 1)
+#endif
+constexpr bool kFLEX = CPPRE_TIN_FLEX != 0;
 // logical arm served by each physical neighbour: I = within the line (flat -+1), M = march axis (register
 // pipeline), L = neighbouring line (flat -+line length)
 constexpr int A_IM = kROLE == 0 ? ARM_TM : ARM_YM, A_IP = kROLE == 0 ? ARM_TP : ARM_YP;

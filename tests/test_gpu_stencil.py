@@ -563,20 +563,43 @@ def test_t_innermost_kernel_takes_fno_views_in_place_and_is_bit_equal_to_the_con
             assert L.last_path() == "tin" and b.data_ptr() == outp.data_ptr() and torch.equal(a, b)
 
 
-def test_t_innermost_kernel_declines_what_it_cannot_take():
-    """Odd Nt (the y-neighbour is an 8-byte shared load), Taylor-4 taps and bf16 input fall back to the
-    transpose + contiguous kernels and still match; PATH_TIN then raises instead of running something else."""
+def test_t_innermost_kernel_odd_lines_unaligned_views_and_what_it_declines():
+    """FNO views the plain t-innermost units cannot stage -- odd Nt (the y-neighbour is no longer an 8-byte shared
+    load), a base that is not 16-byte aligned -- run on the flexible units (stencil_tinx_*: 4-byte cp.async staging,
+    scalar epilogue) and equal the contiguous run bit for bit, every epilogue; Taylor-4 taps and bf16 input still fall
+    back to the transpose + contiguous kernels and match; PATH_TIN on a contiguous tensor raises."""
     o, n = _programs_2d(), synth.NS
     prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], n["dx"], n["dy"], n["dt"], n["nu"])
-    v = torch.randn((2, 3, 33, 12, 20), device="cuda")
-    got = prog.residual(_tin(v), boundary=True)
-    assert L.last_path() != "tin" and torch.equal(got, prog.residual(v, boundary=True))
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for shape, misalign in (((2, 3, 33, 12, 20), False), ((2, 3, 25, 9, 7), False), ((2, 3, 50, 12, 20), True),
+                            ((1, 3, 101, 6, 10), True)):
+        v = torch.randn(shape, device="cuda", generator=g)
+        bs, nf, nt, nx, ny = shape
+        buf = torch.empty(v.numel() + 1, device="cuda")
+        raw = buf[1 if misalign else 0:][: v.numel()].view(bs, nf, nx, ny, nt)      # physical [BS,F,Nx,Ny,Nt]
+        raw.copy_(v.permute(0, 1, 3, 4, 2))
+        vt = raw.permute(0, 1, 4, 2, 3)
+        want = prog.residual(v, boundary=True)
+        got = prog.residual(vt, boundary=True)
+        assert L.last_path() == "tin", (shape, misalign)
+        assert torch.equal(got, want), (shape, misalign)
+        ref = torch.randn(want.shape, device="cuda", generator=g)
+        w = torch.rand(want.shape[1:], device="cuda", generator=g) + 0.1
+        for interior in (True, False):
+            a = prog.joint_scores(v, inv_modulation=w, ref=ref, interior=interior)
+            b = prog.joint_scores(vt, inv_modulation=w, ref=_tin(ref), interior=interior)
+            assert L.last_path() == "tin" and torch.equal(a, b), (shape, interior)
+            a = prog.coverage_counts(v, 0.7, half=w, centre=ref, interior=interior)
+            b = prog.coverage_counts(vt, 0.7, half=w, centre=ref, interior=interior)
+            assert L.last_path() == "tin" and torch.equal(a, b), (shape, interior)
     prog.path = L.PATH_TIN
     with pytest.raises(NotImplementedError):
-        prog.residual(_tin(v), boundary=True)
-    with pytest.raises(NotImplementedError):
-        prog.residual(v, boundary=True)                                  # contiguous input is not t-innermost
+        prog.residual(torch.randn((2, 3, 16, 12, 20), device="cuda"), boundary=True)     # contiguous input is not t-innermost
     prog.path = L.PATH_AUTO
+    lap4 = programs.linear(_mods()["2d"].ConvOperator(("x", "y"), 2, taylor_order=4))     # 5x5x5 taps
+    u = torch.randn((2, 16, 12, 20), device="cuda", generator=g)
+    assert torch.equal(lap4.residual(_tin(u), boundary=True), lap4.residual(u, boundary=True))
+    assert L.last_path() != "tin"
     vb = torch.randn((2, 3, 16, 12, 128), device="cuda").to(torch.bfloat16)
     assert torch.equal(prog.residual(_tin(vb), boundary=True), prog.residual(vb, boundary=True))
     assert L.last_path() != "tin"
