@@ -206,9 +206,6 @@ class StencilOperator:
     _flavour = "2d"
 
     # --- construction ---------------------------------------------------------------
-    def _build(self, domain, order, scale, taylor_order, device, requires_grad):
-        raise NotImplementedError
-
     def _select_conv(self, conv):
         if conv == "direct":
             self.conv = self.convolution
