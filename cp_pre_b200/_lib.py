@@ -12,6 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libcppre.so")
 
 MAX_FIELDS, MAX_SLOTS, MAX_SCALARS, MAX_TAPS = 6, 6, 12, 512
+NOALLOC_MAX_RANKS = 16      # CPPRE_NOALLOC_MAX_RANKS
 
 OK, ERR_BAD_ARG, ERR_UNSUPPORTED, ERR_CUDA = 0, 1, 2, 3
 
@@ -91,6 +92,7 @@ SIGNATURES = {
     "cppre_radix_select_begin": (C.c_int, [_P, _P, _I64, _P]),
     "cppre_radix_select_hist": (C.c_int, [_P, _I64, _P, C.c_int32, _P, _P]),
     "cppre_radix_select_pick": (C.c_int, [_P, _P, C.c_int32, _P, _P]),
+    "cppre_radix_select_ranks_noalloc": (C.c_int, [_P, _I64, C.POINTER(_I64), C.c_int32, _P, _P]),
     "cppre_inside_count": (C.c_int, [_P, _I64, _P, _I64, _P, _I64, _I64, _I64, _P, _P]),
     "cppre_inside_count_band": (C.c_int, [_P, _I64, _P, _I64, _P, C.c_float, _I64, _I64, _P, _P]),
     "cppre_transpose_inner": (C.c_int, [_P, _I64, _I64, _I64, _I64, _P, _P]),

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <initializer_list>
+#include <mutex>
 #include <type_traits>
 
 #include "common.cuh"
@@ -1623,3 +1624,84 @@ int cppre_inside_count_band(const float* d_y, int64_t ys, const float* d_centre,
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// K3d without caller scratch (cppre_radix_select_ranks_noalloc)
+//
+// For hosts that cannot give the radix select its 261 words of state per rank because they have no
+// device allocator to ask (all of HBM sits in somebody else's arena, or the binding only forwards
+// field buffers, or cudaMalloc's implicit synchronisation is unwelcome where they call from).  The
+// state lives in the array below: device memory that belongs to the library image, present on every
+// GPU that loads it.
+//
+// `g_noalloc_scratch` as written in HOST code is only the host-side handle of the symbol, not a
+// device address -- a kernel handed that value would fault, or quietly scribble over host memory on
+// a system where the GPU can reach it.  The address kernels may use comes from cudaGetSymbolAddress,
+// asked once per device with that device current (each device has its own copy of the array).
+// ------------------------------------------------------------------------------------------
+namespace {
+constexpr int kNoallocSlotWords = 384;   // one rank: state at word 0 (4 words), counters at word 64 (257 words)
+constexpr int kNoallocHistWord = 64;
+static_assert(kNoallocHistWord + 257 <= kNoallocSlotWords, "slot too small for the counters");
+static_assert(kNoallocSlotWords * 4 * CPPRE_NOALLOC_MAX_RANKS == CPPRE_NOALLOC_SCRATCH_BYTES,
+              "header constant out of step with the array");
+}  // namespace
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[kNoallocSlotWords * CPPRE_NOALLOC_MAX_RANKS];
+
+namespace {
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_addr[cppre::kMaxDevices];   // per device, filled on the first call there
+
+// Device address of g_noalloc_scratch on the CURRENT device.
+int noalloc_scratch(uint32_t** out) {
+    int dev = -1;
+    CPPRE_CHECK_CUDA(cudaGetDevice(&dev));
+    CPPRE_REQUIRE(dev >= 0 && dev < cppre::kMaxDevices, CPPRE_ERR_UNSUPPORTED, "device index %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_addr[dev] == nullptr) {
+        void* p = nullptr;
+        CPPRE_CHECK_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        CPPRE_REQUIRE(p != nullptr, CPPRE_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_addr[dev] = static_cast<uint32_t*>(p);
+    }
+    *out = g_noalloc_addr[dev];
+    return CPPRE_OK;
+}
+}  // namespace
+
+extern "C" int cppre_radix_select_ranks_noalloc(const float* d_x, int64_t n, const int64_t* h_ranks, int32_t n_ranks,
+                                                float* d_out, void* stream) {
+    CPPRE_REQUIRE(n >= 0 && n_ranks >= 0, CPPRE_ERR_BAD_ARG, "negative size");
+    CPPRE_REQUIRE(n_ranks <= CPPRE_NOALLOC_MAX_RANKS, CPPRE_ERR_UNSUPPORTED,
+                  "n_ranks = %d is more than CPPRE_NOALLOC_MAX_RANKS = %d: the built-in scratch holds one radix "
+                  "state per rank; split the call or use cppre_radix_select_begin/hist/pick with your own scratch",
+                  (int)n_ranks, CPPRE_NOALLOC_MAX_RANKS);
+    CPPRE_REQUIRE(n < (int64_t(1) << 32), CPPRE_ERR_UNSUPPORTED,
+                  "n = %lld does not fit the 32-bit counters of the built-in scratch (limit 2^32 - 1)", (long long)n);
+    if (n_ranks == 0) return CPPRE_OK;
+    CPPRE_REQUIRE(h_ranks && d_out && (d_x || n == 0), CPPRE_ERR_BAD_ARG, "null pointer");
+    for (int r = 0; r < n_ranks; ++r)
+        CPPRE_REQUIRE(h_ranks[r] >= 0 && h_ranks[r] < (int64_t(1) << 32), CPPRE_ERR_BAD_ARG, "rank out of range");
+    uint32_t* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t blocks = (n + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    for (int r = 0; r < n_ranks; ++r) {
+        uint32_t* state = scratch + (size_t)r * kNoallocSlotWords;
+        uint32_t* hist = state + kNoallocHistWord;
+        // the previous call's leftovers end here: state = {0, 0, k, 0}, all 257 counters = 0
+        radix_begin_kernel<<<2, kThreads, 0, st>>>(state, hist, (uint32_t)h_ranks[r]);
+        CPPRE_CHECK_LAUNCH();
+        for (int pass = 0; pass < 4; ++pass) {
+            if (n > 0) {
+                radix_hist_dev_kernel<<<(unsigned)blocks, kThreads, 0, st>>>(d_x, n, state, pass, hist);
+                CPPRE_CHECK_LAUNCH();
+            }
+            radix_pick_kernel<<<1, kThreads, 0, st>>>(hist, state, pass, d_out + r);
+            CPPRE_CHECK_LAUNCH();
+        }
+    }
+    return CPPRE_OK;
+}

@@ -252,6 +252,43 @@ int cppre_radix_select_hist(const float* d_x, int64_t n, const uint32_t* d_state
                             uint32_t* d_hist, void* stream);
 int cppre_radix_select_pick(uint32_t* d_hist, uint32_t* d_state, int32_t pass, float* d_out, void* stream);
 
+/* ---- K3d for callers that have no device allocator ---------------------------------------
+ * No counterpart in the reference (it never manages device memory itself).
+ *
+ * The begin/hist/pick calls above need 261 words of device scratch (state + counters) per rank,
+ * and somebody has to own them.  Some hosts of this library cannot provide that: a solver or
+ * serving worker whose framework handed every byte of HBM to an arena the plugin call site has no
+ * handle to, a coupling layer written in a language that only passes the field buffers through,
+ * or a section of a time loop where the device-wide synchronisation hidden inside
+ * cudaMalloc/cudaFree is not acceptable.  For those callers this entry point does the whole
+ * device-state radix select -- begin, then four (histogram, pick) passes, for each requested rank
+ * -- with the state and counters in a fixed array that is part of the library image itself.
+ *
+ *   d_out[r] = the h_ranks[r]-th smallest (0-based) of d_x[0..n),  r < n_ranks;
+ *              NaN when some score is a NaN or the rank is >= n (the rules of
+ *              cppre_radix_select, and bit-equal to it).
+ *
+ * d_x (n floats) and d_out (n_ranks floats) are the caller's; h_ranks is a host array (the alpha
+ * grid of Marginal/NS_Residuals_CP.py:331-337 applied to Joint scores is the typical use).
+ *
+ * Limits and rules
+ *  - n_ranks <= CPPRE_NOALLOC_MAX_RANKS and n < 2^32 (the counters are 32-bit); anything larger
+ *    is refused with CPPRE_ERR_UNSUPPORTED and a message, nothing is launched.
+ *  - The array is CPPRE_NOALLOC_SCRATCH_BYTES of device memory on every GPU that loads the
+ *    library, held until the process exits whether or not this entry point is ever called.
+ *  - The FIRST call on each device looks the array's device address up (cudaGetSymbolAddress,
+ *    which may load the module); make that first call with the device current and before any
+ *    stream capture begins.  Later calls only enqueue kernels on `stream`.
+ *  - It calls no cudaMalloc / cudaFree / allocating library routine, on any call.
+ *  - All calls on one device share the one array.  Each call re-initialises the part it uses,
+ *    so it does not matter what the previous call left behind, but two calls that can be in
+ *    flight on the GPU at the same time (different streams, different host threads) race on it:
+ *    order them on one stream or with events. */
+#define CPPRE_NOALLOC_MAX_RANKS 16
+#define CPPRE_NOALLOC_SCRATCH_BYTES (CPPRE_NOALLOC_MAX_RANKS * 1536)
+int cppre_radix_select_ranks_noalloc(const float* d_x, int64_t n, const int64_t* h_ranks, int32_t n_ranks,
+                                     float* d_out, void* stream);
+
 /* ---- K3w: multi-GPU marginal quantile (batch axis sharded over ranks) --------------------
  * No counterpart in the reference (it is single-process); these three calls replace the naive
  * all-to-all of the whole score tensor in front of np.quantile (Marginal/NS_Residuals_CP.py:311):
