@@ -98,6 +98,14 @@ int prepare(const cppre_program_t* prog, const int64_t shape[4], const cppre_fie
         CPPRE_REQUIRE(!(epi->flags & CPPRE_FLAG_IN_BF16), CPPRE_ERR_UNSUPPORTED,
                       "the decode fold takes fp32 fields only");
         CPPRE_REQUIRE(same, CPPRE_ERR_UNSUPPORTED, "the decode fold needs 'same'-padded derivative slots");
+        // The fold is only claimed on the one-cell-deep interior; a tap two or more cells out reaches the padding
+        // from there, and the reference pads the DECODED field (offset, not zero, would be missing).
+        for (int t = 0; t < ntap; ++t)
+            CPPRE_REQUIRE(P.taps.o2[t] >= -1 && P.taps.o2[t] <= 1 && P.taps.o1[t] >= -1 && P.taps.o1[t] <= 1 &&
+                              P.taps.o0[t] >= -1 && P.taps.o0[t] <= 1,
+                          CPPRE_ERR_UNSUPPORTED,
+                          "the decode fold needs every non-zero tap within one cell of the centre (3-point stencils); "
+                          "decode the fields explicitly for wider stencils");
         for (int s = 0; s < prog->n_slots; ++s) {
             double sum = 0.0;       // sum of the slot's taps: what the slot returns on a constant field of ones
             for (int t = P.taps.begin[s]; t < P.taps.begin[s + 1]; ++t) sum += (double)P.taps.c[t];

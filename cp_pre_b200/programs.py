@@ -120,6 +120,18 @@ class ResidualProgram:
         return ([sc[j] for j in idx] + [1.0] * (n_fields - len(idx)),
                 [of[j] for j in idx] + [0.0] * (n_fields - len(idx)))
 
+    def _fold_ok(self):
+        """Whether the decode fold reproduces the reference on the kept interior ``[1:-1]``: only while no non-zero
+        tap lies more than one cell from the centre.  A Taylor-4/6 stencil reaches the zero padding from the first
+        kept layer, where the reference has padded the DECODED field; those operators take the explicit decode."""
+        for k in self._slots()[0]:
+            for ax, s in enumerate(k.shape):
+                if s > 3:
+                    outer = [i for i in range(s) if abs(i - s // 2) > 1]
+                    if np.any(np.take(np.asarray(k), outer, axis=ax) != 0):
+                        return False
+        return True
+
     def _decoded(self, vars_, decode, keep_graph=False):
         """The explicit decode (one elementwise pass): what the fold replaces.  Used where the fold is not
         defined -- boundary=True results (in the reference the shell cells see the zero padding of the DECODED
@@ -167,7 +179,7 @@ class ResidualProgram:
         normaliser object: the residual of ``scale * vars + offset`` (``out_normalizer.decode(pred)``,
         [ref: Joint/Wave_Residuals_CP.py:213-217]) with the decode folded into the kernel's loads."""
         staged = ops.Staged(vars_)
-        if decode is not None and (boundary or self._needs_grad(vars_)):
+        if decode is not None and (boundary or self._needs_grad(vars_) or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_):
             full = self._residual_autograd(vars_)
@@ -186,7 +198,8 @@ class ResidualProgram:
         CUDA destination (e.g. a batch slice of a larger score tensor); ``decode`` as in ``residual``
         (with ``out`` / boundary=True the shell cells of the full field are not those of the decoded field)."""
         staged = ops.Staged(vars_)
-        if decode is not None and ((boundary and out is None) or self._needs_grad(vars_) or ops.needs_grad(ref)):
+        if decode is not None and ((boundary and out is None) or self._needs_grad(vars_) or ops.needs_grad(ref)
+                                   or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref):
             full = self._residual_autograd(vars_)
@@ -207,7 +220,8 @@ class ResidualProgram:
         are written.  ``inv_modulation`` / ``ref`` are FULL-size ([Nt,Nx(,Ny)] / [BS,Nt,...]);
         ``decode`` as in ``residual`` (folded when ``interior``)."""
         staged = ops.Staged(vars_)
-        if decode is not None and (not interior or self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation)):
+        if decode is not None and (not interior or self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation)
+                                   or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation):
             v = self.abs_scores(vars_, ref=ref, boundary=True)
@@ -231,7 +245,7 @@ class ResidualProgram:
         With ``interior`` the shell cells the reference crops are not counted
         [ref: Marginal/NS_Residuals_CP.py:311-312,336-337; Joint/NS_Residuals_CP.py:312,336]."""
         staged = ops.Staged(vars_)
-        if decode is not None and not interior:
+        if decode is not None and (not interior or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode), None
         w = None if half is None else self._unsq(ops.to_cuda(half))
         r = None if centre is None else self._unsq(ops.to_cuda(centre))

@@ -133,7 +133,12 @@ enum {
      * the field, and raw field factors are decoded at the output cell.  Results are those of the decoded field
      * on the INTERIOR (the cells the reference keeps, [...,1:-1,1:-1,1:-1]); cells whose stencil reaches into
      * the zero padding see the padding of the STORED field (zeros before the decode) and are unspecified:
-     * crop them (STORE) or set the INTERIOR flags (SCORE / COVER).  fp32 fields only. */
+     * crop them (STORE) or set the INTERIOR flags (SCORE / COVER).  fp32 fields only.
+     * Because that interior is ONE cell deep, the fold is offered only while no non-zero tap lies more than one
+     * cell from the centre (the 3-point stencils every reference script builds).  A wider stencil (Taylor order
+     * 4 / 6) would reach the padding from the first kept layer, where the reference pads the DECODED field and
+     * the fold would be off by offset_f * (taps outside the field): such a request is refused with
+     * CPPRE_ERR_UNSUPPORTED -- decode the fields explicitly and call without the flag. */
     CPPRE_FLAG_DECODE = 32,
     /* bf16-input mode: every cppre_field_t::d_data points to bfloat16 elements (strides in
      * elements), staged as bf16 and widened to fp32 in the kernel; arithmetic, reference, weight

@@ -710,6 +710,62 @@ def test_autograd_through_nonlinear_programs_kernel_tensor_and_spectral_paths():
     assert x.grad is not None and float(x.grad.abs().sum()) > 0
 
 
+def _every_program():
+    """One instance of every CPPRE_PROG_* kind with an input of the right shape: (name, program, vars)."""
+    o, m1, c, b = _programs_2d(), _mods()["1d"], synth.NS, synth.BURGERS
+    C2 = _mods()["2d"].ConvOperator
+    grid = (2, 6, 12, 16)
+    one = lambda seed: cuda(synth.fields(seed, 1, grid))[:, 0]
+    out = [("linear", programs.linear(_wave_op()), one(1)),
+           ("linear_1d", programs.linear(m1.ConvOperator("x", 2)), one(2)[:, :, 0].contiguous()),   # the nd == 2 squeeze path
+           ("burgers", programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                                        b["dx"], b["dt"], b["nu"]), one(3)[:, :, 0].contiguous()),
+           ("ns_continuity", programs.ns_continuity(o["D_x"], o["D_y"], c["dx"], c["dy"]), cuda(synth.fields(4, 3, grid))),
+           ("ns_momentum", programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], c["dx"], c["dy"], c["dt"],
+                                                c["nu"]), cuda(synth.fields(5, 3, grid)))]
+    for eq in ("continuity", "momentum", "energy", "induction", "gauss"):
+        out.append(("mhd_" + eq, programs.mhd(eq, o["D_t"], o["D_x"], o["D_y"], synth.MHD["gamma"]),
+                    cuda(synth.fields(6, 6, grid, positive=(0, 3)))))
+    gam = torch.tensor(5 / 3, dtype=torch.float32)
+    D = [C2(domain="t", order=1, scale=1), C2(domain="x", order=1, scale=1), C2(domain="y", order=1, scale=1),
+         C2(domain="x", order=2, scale=gam), C2(domain="y", order=2, scale=gam)]
+    R = torch.linspace(1.5, 2.5, grid[-1])
+    for eq, coef in (("continuity", 3.4), ("temperature", 2.25e-7)):
+        out.append(("jorek_" + eq, programs.jorek(eq, *D, R, torch.tensor(coef), gam),
+                    cuda(synth.fields(7, 3, grid, positive=(0, 2)))))
+    return out
+
+
+def test_autograd_forward_equals_the_fused_forward_for_every_program_kind():
+    """the gradient path restates all programs in torch (programs._FORMULAS) beside csrc/programs.cuh.
+    This pins the two copies together: for EVERY program kind (and the 1-D squeeze path) the residual computed on
+    the autograd graph equals the fused kernel's on the same input, fp32 tolerance (2e-5 of max|ref|: the two sides
+    order their fp32 sums differently)."""
+    seen = set()
+    for name, prog, v in _every_program():
+        fused = prog.residual(v)
+        assert not fused.requires_grad
+        on_graph = prog.residual(v.clone().requires_grad_(True))
+        assert on_graph.requires_grad, name
+        assert_close_rel(on_graph.detach().cpu().numpy(), fused.cpu().numpy(), 2e-5, name)
+        seen.add(prog.kind)
+    assert seen == set(programs._FORMULAS), "a program kind has no autograd-vs-fused check"
+
+
+def test_burgers_gradient_equals_torch_autograd_through_the_plain_expression():
+    """Gradcheck-style comparison for a 1-D program: d(sum res^2)/du through the library's autograd path against
+    torch.autograd through the plain PyTorch fp32 expression of the same residual (oracle/torch_port.py)."""
+    from oracle import torch_port as TP
+    b, m1 = synth.BURGERS, _mods()["1d"]
+    prog = programs.burgers(m1.ConvOperator("t", 1), m1.ConvOperator("x", 1), m1.ConvOperator("x", 2),
+                            b["dx"], b["dt"], b["nu"])
+    u = cuda(synth.fields(11, 1, (3, 10, 4, 24)))[:, 0, :, 0].contiguous().requires_grad_(True)
+    (prog.residual(u) ** 2).sum().backward()
+    u2 = u.detach().cpu().clone().requires_grad_(True)
+    (TP.burgers(u2, b["dx"], b["dt"], b["nu"]) ** 2).sum().backward()
+    assert_close_rel(u.grad.cpu().numpy(), u2.grad.numpy(), 2e-5, "d loss / d u (Burgers)")
+
+
 class _MinMax:
     """Shape of the normaliser the scripts use: attributes a, b; decode(x) = (x - b) / a
     [ref: Tests/test_ns.py:111-134; class in the un-vendored Neural_PDE package]."""
@@ -779,6 +835,19 @@ def test_normaliser_decode_fold_equals_the_residual_of_the_decoded_field():
     got = wave.residual(cuda(u), decode=nrm)
     assert L.last_path() == "tma"
     assert_close_rel(got.cpu().numpy(), want, TOL)
+    # Taylor-4 stencil (5 points per axis): from the first kept layer it reaches the padding, where the reference
+    # pads the DECODED field, so the fold does not apply.  The library refuses the flag; the program object decodes
+    # explicitly and still equals the oracle on the decoded field (an offset != 0 is what would expose a wrong fold)
+    lap4 = programs.linear(_mods()["2d"].ConvOperator(("x", "y"), 2, taylor_order=4))
+    assert not lap4._fold_ok() and wave._fold_ok()
+    u4 = synth.fields(4, 1, (2, 8, 16, 128))[:, 0]
+    dec4 = (u4 * np.float32(2.0) + np.float32(0.75)).astype(np.float32)
+    want4 = O.correlate(dec4, O.build_kernel("2d", ("x", "y"), 2, taylor_order=4))[:, 1:-1, 1:-1, 1:-1]
+    got4 = lap4.residual(cuda(u4), decode=(2.0, 0.75))
+    assert_close_rel(got4.cpu().numpy(), want4, TOL)
+    assert_close_rel(lap4.abs_scores(cuda(u4), decode=(2.0, 0.75)).cpu().numpy(), np.abs(want4), TOL)
+    with pytest.raises(NotImplementedError, match="within one cell"):
+        ops.run_program(L.PROG_LINEAR, [cuda(u4)], *lap4._slots(), [], decode=([2.0], [0.75]))
     # 1-D + time (batch-rows TMA mode): Burgers with a scalar decode
     import ConvOps_1d as C1
     b = synth.BURGERS
