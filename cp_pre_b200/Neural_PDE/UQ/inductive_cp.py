@@ -35,7 +35,11 @@ def calibrate_rank(n_rows, n, alpha, dtype=np.float32):
     NumPy float q is cast to the array's dtype first, ``numpy/lib/_function_base_impl.py: quantile``):
     float32 for the float32 score arrays this library processes, float64 when the caller hands over
     float64 scores.  The two differ when n != n_rows (rows=14, n=13, alpha=0.5: index 8 in float32
-    arithmetic, 7 in float64).  q outside [0,1] raises like NumPy."""
+    arithmetic, 7 in float64).  q outside [0,1] raises like NumPy.
+
+    This follows NumPy >= 2 (the version this image and the golden vectors use).  NumPy 1.x kept a Python-float
+    q in float64 whatever the array's dtype, so on such an install ``np.quantile`` on float32 scores would pick
+    the float64 index; the library does not branch on ``np.__version__`` -- its contract is the NumPy 2 result."""
     q = calibrate_level(n, alpha)
     if not (0.0 <= q <= 1.0):
         raise ValueError("Quantiles must be in the range [0, 1]")

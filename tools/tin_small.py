@@ -1,4 +1,4 @@
-"""Small t-innermost cases for compute-sanitizer (tools/gpu_r2d.sh): every mode, ragged tiles, both Nt%4 classes."""
+"""Small t-innermost cases for a sanitizer / bounds-check pass: every mode, ragged tiles, both Nt%4 classes."""
 import os
 import sys
 
