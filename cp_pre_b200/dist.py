@@ -68,38 +68,54 @@ def _world(group=None) -> int:
 # ---------------------------------------------------------------------------------------
 # Joint: modulation over the global batch
 # ---------------------------------------------------------------------------------------
-_N_CACHE = {}
+_SIDE_STREAMS = {}
+
+
+def _rank_counts(n_local: int, group) -> list:
+    """Every rank's local sample count, as one all-reduce that EVERY rank issues on EVERY call.
+
+    There is deliberately no cache here: whether a rank may skip the collective cannot be decided from
+    its own ``n_local`` (the global total is not a function of one rank's count), so a rank-local cache
+    lets ranks disagree on hit vs miss -- one raises from a stale entry while its peer waits alone in
+    the all-reduce.  Under NCCL the collective and the host read run on a side stream that has nothing
+    else queued, so they do not wait for (or stall) the K1 work already enqueued on the caller's stream."""
+    w, me = _world(group), dist.get_rank(group)
+    mine = [0] * w
+    mine[me] = int(n_local)
+    if dist.get_backend(group) != "nccl":
+        t = torch.tensor(mine, dtype=torch.int64)
+        dist.all_reduce(t, group=group)
+        return t.tolist()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    side = _SIDE_STREAMS.get(dev.index)
+    if side is None:
+        side = _SIDE_STREAMS[dev.index] = torch.cuda.Stream(dev)
+    with torch.cuda.stream(side):
+        t = torch.tensor(mine, dtype=torch.int64, device=dev)
+        dist.all_reduce(t, group=group)
+        return t.tolist()                       # synchronises the side stream only
 
 
 def global_count(n_local: int, group=None, require_equal: bool = False) -> int:
-    """Sum of the ranks' local sample counts.  One tiny all-reduce + host read the first time a
-    (group, n_local) pair is seen, cached afterwards, so steady-state steps have no host round
-    trip.  ``require_equal`` raises when the shards are uneven (``shard_range`` produces such
-    shards whenever BS % world != 0; the windowed marginal quantile and the equal-count gathers
-    assume equal shards and would otherwise return a wrong quantile or hang in NCCL)."""
-    w = _world(group)
-    if w == 1:
+    """Sum of the ranks' local sample counts (one small all-reduce per call, see ``_rank_counts``).
+    ``require_equal`` raises -- on every rank alike -- when the shards are uneven (``shard_range``
+    produces such shards whenever BS % world != 0; the windowed marginal quantile and the equal-count
+    gathers assume equal shards and would otherwise return a wrong quantile or hang in NCCL)."""
+    if _world(group) == 1:
         return int(n_local)
-    key = (0 if group is None else id(group), int(n_local))
-    if key not in _N_CACHE:
-        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
-        t = torch.tensor([n_local, -n_local], dtype=torch.int64, device=dev)
-        s = torch.tensor([n_local], dtype=torch.int64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
-        dist.all_reduce(s, group=group)
-        _N_CACHE[key] = (int(s.item()), int(t[0].item()), -int(t[1].item()))
-    total, n_max, n_min = _N_CACHE[key]
+    counts = _rank_counts(n_local, group)
+    n_min, n_max = min(counts), max(counts)
     if require_equal and n_max != n_min:
         raise ValueError(f"uneven batch shards (between {n_min} and {n_max} samples per rank): this exchange needs the "
                          "same number of samples on every rank -- pad or trim the batch to a multiple of the world size")
-    return total
+    return int(sum(counts))
 
 
 def merge_moments(mean: torch.Tensor, m2: torch.Tensor, count: float, group=None):
     """Chan et al. pairwise merge of per-rank (count, mean, M2) -> global (mean, M2, count) with
     two all-reduces of [cells] fp64:  mean = sum(n_r mean_r)/N;  M2 = sum(M2_r + n_r (mean_r - mean)^2).
-    The global count comes from ``global_count`` (cached), so no host round trip sits between
-    the two all-reduces."""
+    The global count comes from ``global_count`` before the first of them, so no host round trip
+    sits between the two all-reduces."""
     if _world(group) == 1:
         return mean, m2, count
     total = float(global_count(int(count), group))

@@ -134,6 +134,15 @@ def _worker(rank, world, port, out):
         D.joint_quantile_device(my_scores, 40, select_fn=_np_radix_select)
     # uneven shards: the equal-count exchanges refuse instead of hanging / answering wrongly
     assert D.global_count(lo + 1 if world > 1 else 1) == sum(D.shard_range(40, r, world)[0] + 1 for r in range(world))
+    # two calibration sets of different size in one process: shards (3, 2, ..) then (3, 3, ..) then back.  Rank 0
+    # sees n_local = 3 every time; every rank must still take part in every count exchange and agree on the answer
+    if world > 1:
+        first = 3 if rank == 0 else 2
+        assert D.global_count(first) == 3 + 2 * (world - 1)
+        with pytest.raises(ValueError, match="uneven batch shards"):
+            D.global_count(first, require_equal=True)
+        assert D.global_count(3, require_equal=True) == 3 * world
+        assert D.global_count(first) == 3 + 2 * (world - 1)
     uneven = torch.from_numpy(np.abs(full[: 3 + rank]))
     with pytest.raises(ValueError, match="uneven batch shards"):
         D.marginal_quantiles(uneven, [1], select_fn=_np_select)
