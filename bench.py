@@ -107,41 +107,85 @@ def k1_traffic(workload, equation=None, points=None):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (recipe in B200_PROFILING.md)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region (the recipe's clocks line in B200_PROFILING.md).
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    Read through NVML inside this process: one sample when the region opens, one every 20 ms from a thread while it
+    runs, one when it closes -- so even a region of a few milliseconds has a record, and eight ranks starting at once
+    do not wait for eight `nvidia-smi` processes to come up (round 2's N=8 lines had `samples: 0` for that reason).
+    If NVML cannot be used the region is covered by two synchronous `nvidia-smi` queries instead; a region that ends
+    with no sample at all raises: a number without a clock record is not a measurement."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index, period=0.02):
+        self.index, self.period, self.rows, self.source = index, period, [], None
+        self.nv = self.handle = self.thread = None
+        self.stop = threading.Event()
+
+    def _open_nvml(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        try:        # the CUDA ordinal is not the NVML index under CUDA_VISIBLE_DEVICES: go by UUID
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            self.handle = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid if not uuid.startswith("GPU-") else uuid).encode())
+        except Exception:
+            self.handle = nv.nvmlDeviceGetHandleByIndex(self.index)
+        self.nv, self.max_mhz = nv, float(nv.nvmlDeviceGetMaxClockInfo(self.handle, nv.NVML_CLOCK_SM))
+
+    def _sample(self):
+        if self.nv is not None:
+            nv = self.nv
+            get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            mask = int(get(self.handle))
+            self.rows.append((float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)), self.max_mhz,
+                              [name for bit, name in self.REASONS if mask & bit]))
+            return
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().splitlines()
+        c = [x.strip() for x in out[0].split(",")]
+        self.rows.append((float(c[0]), float(c[1]),
+                          [n for n, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[2:6])
+                           if v.lower() == "active"]))
+
+    def _loop(self):
+        while not self.stop.wait(self.period):
+            try:
+                self._sample()
+            except Exception:
+                return
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
+            self._open_nvml()
+            self.source = "nvml in-process, 20 ms"
         except Exception:
-            self.proc = None
+            self.nv, self.source = None, "nvidia-smi, at both ends of the region"
+        try:
+            self._sample()
+        except Exception:
+            pass
+        if self.nv is not None:
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
-
     def __exit__(self, *a):
-        if self.proc:
-            time.sleep(0.15)
-            self.proc.terminate()
-            self.t.join(timeout=2)
+        self.stop.set()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        try:
+            self._sample()
+        except Exception:
+            pass
+        if not self.rows and a[0] is None:
+            raise RuntimeError("no clock sample could be taken during the timed region (NVML and nvidia-smi both failed)")
 
     def summary(self):
-        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 8 for i in range(4) if r[4 + i].lower() == "active"})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        sm = [r[0] for r in self.rows]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(r[1] for r in self.rows) if sm else None,
+                "reasons": sorted({n for r in self.rows for n in r[2]}), "samples": len(sm), "source": self.source}
 
 
 # ----------------------------------------------------------------------------------------
