@@ -22,6 +22,24 @@ from . import _lib as L
 from . import ops
 
 
+_WARNED_UNFUSED = set()
+
+
+def _warn_unfused(entry: str):
+    """Once per entry point: a scoring call (calibration / UQ, not a training loss) whose input carries
+    ``requires_grad`` -- typically a model output produced outside ``torch.no_grad()`` -- leaves the fused kernel
+    for the differentiable path: one K1 launch per derivative slot plus torch elementwise ops, and a full-size
+    score tensor.  Correct, but several times slower and heavier; say so instead of degrading silently."""
+    if entry in _WARNED_UNFUSED:
+        return
+    _WARNED_UNFUSED.add(entry)
+    import warnings
+    warnings.warn(f"cp_pre_b200: {entry}() received a tensor that requires grad and is taking the unfused differentiable "
+                  "path (one kernel launch per derivative, the full score field materialised). If no gradient is "
+                  "wanted, call it under torch.no_grad() or pass .detach() to get the fused kernel.",
+                  RuntimeWarning, stacklevel=3)
+
+
 class ResidualProgram:
     """``kind`` evaluated with taps from ``operators`` on the fields ``field_index`` of vars."""
 
@@ -202,6 +220,7 @@ class ResidualProgram:
                                    or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref):
+            _warn_unfused("abs_scores")
             full = self._residual_autograd(vars_)
             if ref is not None:
                 full = full - ops.to_cuda(ref, keep_graph=True)
@@ -224,6 +243,7 @@ class ResidualProgram:
                                    or not self._fold_ok()):
             vars_, decode = self._decoded(vars_, decode, keep_graph=True), None
         if self._needs_grad(vars_) or ops.needs_grad(ref, inv_modulation):
+            _warn_unfused("joint_scores")
             v = self.abs_scores(vars_, ref=ref, boundary=True)
             if inv_modulation is not None:
                 v = v * ops.to_cuda(inv_modulation, keep_graph=True)

@@ -766,6 +766,23 @@ def test_burgers_gradient_equals_torch_autograd_through_the_plain_expression():
     assert_close_rel(u.grad.cpu().numpy(), u2.grad.numpy(), 2e-5, "d loss / d u (Burgers)")
 
 
+def test_scoring_call_on_a_grad_carrying_input_warns_once_about_the_unfused_path():
+    """a scoring entry point handed a tensor that requires grad (a model output made outside no_grad)
+    leaves the fused kernel for the differentiable path; that is announced once per entry point, not silent."""
+    import warnings
+    o, c = _programs_2d(), synth.NS
+    prog = programs.ns_momentum(o["D_t"], o["D_x"], o["D_y"], o["D_xx_yy"], c["dx"], c["dy"], c["dt"], c["nu"])
+    v = cuda(synth.fields(5, 3, (2, 6, 12, 16)))
+    programs._WARNED_UNFUSED.clear()
+    with pytest.warns(RuntimeWarning, match="unfused differentiable path"):
+        on_graph = prog.joint_scores(v.clone().requires_grad_(True))
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        again = prog.joint_scores(v.clone().requires_grad_(True))       # announced once
+        fused = prog.joint_scores(v)                                     # the fused path never warns
+    assert torch.equal(on_graph, again) and torch.allclose(on_graph.detach(), fused, rtol=1e-4, atol=0)
+
+
 class _MinMax:
     """Shape of the normaliser the scripts use: attributes a, b; decode(x) = (x - b) / a
     [ref: Tests/test_ns.py:111-134; class in the un-vendored Neural_PDE package]."""
