@@ -101,7 +101,8 @@ def k1_traffic(workload, equation=None, points=None):
         return {"bytes": k * (d["dram_bytes_read"] + d["dram_bytes_write"]), "read": k * d["dram_bytes_read"],
                 "write": k * d["dram_bytes_write"], "algorithmic": k * d["algorithmic_bytes"],
                 "over_algorithmic": (d["dram_bytes_read"] + d["dram_bytes_write"]) / d["algorithmic_bytes"],
-                "scaled_from_points": d.get("points_per_launch"), "source": d["source"]}
+                "scaled_from_points": d.get("points_per_launch"), "source": d["source"],
+                "cover_launch_over_algorithmic": (d.get("cover_launch") or {}).get("traffic_over_algorithmic")}
     except (OSError, ValueError, KeyError):
         return None
 

@@ -26,7 +26,7 @@ def main(path, workload, equation=None, samples=None):
     col = {h: i for i, h in enumerate(hdr)}
     w = bench.WORKLOADS[workload]
     nf = bench.MHD_EQUATIONS[equation] if workload == "mhd" else w["nf"]
-    rec = None
+    rec = cover = None
     for r in rows[2:]:
         name = r[col["Kernel Name"]]
         if "star_kernel" not in name:
@@ -34,13 +34,16 @@ def main(path, workload, equation=None, samples=None):
         rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
         wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
         if wr < 0.05 * rd:          # a COVER / SCORE launch: nothing written
+            if cover is None:
+                cover = {"kernel": name[:160], "dram_bytes_read": rd, "dram_bytes_write": wr}
+            continue
+        if rec is not None:
             continue
         grid = int(r[col["launch__grid_size"]].replace(",", ""))
         ms = float(r[col["gpu__time_duration.sum"]].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(
             units[col["gpu__time_duration.sum"]], 1e-6)
         rec = {"kernel": name[:160], "workload": workload, "grid": grid, "dram_bytes_read": rd, "dram_bytes_write": wr,
                "ncu_duration_ms": ms}
-        break
     assert rec is not None, "no STORE launch of star_kernel in the capture"
     # algorithmic bytes of the captured launch: (4F + 4) B per point; points from the written bytes (4 B per point)
     import numpy as np
@@ -53,6 +56,12 @@ def main(path, workload, equation=None, samples=None):
     rec["points_per_launch"] = points
     rec["samples_per_launch"] = samples
     rec["traffic_over_algorithmic"] = (rec["dram_bytes_read"] + rec["dram_bytes_write"]) / rec["algorithmic_bytes"]
+    if cover is not None:
+        # the COVER launch of the same step (validation half, as many samples as the STORE launch in bench.py's split):
+        # reads the fields + the per-cell band tile, writes per-sample counters only
+        cover["algorithmic_bytes"] = 4 * nf * points
+        cover["traffic_over_algorithmic"] = (cover["dram_bytes_read"] + cover["dram_bytes_write"]) / cover["algorithmic_bytes"]
+        rec["cover_launch"] = cover
     rec["kernel_source_sha"] = bench.kernel_source_sha()
     rec["source"] = f"ncu --set full --clock-control none, {os.path.basename(path)} (first STORE launch of star_kernel)"
     name = f"k1_traffic_{workload}" + (f"_{equation}" if workload == "mhd" else "") + ".json"
