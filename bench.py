@@ -28,7 +28,8 @@ HBM, CUDA-event timed, max over ranks.  `e2e` = the same step through the public
 (pinned) inputs streamed to the device in batch chunks and qhat + coverage read back.  `roofline` is
 for the dominant kernel (K1 STORE): algorithmic bytes (4F+4 per point) / its own CUDA-event duration
 vs the measured HBM peak in MEASURED_PEAKS.json.  `cpu_baseline` / `--impl reference` time the
-reference's CPU path (oracle/torch_port.py: F.conv3d + elementwise + NumPy quantile, all host threads)
+reference's CPU path (oracle/ref_arm.py: the reference's own operators and residual functions from the build-time
+snapshot, all host threads; oracle/torch_port.py, the restated port, only where the snapshot is absent)
 on a bounded sample of the same workload: the full batch on a slab of time planes -- measured, not
 extrapolated.  With --gpus N (torchrun) the batch axis is sharded (cp_pre_b200/dist.py).
 """
@@ -522,7 +523,7 @@ class E2E:
 
 
 # ----------------------------------------------------------------------------------------
-# the reference's CPU path (oracle/torch_port.py) -- cpu_baseline leg and --impl reference
+# the reference's CPU path (oracle/ref_arm.py, else oracle/torch_port.py) -- cpu_baseline leg and --impl reference
 # ----------------------------------------------------------------------------------------
 def cpu_arm():
     """(module, kind) of the CPU arm: the reference's own code when the build-time snapshot (or the checkout)
@@ -586,6 +587,101 @@ def cpu_pipeline(args, bs, nt, seed=99, threads=None, chunk=32):
     t_cp = time.perf_counter() - t0
     pts = bs * int(np.prod(grid))
     return pts, t_pre + t_cp, {"pre_s": t_pre, "cp_s": t_cp}, kind
+
+
+def joint_slab_check(args, device, bs=128, nt=4, seed=4242):
+    """Joint lines only: the CPU arm's joint CP and the GPU flow on the SAME seeded slab ([bs, F, nt, Nx(, Ny)], half
+    calibration / half validation), so that the empirical coverage a Joint line prints can be told apart from a bug.
+    With few calibration samples the reference's algorithm itself under-covers (the modulation and the scores come from
+    the same samples): the check is that the GPU flow lands on the CPU arm's number, not on 1 - alpha.
+    [ref: Joint/MHD_Residuals_CP.py:340-360,405-420; Joint/NS_Residuals_CP.py:289-312]"""
+    from cp_pre_b200 import ops
+    from cp_pre_b200.Neural_PDE.UQ.inductive_cp import calibrate_rank
+    from oracle import synth
+    arm, kind = cpu_arm()
+    torch.set_num_threads(os.cpu_count())           # torchrun pins OMP_NUM_THREADS=1 for its workers
+    w = WORKLOADS[args.workload]
+    grid = (nt,) + tuple(w["grid"][1:])
+    eps = 1e-6 if args.workload == "mhd" else 0.0
+    v = torch.from_numpy(synth.fields(seed, w["nf"], (bs,) + grid, positive=(0, 3) if args.workload == "mhd" else ()))
+    if w["nf"] == 1:
+        v = v[:, 0]
+    n_cal = bs // 2
+    res = cpu_residual_fn(args, arm, kind)(v).contiguous()
+    q_cpu, _, cov_cpu = arm.joint_cp(res[:n_cal], res[n_cal:], ALPHA, eps)
+    # the GPU flow of JointStep on one GPU: K1 STORE -> K2 modulation -> K2 scores -> K3d -> K1 COVER
+    prog = make_program(args.workload, args.equation)
+    vg = v.to(device)
+    store = torch.empty((n_cal,) + grid, dtype=torch.float32, device=device)
+    prog._run(vg[:n_cal], out=prog._unsq(store))
+    mod, _ = ops.cell_modulation(store, None, eps)
+    masked = torch.full_like(mod, float("inf"))
+    prog._crop(masked).copy_(prog._crop(mod))
+    qhat = ops.radix_select(ops.joint_score(store, None, masked), calibrate_rank(n_cal, n_cal, ALPHA))
+    inside = prog.coverage_counts(vg[n_cal:], qhat, mod)
+    cov_gpu = float((inside == prog.interior_cells(vg.shape)).double().mean())
+    q_cpu, q_gpu = float(np.asarray(q_cpu).reshape(-1)[0]), float(qhat)
+    return {"slab": list(v.shape), "n_cal": n_cal, "n_val": bs - n_cal, "cpu_arm_kind": kind,
+            "coverage_cpu_arm": float(cov_cpu), "coverage_gpu": cov_gpu, "qhat_cpu_arm": q_cpu, "qhat_gpu": q_gpu,
+            "qhat_rel_diff": abs(q_gpu - q_cpu) / max(abs(q_cpu), 1e-30),
+            "coverage_equals_cpu_arm": bool(abs(cov_gpu - float(cov_cpu)) <= 1.0 / (bs - n_cal) + 1e-12),
+            "tolerance": "one validation sample (fp32 residuals of the two arms differ in the last bits)"}
+
+
+_ELASTIC_ENV = ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE", "ROLE_RANK",
+                "ROLE_WORLD_SIZE", "ROLE_NAME", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS")
+
+
+def run_other_configs(args, world, budget_s=400.0):
+    """The default (`--workload ns`) run also carries a SHORT run of every other configuration, so that the one command
+    the driver launches shows them on its own box: each in a process (group) of its own on the same GPUs -- this
+    process idles meanwhile, its ranks waiting on the host, not in a collective -- through the same bench.py, with its
+    own timed region, clock record, checks and e2e leg.  The headline keys are untouched; these lines are extra.
+    mhd: the real configs[4] (BS = 2048 over the ranks) from 4 GPUs up, 256 samples per GPU below that."""
+    import socket
+    plans = [("mhd", ["--global-batch", str(256 * world)] if world < 4 else []), ("wave-joint", [])]
+    if world == 1:
+        plans += [("burgers", []), ("advection", [])]
+    env = {k: v for k, v in os.environ.items() if k not in _ELASTIC_ENV and not k.startswith("TORCHELASTIC_")}
+    out, t0 = {}, time.time()
+    for wl, extra in plans:
+        left = budget_s - (time.time() - t0)
+        if left < 45:
+            out[wl] = {"skipped": "time budget of the default run used up"}
+            continue
+        w = WORKLOADS[wl]
+        per, _, _ = geometry(argparse.Namespace(workload=wl, global_batch=int(extra[1]) if extra else 0), world)
+        host_bytes = per * w["nf"] * int(np.prod(w["grid"])) * 4 * world      # the e2e leg pins the whole host batch
+        try:
+            import psutil
+            e2e_ok = psutil.virtual_memory().available > 2.5 * host_bytes
+        except Exception:
+            e2e_ok = host_bytes < (64 << 30)
+        cmd = [sys.executable]
+        if world > 1:
+            with socket.socket() as sk:
+                sk.bind(("127.0.0.1", 0))
+                port = sk.getsockname()[1]
+            cmd += ["-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+                    "--master-port", str(port)]
+        cmd += [os.path.join(ROOT, "bench.py"), "--gpus", str(world), "--workload", wl, "--steps", str(max(2, min(args.steps, 10))),
+                "--warmup", "3", "--no-cpu", "--slab-check", "--no-other-configs"] + extra + ([] if e2e_ok else ["--no-e2e"])
+        t1 = time.time()
+        try:
+            r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=max(45.0, min(left, 240.0)))
+            d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+            roof = d.get("roofline") or {}
+            out[wl] = {"metric": d.get("metric"), "value": d.get("value"), "unit": d.get("unit"), "n_gpus": d.get("n_gpus"),
+                       "steps": d.get("steps"), "ms_per_step": d.get("ms_per_step"), "scaling": d.get("scaling"),
+                       "config": d.get("config"), "checks": d.get("checks"),
+                       "roofline": {"kernel": roof.get("kernel"), "frac": roof.get("frac"), "achieved": roof.get("achieved"),
+                                    "peak": roof.get("peak"), "cover_kernel_frac": (roof.get("cover_kernel") or {}).get("frac"),
+                                    "step_algorithmic_frac": (roof.get("step") or {}).get("algorithmic_frac")},
+                       "e2e": d.get("e2e") if e2e_ok else {"skipped": "host RAM too small to pin this batch"},
+                       "gpu_launches": d.get("gpu_launches"), "clocks": d.get("clocks"), "wall_s": time.time() - t1}
+        except Exception as e:
+            out[wl] = {"error": f"{type(e).__name__}: {str(e)[:300]}", "wall_s": time.time() - t1}
+    return out
 
 
 CPU_SAMPLE = {   # (batch, time planes) of the bounded CPU sample: the FULL per-GPU batch (the calibration set keeps
@@ -781,7 +877,7 @@ def run_advection(args):
                                          "l2": "4.3 MB of inputs: L2-resident and launch-latency bound by construction (CPU-scale config)"},
         "checks": {"empirical_coverage_per_alpha": cov, "cpu_arm_coverage_per_alpha": cpu_cov, "coverage_equals_cpu_arm": ok,
                    "kernel_path": path},
-        "roofline": {"bound": "hbm", "kernel": "generic_kernel<linear> (K1g: Nx=197 is ragged), STORE of the test-set residual",
+        "roofline": {"bound": "hbm", "kernel": f"K1 on the '{path}' path (Nx=197 rows are ragged: no TMA tiles), STORE of the test-set residual",
                      "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                      "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
                      "bytes_per_point": 8, "kernel_ms": k1_ms, "points_per_launch": ADV_N_TEST * 10 * 197,
@@ -830,6 +926,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-full-cpu", action="store_true")
+    ap.add_argument("--slab-check", action="store_true", help="Joint lines: run the CPU-arm coverage check even with --no-cpu")
+    ap.add_argument("--no-other-configs", action="store_true",
+                    help="ns workload: do not append the short runs of the other configurations (other_configs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -972,6 +1071,31 @@ def main():
                 "bytes_per_point": 2 * step.nf + 4, "achieved": (2 * step.nf + 4) * bpts / (bms * 1e-3) / 1e9,
                 "kernel_gpoints_s": bpts / (bms * 1e-3) / 1e9}
         del vb
+    slab = None
+    if kind == "joint" and rank == 0 and (args.slab_check or not args.no_cpu):
+        try:
+            slab = joint_slab_check(args, device)
+        except Exception as e:                   # the check must never cost the line its timing
+            slab = {"error": f"{type(e).__name__}: {e}"}
+    others = None
+    if args.workload == "ns" and not args.no_other_configs:
+        # free this run's device and pinned memory first; the other ranks wait on the HOST (a file flag, not a
+        # collective: a barrier kernel spinning on their GPUs would disturb the runs below)
+        flag = os.path.join("/tmp", f"cppre_bench_others_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}")
+        if rank == 0 and os.path.exists(flag):
+            os.remove(flag)
+        barrier()
+        step.vars = step.store = None
+        torch.cuda.empty_cache()
+        if rank == 0:
+            try:
+                others = run_other_configs(args, world)
+            finally:
+                open(flag, "w").close()
+        else:
+            t_wait = time.time()
+            while not os.path.exists(flag) and time.time() - t_wait < 900:
+                time.sleep(0.25)
     sys.stdout.flush()
     os.dup2(real_stdout, 1)
     if rank == 0:
@@ -1001,7 +1125,7 @@ def main():
                        "calibration_equals_independent_torch_path": verified,
                        "what": "marginal: 4096 random cells of qhat == torch.kthvalue on the gathered score columns; joint: "
                                "qhat == torch.kthvalue on the gathered scores and modulation == fp64 std of 4096 gathered columns (1e-6)",
-                       "quantile_overflow_check": quantile_check},
+                       "quantile_overflow_check": quantile_check, "joint_coverage_vs_cpu_arm": slab},
             "roofline": {"bound": "hbm", "kernel": f"star_kernel<{step.prog.name}> (K1: TMA stencil, STORE epilogue)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_nominal_8000_gbs": achieved / 8000.0,
@@ -1028,6 +1152,7 @@ def main():
                                          "bytes_per_score": cal_bpp, "share_of_step": cal_ms / ms},
                          "bf16_input_mode": bf16},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+            "other_configs": others,
         }))
     sys.stdout.flush()
     os.dup2(2, 1)
